@@ -1,0 +1,140 @@
+/*
+ * cudasw.h - C ABI of libcudasw.so, the B200-native batched Smith-Waterman engine that drops in
+ * behind GRIDSS's `Aligner.align_smith_waterman` (reference: src/main/java/au/edu/wehi/idsv/
+ * alignment/Aligner.java:10, SswJniAligner.java:42-61).
+ *
+ * Plain pointers and sizes only; no torch / C++ types. Every entry point names the reference
+ * interface it replaces. All functions return 0 (CUDASW_OK) or a negative CUDASW_E* code and never
+ * abort the process (the reference's native code calls exit(1) on oversize direction matrices,
+ * SURVEY.md §5 "Failure detection").
+ *
+ * There is NO CPU fallback in this library: if no CUDA device is usable, cudasw_create fails with
+ * CUDASW_ECUDA.
+ */
+#ifndef CUDASW_H
+#define CUDASW_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CUDASW_OK 0
+#define CUDASW_EINVAL (-1)    /* bad argument (maps to java.lang.IllegalArgumentException) */
+#define CUDASW_ENOMEM (-2)    /* host or device allocation failed */
+#define CUDASW_ECUDA (-3)     /* CUDA runtime error; see cudasw_last_error */
+#define CUDASW_ETOOLARGE (-4) /* pair exceeds the engine's limits (per-pair status only) */
+#define CUDASW_EUNDEF (-5)    /* per-pair: the reference's own traceback is undefined here */
+
+/* CIGAR op codes of the packed `(len << 4) | op` words (BAM numbering; the reference's native
+ * to_cigar_int uses M=0,I=1,D=2 and SswJniAligner.java:52-59 adds the S runs in Java). */
+#define CUDASW_CIGAR_M 0u
+#define CUDASW_CIGAR_I 1u
+#define CUDASW_CIGAR_D 2u
+#define CUDASW_CIGAR_S 4u
+
+/* One result per pair. Replaces ssw.Alignment (ctor sig (SSIIIIILjava/lang/String;)V in
+ * repo/ssw/ssw/1.0/ssw-1.0.jar) + the soft-clip wrapping of SswJniAligner.java:52-60.
+ * `ref_begin` is Alignment.getStartPosition() (Alignment.java:23); the CIGAR words
+ * cigar_blob[cigar_off .. cigar_off+cigar_len) render to Alignment.getCigar() (Alignment.java:30). */
+typedef struct cudasw_result {
+    int32_t score;      /* score1 */
+    int32_t ref_begin;  /* 0-based start on ref; -1 when score == 0 (reference behaviour) */
+    int32_t ref_end;    /* 0-based inclusive end on ref */
+    int32_t read_begin; /* 0-based first aligned query base  (= leading soft clip length) */
+    int32_t read_end;   /* 0-based last aligned query base */
+    int32_t cigar_off;  /* offset into the cigar blob, in uint32 words */
+    int32_t cigar_len;  /* number of packed ops, soft clips included */
+    int32_t status;     /* CUDASW_OK or a per-pair CUDASW_E* */
+} cudasw_result;
+
+/* Scoring. Replaces SswJniAligner(int match, int mismatch, int ambiguous, int gapOpen,
+ * int gapExtend) (SswJniAligner.java:13-17) as built by AlignerFactory.create(...)
+ * (AlignerFactory.java:108-120; defaults 1,-4,-4,6,1 at :90). Symbol classes after clean():
+ * equal symbols (N vs N included) -> match; both in ACGT and different -> mismatch; otherwise
+ * ambiguous (SswJniAligner.java:19-33). A k-base gap costs gapOpen + (k-1)*gapExtend. */
+typedef struct cudasw_scoring {
+    int32_t match, mismatch, ambiguous, gap_open, gap_extend;
+} cudasw_scoring;
+
+typedef struct cudasw cudasw_t; /* opaque engine handle: owns device memory, pinned staging, streams */
+
+/* Counters of the last cudasw_align_batch call on a handle (device time from CUDA events). */
+typedef struct cudasw_stats {
+    uint64_t pairs;
+    uint64_t cells;            /* sum of query_len * window_len (forward matrix cells) */
+    uint64_t kernel_launches;  /* kernels of this library launched for the batch */
+    float ms_total;            /* H2D + kernels + D2H, device-timed */
+    float ms_h2d, ms_pack, ms_forward, ms_reverse, ms_traceback, ms_d2h;
+    uint64_t h2d_bytes, d2h_bytes;
+    uint64_t forward_cells_padded; /* cells actually computed by the forward kernels */
+} cudasw_stats;
+
+/* Create an engine on CUDA device `device`. Replaces the AlignerFactory static initialiser's
+ * System.load + self-test (AlignerFactory.java:55-84): fails (no fallback) if the device or the
+ * kernels are unusable. Validation mirrors ssw.Aligner.align: 0 <= gap < 256 and |score| <= 127. */
+int cudasw_create(const cudasw_scoring* scoring, int device, cudasw_t** out);
+void cudasw_destroy(cudasw_t* h);
+
+/* Batched Aligner.align_smith_waterman (Aligner.java:10): pair i aligns
+ * seq_blob[seq_off[i]..seq_off[i+1]) inside ref_blob[ref_off[i]..ref_off[i+1]).
+ * Bytes are raw ASCII in any case; the clean() map of SswJniAligner.java:71-79 (upper-case,
+ * non-ACGT -> N) is applied on the device. Offsets have n_pairs+1 entries. Empty seq or ref ->
+ * per-pair CUDASW_EINVAL (SswJniAligner.java:45-50 throws IllegalArgumentException).
+ * `out` has n_pairs entries; CIGAR words are appended to cigar_blob (capacity cigar_cap words);
+ * if capacity is exceeded the call returns CUDASW_ENOMEM and *cigar_used holds the needed size.
+ * Host buffers may be pageable or pinned; results are complete on return. Thread-safe per handle
+ * (calls serialise on the handle, like -Dsswjni.sync=true, SswJniAligner.java:36-40,62-64). */
+int cudasw_align_batch(cudasw_t* h, int64_t n_pairs,
+                       const uint8_t* seq_blob, const int64_t* seq_off,
+                       const uint8_t* ref_blob, const int64_t* ref_off,
+                       cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap,
+                       int64_t* cigar_used);
+
+/* Same hot path with inputs already resident in device memory (what bench.py's `value` times).
+ * d_* are device pointers on the handle's device; out/cigar are HOST buffers. */
+int cudasw_align_batch_device(cudasw_t* h, int64_t n_pairs,
+                              const uint8_t* d_seq_blob, const int64_t* d_seq_off,
+                              const uint8_t* d_ref_blob, const int64_t* d_ref_off,
+                              const int64_t* h_seq_off, const int64_t* h_ref_off,
+                              cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap,
+                              int64_t* cigar_used);
+
+/* Device-memory helpers so a torch-free host (the JNI shim, the ctypes mirror) can stage inputs. */
+int cudasw_device_alloc(cudasw_t* h, size_t bytes, void** dptr);
+int cudasw_device_free(cudasw_t* h, void* dptr);
+int cudasw_upload(cudasw_t* h, void* dptr, const void* src, size_t bytes);
+/* Pinned host staging (the JNI shim hands these out as direct ByteBuffers). */
+int cudasw_host_alloc(size_t bytes, void** hptr);
+int cudasw_host_free(void* hptr);
+
+/* Async trio modelled on StreamingAligner.asyncAlign/flush/getAlignment
+ * (StreamingAligner.java:10-44) and BwaStreamingAligner's size-triggered flush
+ * (BwaStreamingAligner.java:79-127): submit copies the pair into the handle's pending batch and
+ * returns a ticket; flush runs every pending pair as one batch; poll fetches a finished ticket. */
+int cudasw_submit(cudasw_t* h, const uint8_t* seq, int64_t seq_len, const uint8_t* ref,
+                  int64_t ref_len, int64_t* ticket);
+int cudasw_flush(cudasw_t* h);
+int64_t cudasw_outstanding(cudasw_t* h); /* submitted, not yet flushed */
+int64_t cudasw_processed(cudasw_t* h);   /* flushed, not yet polled */
+/* Returns 1 and fills res/cigar (up to cigar_cap words, *cigar_len = words needed) if the ticket
+ * is done, 0 if it is still pending, <0 on error (unknown ticket -> CUDASW_EINVAL). */
+int cudasw_poll(cudasw_t* h, int64_t ticket, cudasw_result* res, uint32_t* cigar,
+                int32_t cigar_cap, int32_t* cigar_len);
+
+int cudasw_get_stats(cudasw_t* h, cudasw_stats* out);
+const char* cudasw_last_error(cudasw_t* h); /* h may be NULL: last create() error */
+int cudasw_device_count(void);
+const char* cudasw_version(void);
+
+/* Render packed ops as the reference's CIGAR string ("4S78M45S"); returns bytes written
+ * (excluding NUL) or CUDASW_EINVAL if `cap` is too small. Replaces s_align_cigar_to_jstring
+ * (libsswjni.so 0xa6c) + the string concat in SswJniAligner.java:52-59. */
+int cudasw_cigar_string(const uint32_t* ops, int32_t n_ops, char* buf, int32_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUDASW_H */
