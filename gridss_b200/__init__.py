@@ -1,0 +1,31 @@
+"""gridss_b200 - B200-native batched Smith-Waterman engine behind GRIDSS's `Aligner` interface.
+
+Host-side mirror of the reference interface for the hot path only
+(reference: src/main/java/au/edu/wehi/idsv/alignment/{Aligner,Alignment,AlignerFactory,
+SswJniAligner,StreamingAligner}.java). All arithmetic happens in libcudasw.so (hand-written
+sm_100a CUDA kernels, C ABI in include/cudasw.h). There is no CPU fallback: importing works
+anywhere, constructing an aligner without the CUDA library or without a GPU raises.
+"""
+from .aligner import (  # noqa: F401
+    Aligner,
+    AlignerFactory,
+    Alignment,
+    BatchingAligner,
+    CudaAligner,
+    CudaSwError,
+    RESULT_DTYPE,
+    cigar_string,
+    load_library,
+)
+
+__all__ = [
+    "Aligner",
+    "AlignerFactory",
+    "Alignment",
+    "BatchingAligner",
+    "CudaAligner",
+    "CudaSwError",
+    "RESULT_DTYPE",
+    "cigar_string",
+    "load_library",
+]

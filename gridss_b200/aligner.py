@@ -1,0 +1,395 @@
+"""Python mirror of the reference's Aligner API over the C ABI of libcudasw.so (ctypes).
+
+Mirrors, name for name where Python allows:
+  Aligner.align_smith_waterman(seq, ref) -> Alignment           alignment/Aligner.java:10
+  Alignment.getStartPosition() / getCigar()                      alignment/Alignment.java:23,30
+  AlignerFactory.create() / create(match, mismatch, ambiguous, gapOpen, gapExtend)
+                                                                 alignment/AlignerFactory.java:108-120
+  StreamingAligner-style asyncAlign / flush / getAlignment       alignment/StreamingAligner.java:10-44
+Error behaviour follows SswJniAligner.java:45-50 (empty seq/ref -> IllegalArgumentException, here
+ValueError) and ssw.Aligner.align's argument checks (gap in [0,255], |score| <= 127).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+from typing import Iterable, Sequence
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libcudasw.so")
+
+CUDASW_OK = 0
+CUDASW_EINVAL = -1
+CUDASW_ENOMEM = -2
+CUDASW_ECUDA = -3
+CUDASW_ETOOLARGE = -4
+CUDASW_EUNDEF = -5
+
+RESULT_DTYPE = np.dtype(
+    [
+        ("score", "<i4"),
+        ("ref_begin", "<i4"),
+        ("ref_end", "<i4"),
+        ("read_begin", "<i4"),
+        ("read_end", "<i4"),
+        ("cigar_off", "<i4"),
+        ("cigar_len", "<i4"),
+        ("status", "<i4"),
+    ]
+)
+_OPS = "MIDNSHP=X"
+
+
+class CudaSwError(RuntimeError):
+    pass
+
+
+class _Scoring(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in ("match", "mismatch", "ambiguous", "gap_open", "gap_extend")]
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [
+        ("pairs", ctypes.c_uint64),
+        ("cells", ctypes.c_uint64),
+        ("kernel_launches", ctypes.c_uint64),
+        ("ms_total", ctypes.c_float),
+        ("ms_h2d", ctypes.c_float),
+        ("ms_pack", ctypes.c_float),
+        ("ms_forward", ctypes.c_float),
+        ("ms_reverse", ctypes.c_float),
+        ("ms_traceback", ctypes.c_float),
+        ("ms_d2h", ctypes.c_float),
+        ("h2d_bytes", ctypes.c_uint64),
+        ("d2h_bytes", ctypes.c_uint64),
+        ("forward_cells_padded", ctypes.c_uint64),
+    ]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+_lib = None
+_lib_lock = threading.Lock()
+
+# every symbol include/cudasw.h declares: (name, restype, argtypes)
+_vp, _i64, _i32, _sz = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, ctypes.c_size_t
+ABI = [
+    ("cudasw_create", ctypes.c_int, [ctypes.POINTER(_Scoring), ctypes.c_int, ctypes.POINTER(_vp)]),
+    ("cudasw_destroy", None, [_vp]),
+    ("cudasw_align_batch", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_align_batch_device", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_device_alloc", ctypes.c_int, [_vp, _sz, ctypes.POINTER(_vp)]),
+    ("cudasw_device_free", ctypes.c_int, [_vp, _vp]),
+    ("cudasw_upload", ctypes.c_int, [_vp, _vp, _vp, _sz]),
+    ("cudasw_host_alloc", ctypes.c_int, [_sz, ctypes.POINTER(_vp)]),
+    ("cudasw_host_free", ctypes.c_int, [_vp]),
+    ("cudasw_submit", ctypes.c_int, [_vp, _vp, _i64, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_flush", ctypes.c_int, [_vp]),
+    ("cudasw_outstanding", _i64, [_vp]),
+    ("cudasw_processed", _i64, [_vp]),
+    ("cudasw_poll", ctypes.c_int, [_vp, _i64, _vp, _vp, _i32, ctypes.POINTER(_i32)]),
+    ("cudasw_get_stats", ctypes.c_int, [_vp, ctypes.POINTER(Stats)]),
+    ("cudasw_last_error", ctypes.c_char_p, [_vp]),
+    ("cudasw_device_count", ctypes.c_int, []),
+    ("cudasw_version", ctypes.c_char_p, []),
+    ("cudasw_cigar_string", ctypes.c_int, [_vp, _i32, ctypes.c_char_p, _i32]),
+]
+
+
+def load_library():
+    """Load libcudasw.so (built in-tree by gridss_b200/build.py). Fails loudly if it is missing."""
+    global _lib
+    with _lib_lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise CudaSwError(
+                    f"{LIB_PATH} not built (run `python -m gridss_b200.build`); gridss_b200 has no CPU fallback"
+                )
+            lib = ctypes.CDLL(LIB_PATH)
+            for name, res, args in ABI:
+                fn = getattr(lib, name)
+                fn.restype = res
+                fn.argtypes = args
+            _lib = lib
+    return _lib
+
+
+def cigar_string(words: Iterable[int]) -> str:
+    return "".join(f"{int(w) >> 4}{_OPS[int(w) & 15]}" for w in words)
+
+
+def pack(seqs: Sequence[bytes]):
+    off = np.zeros(len(seqs) + 1, dtype=np.int64)
+    if len(seqs):
+        off[1:] = np.cumsum([len(s) for s in seqs])
+    blob = np.frombuffer(b"".join(bytes(s) for s in seqs), dtype=np.uint8)
+    if blob.size == 0:
+        blob = np.zeros(1, dtype=np.uint8)
+    return np.ascontiguousarray(blob), off
+
+
+class Alignment:
+    """alignment/Alignment.java:8-34."""
+
+    __slots__ = ("_start", "_cigar", "score")
+
+    def __init__(self, startPosition: int, cigar: str, score: int | None = None):
+        self._start = int(startPosition)
+        self._cigar = cigar
+        self.score = score
+
+    def getStartPosition(self) -> int:
+        return self._start
+
+    def getCigar(self) -> str:
+        return self._cigar
+
+    def __repr__(self):
+        return f"Alignment(startPosition={self._start}, cigar={self._cigar!r})"
+
+    def __eq__(self, other):
+        return isinstance(other, Alignment) and (self._start, self._cigar) == (other._start, other._cigar)
+
+
+class Aligner:
+    """alignment/Aligner.java:3-11."""
+
+    def align_smith_waterman(self, seq: bytes, ref: bytes) -> Alignment:  # pragma: no cover - interface
+        raise NotImplementedError
+
+
+class PinnedBuffer:
+    """Page-locked host memory from cudasw_host_alloc, exposed as a numpy uint8 array."""
+
+    def __init__(self, nbytes: int):
+        lib = load_library()
+        p = ctypes.c_void_p()
+        rc = lib.cudasw_host_alloc(max(1, nbytes), ctypes.byref(p))
+        if rc != 0:
+            raise CudaSwError("cudasw_host_alloc failed")
+        self.ptr = p.value
+        self.nbytes = nbytes
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * max(1, nbytes)).from_address(self.ptr))
+
+    def close(self):
+        if self.ptr:
+            load_library().cudasw_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class CudaAligner(Aligner):
+    """The drop-in for SswJniAligner (alignment/SswJniAligner.java:8-61) on one B200."""
+
+    def __init__(self, match=1, mismatch=-4, ambiguous=-4, gapOpen=6, gapExtend=1, device: int = 0):
+        lib = load_library()
+        self._lib = lib
+        self.scoring = (match, mismatch, ambiguous, gapOpen, gapExtend)
+        sc = _Scoring(match, mismatch, ambiguous, gapOpen, gapExtend)
+        h = ctypes.c_void_p()
+        rc = lib.cudasw_create(ctypes.byref(sc), device, ctypes.byref(h))
+        if rc != 0:
+            msg = (lib.cudasw_last_error(None) or b"").decode()
+            if rc == CUDASW_EINVAL:
+                raise ValueError(msg)  # IllegalArgumentException in the reference
+            raise CudaSwError(f"cudasw_create failed ({rc}): {msg}")
+        self._h = h
+        self.device = device
+
+    # -- lifecycle
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.cudasw_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _err(self) -> str:
+        return (self._lib.cudasw_last_error(self._h) or b"").decode()
+
+    # -- Aligner.align_smith_waterman (Aligner.java:10)
+    def align_smith_waterman(self, seq: bytes, ref: bytes) -> Alignment:
+        if seq is None or len(seq) == 0:
+            raise ValueError("seq must be non-zero size")  # SswJniAligner.java:45-47
+        if ref is None or len(ref) == 0:
+            raise ValueError("ref must be non-zero size")  # SswJniAligner.java:48-50
+        return self.align_batch([seq], [ref])[0]
+
+    # -- batched entry points
+    def align_blobs(self, seq_blob, seq_off, ref_blob, ref_off, cigar_cap: int | None = None):
+        """Host blobs (numpy uint8 + int64 offsets) -> (RESULT_DTYPE[n], uint32 cigar blob)."""
+        n = len(seq_off) - 1
+        res = np.zeros(n, dtype=RESULT_DTYPE)
+        cap = int(cigar_cap if cigar_cap is not None else max(64, 24 * n))
+        while True:
+            cig = np.zeros(cap, dtype=np.uint32)
+            used = ctypes.c_int64(0)
+            rc = self._lib.cudasw_align_batch(
+                self._h, n, seq_blob.ctypes.data, seq_off.ctypes.data, ref_blob.ctypes.data,
+                ref_off.ctypes.data, res.ctypes.data, cig.ctypes.data, cap, ctypes.byref(used))
+            if rc == CUDASW_ENOMEM and used.value > cap:
+                cap = int(used.value) + 16
+                continue
+            if rc != 0:
+                raise CudaSwError(f"cudasw_align_batch failed ({rc}): {self._err()}")
+            return res, cig[: used.value]
+
+    def align_blobs_device(self, d_seq, d_seq_off, d_ref, d_ref_off, h_seq_off, h_ref_off, res=None, cig=None):
+        """Inputs already resident in device memory (raw device pointers as ints)."""
+        n = len(h_seq_off) - 1
+        res = np.zeros(n, dtype=RESULT_DTYPE) if res is None else res
+        cig = np.zeros(max(64, 24 * n), dtype=np.uint32) if cig is None else cig
+        used = ctypes.c_int64(0)
+        rc = self._lib.cudasw_align_batch_device(
+            self._h, n, d_seq, d_seq_off, d_ref, d_ref_off, h_seq_off.ctypes.data, h_ref_off.ctypes.data,
+            res.ctypes.data, cig.ctypes.data, cig.size, ctypes.byref(used))
+        if rc != 0:
+            raise CudaSwError(f"cudasw_align_batch_device failed ({rc}): {self._err()}")
+        return res, cig[: used.value]
+
+    def align_batch(self, seqs: Sequence[bytes], refs: Sequence[bytes]) -> list[Alignment]:
+        """Alignment[] alignBatch(byte[][] seqs, byte[][] refs)."""
+        if len(seqs) != len(refs):
+            raise ValueError("seqs and refs differ in length")
+        for s, r in zip(seqs, refs):
+            if s is None or len(s) == 0:
+                raise ValueError("seq must be non-zero size")
+            if r is None or len(r) == 0:
+                raise ValueError("ref must be non-zero size")
+        sb, so = pack(seqs)
+        rb, ro = pack(refs)
+        res, cig = self.align_blobs(sb, so, rb, ro)
+        out = []
+        for r in res:
+            if r["status"] != 0:
+                raise CudaSwError(f"pair failed with status {int(r['status'])}")
+            out.append(Alignment(int(r["ref_begin"]), cigar_string(cig[r["cigar_off"] : r["cigar_off"] + r["cigar_len"]]), int(r["score"])))
+        return out
+
+    def stats(self) -> dict:
+        st = Stats()
+        self._lib.cudasw_get_stats(self._h, ctypes.byref(st))
+        return st.as_dict()
+
+    # -- async trio (StreamingAligner.java:10-44)
+    def submit(self, seq: bytes, ref: bytes) -> int:
+        if not seq or not ref:
+            raise ValueError("seq and ref must be non-zero size")
+        t = ctypes.c_int64(0)
+        s = np.frombuffer(bytes(seq), dtype=np.uint8)
+        r = np.frombuffer(bytes(ref), dtype=np.uint8)
+        rc = self._lib.cudasw_submit(self._h, s.ctypes.data, len(s), r.ctypes.data, len(r), ctypes.byref(t))
+        if rc != 0:
+            raise CudaSwError(f"cudasw_submit failed ({rc})")
+        return t.value
+
+    def flush(self) -> None:
+        rc = self._lib.cudasw_flush(self._h)
+        if rc != 0:
+            raise CudaSwError(f"cudasw_flush failed ({rc}): {self._err()}")
+
+    def outstanding(self) -> int:
+        return int(self._lib.cudasw_outstanding(self._h))
+
+    def processed(self) -> int:
+        return int(self._lib.cudasw_processed(self._h))
+
+    def poll(self, ticket: int) -> Alignment | None:
+        res = np.zeros(1, dtype=RESULT_DTYPE)
+        cap = 256
+        while True:
+            cig = np.zeros(cap, dtype=np.uint32)
+            need = ctypes.c_int32(0)
+            rc = self._lib.cudasw_poll(self._h, ticket, res.ctypes.data, cig.ctypes.data, cap, ctypes.byref(need))
+            if rc == CUDASW_ENOMEM and need.value > cap:
+                cap = need.value
+                continue
+            break
+        if rc == 0:
+            return None
+        if rc < 0:
+            raise KeyError(f"unknown ticket {ticket}")
+        r = res[0]
+        if r["status"] != 0:
+            raise CudaSwError(f"pair failed with status {int(r['status'])}")
+        return Alignment(int(r["ref_begin"]), cigar_string(cig[: need.value]), int(r["score"]))
+
+
+class BatchingAligner(Aligner):
+    """Caller-side batch-collect layer, modelled on BwaStreamingAligner's
+    size-triggered flush (alignment/BwaStreamingAligner.java:79-127) and the StreamingAligner
+    contract (alignment/StreamingAligner.java:10-44): asyncAlign queues, flush dispatches one GPU
+    batch, getAlignment returns results in submission order."""
+
+    def __init__(self, aligner: CudaAligner, batch_size: int = 65536):
+        self.aligner = aligner
+        self.batch_size = batch_size
+        self._tickets: list[int] = []
+        self._lock = threading.Lock()
+
+    def asyncAlign(self, seq: bytes, ref: bytes) -> int:
+        with self._lock:
+            t = self.aligner.submit(seq, ref)
+            self._tickets.append(t)
+            if self.aligner.outstanding() >= self.batch_size:
+                self.aligner.flush()
+            return t
+
+    def flush(self) -> None:
+        with self._lock:
+            self.aligner.flush()
+
+    def outstandingAlignmentRecord(self) -> int:
+        return self.aligner.outstanding()
+
+    def processedAlignmentRecords(self) -> int:
+        return self.aligner.processed()
+
+    def getAlignment(self) -> Alignment:
+        with self._lock:
+            if not self._tickets:
+                raise RuntimeError("no alignment record is available")  # IllegalStateException
+            a = self.aligner.poll(self._tickets[0])
+            if a is None:
+                raise RuntimeError("no alignment record is available; call flush()")
+            self._tickets.pop(0)
+            return a
+
+    def align_smith_waterman(self, seq: bytes, ref: bytes) -> Alignment:
+        t = self.asyncAlign(seq, ref)
+        with self._lock:
+            self.aligner.flush()
+            a = self.aligner.poll(t)
+            self._tickets.remove(t)
+        return a
+
+
+class AlignerFactory:
+    """alignment/AlignerFactory.java:108-120: one shared default instance (1,-4,-4,6,1 at :90);
+    create(...) with explicit scoring builds a new aligner. No fallback chain here: the reference
+    falls back SSW -> JAligner on the GRIDSS side, this package only provides the CUDA backend."""
+
+    _default: CudaAligner | None = None
+    _lock = threading.Lock()
+
+    @classmethod
+    def create(cls, match=None, mismatch=None, ambiguous=None, gapOpen=None, gapExtend=None, device: int = 0) -> CudaAligner:
+        if match is None:
+            with cls._lock:
+                if cls._default is None:
+                    cls._default = CudaAligner(1, -4, -4, 6, 1, device=device)
+                return cls._default
+        return CudaAligner(match, mismatch, ambiguous, gapOpen, gapExtend, device=device)

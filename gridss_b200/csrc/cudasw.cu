@@ -1,0 +1,585 @@
+// cudasw.cu - host side of libcudasw.so: engine handle, batch pipeline, C ABI (include/cudasw.h).
+//
+// Pipeline of one batch (all on one stream, no host round trip per pair):
+//   H2D blobs+offsets -> encode (clean(): SswJniAligner.java:71-79) -> bin pairs by query rows
+//   (device radix sort) -> forward score pass per variant -> bin by read_end -> reverse score pass
+//   -> banded traceback + CIGAR emission -> D2H results.
+// There is no CPU alignment path in this file or anywhere in the library.
+#include <cub/device/device_radix_sort.cuh>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "sw_kernels.cuh"
+
+using namespace cusw;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+#define CK(expr)                                                                              \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess) {                                                              \
+            set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));                   \
+            return CUDASW_ECUDA;                                                              \
+        }                                                                                     \
+    } while (0)
+
+typedef void (*score_launch_fn)(const int*, int, PairIO, const int4*, int4*, ScoreConst, cudaStream_t);
+
+template <int G, int R, bool REV>
+void launch_score(const int* order, int njobs, PairIO io, const int4* fwd, int4* out, ScoreConst sc,
+                  cudaStream_t st) {
+    constexpr int GPB = 128 / G;
+    int blocks = (njobs + GPB - 1) / GPB;
+    sw_score_kernel<G, R, REV><<<blocks, 128, 0, st>>>(order, njobs, io, fwd, out, sc);
+}
+
+struct Variant {
+    int G, R, rows;
+    score_launch_fn fwd, rev;
+};
+
+#define V(G, R) Variant{G, R, 2 * G * R, launch_score<G, R, false>, launch_score<G, R, true>}
+const Variant kVariants[] = {
+    V(1, 8),   V(1, 12),  V(1, 16),  V(1, 20),  V(1, 24),  V(2, 16),  V(2, 20),
+    V(2, 24),  V(4, 16),  V(4, 20),  V(4, 24),  V(8, 16),  V(8, 20),  V(8, 24),
+    V(16, 16), V(16, 20), V(16, 24), V(32, 16), V(32, 20), V(32, 24), V(32, 32),
+};
+#undef V
+constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n + n / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+}  // namespace
+
+struct cudasw {
+    int device = 0;
+    cudasw_scoring scoring{};
+    ScoreConst sc{};
+    TbConst tc{};
+    VariantTable vt{};
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8]{};
+    std::mutex mu;
+    std::string error;
+    cudasw_stats stats{};
+
+    // staged raw inputs (host API) and encoded copies
+    DevBuf<uint8_t> raw_seq, raw_ref, enc_seq, enc_ref;
+    DevBuf<int64_t> seq_off, ref_off;
+    DevBuf<uint32_t> keys, keys_alt;
+    DevBuf<int> vals, vals_alt, retry_a, retry_b;
+    DevBuf<int4> fwd, rev;
+    DevBuf<cudasw_result> res;
+    DevBuf<uint32_t> cig;
+    DevBuf<uint8_t> cub_tmp;
+    DevBuf<uint8_t> tb_pool;
+    int* d_hist = nullptr;  // 64 ints
+    unsigned long long* d_counters = nullptr;  // [0] pool used, [1] cigar used, [2] retry count(int)
+    int* h_hist = nullptr;                     // pinned
+    unsigned long long* h_counters = nullptr;  // pinned
+    size_t tb_pool_bytes = 0;
+
+    // async trio state
+    std::vector<uint8_t> pend_seq, pend_ref;
+    std::vector<int64_t> pend_seq_off{0}, pend_ref_off{0};
+    std::vector<int64_t> pend_tickets;
+    int64_t next_ticket = 1;
+    struct Done {
+        cudasw_result r;
+        std::vector<uint32_t> cigar;
+    };
+    std::unordered_map<int64_t, Done> done;
+
+    void set_error(const std::string& s) { error = s; }
+    int run(int64_t n, const uint8_t* d_seq, const int64_t* d_seq_off, const uint8_t* d_ref,
+            const int64_t* d_ref_off, int64_t total_q, int64_t total_w, cudasw_result* out,
+            uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used, bool inputs_on_host,
+            const uint8_t* h_seq, const int64_t* h_seq_off, const uint8_t* h_ref,
+            const int64_t* h_ref_off);
+};
+
+static uint32_t pack2(int v) { return ((uint32_t)v & 0xFFFFu) | (((uint32_t)v & 0xFFFFu) << 16); }
+
+extern "C" int cudasw_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+extern "C" const char* cudasw_version(void) { return "cudasw 0.1 (sm_100a)"; }
+
+extern "C" const char* cudasw_last_error(cudasw_t* h) {
+    return h ? h->error.c_str() : g_create_error.c_str();
+}
+
+extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out) {
+    if (!out) return CUDASW_EINVAL;
+    *out = nullptr;
+    cudasw_scoring sc = {1, -4, -4, 6, 1};  // AlignerFactory.java:90
+    if (s) sc = *s;
+    // ssw.Aligner.align argument checks (jar bytecode)
+    if (sc.gap_open < 0 || sc.gap_open > 255 || sc.gap_extend < 0 || sc.gap_extend > 255) {
+        g_create_error = "Gap open and extension penalties must be in [0, 255]";
+        return CUDASW_EINVAL;
+    }
+    if (std::abs(sc.match) > 127 || std::abs(sc.mismatch) > 127 || std::abs(sc.ambiguous) > 127) {
+        g_create_error = "Scoring matrix values must fit into signed 8-bit integer";
+        return CUDASW_EINVAL;
+    }
+    if (sc.mismatch > 0 || sc.ambiguous > 0 || sc.match < 0) {
+        g_create_error = "cudasw requires match >= 0 and mismatch, ambiguous <= 0";
+        return CUDASW_EINVAL;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                         " (libcudasw has no CPU fallback)";
+        return CUDASW_ECUDA;
+    }
+    if (device < 0 || device >= ndev) {
+        g_create_error = "device index out of range";
+        return CUDASW_EINVAL;
+    }
+    cudasw_t* h = new cudasw();
+    h->device = device;
+    h->scoring = sc;
+    auto fail = [&](const std::string& m) {
+        g_create_error = m;
+        delete h;
+        return CUDASW_ECUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess)
+        return fail(cudaGetErrorString(e));
+    for (auto& ev : h->ev)
+        if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_hist, 64 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
+        return fail(cudaGetErrorString(e));
+    if ((e = cudaMallocHost(&h->h_hist, 64 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMallocHost(&h->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
+        return fail(cudaGetErrorString(e));
+
+    // PRMT pool: x = qcode ^ wcode; 0 -> match, 1..3 -> mismatch, 4..7 -> ambiguous
+    auto b = [](int v) { return (uint32_t)(uint8_t)(int8_t)v; };
+    h->sc.poolA = b(sc.match) | (b(sc.mismatch) << 8) | (b(sc.mismatch) << 16) | (b(sc.mismatch) << 24);
+    h->sc.poolB = b(sc.ambiguous) * 0x01010101u;
+    h->sc.B = sc.gap_open;
+    h->sc.BB = pack2(sc.gap_open);
+    h->sc.GO2 = pack2(sc.gap_open);
+    h->sc.NGE2 = pack2(-sc.gap_extend);
+    h->tc = TbConst{sc.match, sc.mismatch, sc.ambiguous, sc.gap_open, sc.gap_extend};
+    h->vt.n = kNumVariants;
+    for (int i = 0; i < kNumVariants; i++) h->vt.rows[i] = kVariants[i].rows;
+
+    // self-test, like AlignerFactory's "A" vs "A" probe (AlignerFactory.java:74-84)
+    {
+        const uint8_t a[1] = {'A'};
+        const int64_t off[2] = {0, 1};
+        cudasw_result r;
+        uint32_t cg[4];
+        int64_t used = 0;
+        int rc = cudasw_align_batch(h, 1, a, off, a, off, &r, cg, 4, &used);
+        if (rc != CUDASW_OK || r.status != 0 || r.score != sc.match || r.cigar_len != 1 || cg[0] != (1u << 4)) {
+            std::string m = "self-test failed: " + h->error;
+            cudasw_destroy(h);
+            g_create_error = m;
+            return CUDASW_ECUDA;
+        }
+    }
+    *out = h;
+    return CUDASW_OK;
+}
+
+extern "C" void cudasw_destroy(cudasw_t* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    h->raw_seq.release(); h->raw_ref.release(); h->enc_seq.release(); h->enc_ref.release();
+    h->seq_off.release(); h->ref_off.release(); h->keys.release(); h->keys_alt.release();
+    h->vals.release(); h->vals_alt.release(); h->retry_a.release(); h->retry_b.release();
+    h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
+    h->cub_tmp.release(); h->tb_pool.release();
+    if (h->d_hist) cudaFree(h->d_hist);
+    if (h->d_counters) cudaFree(h->d_counters);
+    if (h->h_hist) cudaFreeHost(h->h_hist);
+    if (h->h_counters) cudaFreeHost(h->h_counters);
+    for (auto& ev : h->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
+                const uint8_t* d_ref_in, const int64_t* d_ref_off_in, int64_t total_q,
+                int64_t total_w, cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap,
+                int64_t* cigar_used, bool inputs_on_host, const uint8_t* h_seq,
+                const int64_t* h_seq_off, const uint8_t* h_ref, const int64_t* h_ref_off) {
+    std::lock_guard<std::mutex> lock(mu);
+    error.clear();
+    stats = cudasw_stats{};
+    if (cigar_used) *cigar_used = 0;
+    if (n < 0 || n > 0x7fffff00ll) { set_error("n_pairs out of range"); return CUDASW_EINVAL; }
+    if (n == 0) return CUDASW_OK;
+    if (!out || (!cigar_blob && cigar_cap > 0) || cigar_cap < 0) { set_error("null output"); return CUDASW_EINVAL; }
+    if (total_q < 0 || total_w < 0) { set_error("offsets must be non-decreasing from 0"); return CUDASW_EINVAL; }
+    CK(cudaSetDevice(device));
+    cudaStream_t st = stream;
+    uint64_t launches = 0;
+
+    // ---- capacity
+    CK(enc_seq.ensure((size_t)total_q + 16));
+    CK(enc_ref.ensure((size_t)total_w + 16));
+    CK(keys.ensure(n)); CK(keys_alt.ensure(n)); CK(vals.ensure(n)); CK(vals_alt.ensure(n));
+    CK(retry_a.ensure(n)); CK(retry_b.ensure(n));
+    CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n));
+    CK(cig.ensure((size_t)std::max<int64_t>(cigar_cap, 1)));
+    size_t cub_bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 26, st));
+    CK(cub_tmp.ensure(cub_bytes + 16));
+    if (!tb_pool.p) {
+        size_t free_b = 0, total_b = 0;
+        CK(cudaMemGetInfo(&free_b, &total_b));
+        size_t want = (size_t)8 << 30;
+        if (const char* e = getenv("CUDASW_TB_POOL_MB")) want = (size_t)atoll(e) << 20;
+        want = std::min(want, free_b / 4);
+        want = std::max(want, (size_t)64 << 20);
+        CK(tb_pool.ensure(want));
+        tb_pool_bytes = want;
+    }
+
+    CK(cudaEventRecord(ev[0], st));
+    // ---- H2D
+    const uint8_t* d_seq = d_seq_in;
+    const uint8_t* d_ref = d_ref_in;
+    const int64_t* d_so = d_seq_off_in;
+    const int64_t* d_ro = d_ref_off_in;
+    if (inputs_on_host) {
+        CK(raw_seq.ensure((size_t)total_q + 16));
+        CK(raw_ref.ensure((size_t)total_w + 16));
+        CK(seq_off.ensure(n + 1));
+        CK(ref_off.ensure(n + 1));
+        CK(cudaMemcpyAsync(raw_seq.p, h_seq, (size_t)total_q, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(raw_ref.p, h_ref, (size_t)total_w, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(seq_off.p, h_seq_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(ref_off.p, h_ref_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
+        d_seq = raw_seq.p; d_ref = raw_ref.p; d_so = seq_off.p; d_ro = ref_off.p;
+        stats.h2d_bytes = (uint64_t)total_q + (uint64_t)total_w + (uint64_t)(n + 1) * 16;
+    }
+    CK(cudaEventRecord(ev[1], st));
+
+    // ---- encode + forward binning
+    {
+        int64_t thr = (total_q + 15) / 16;
+        int blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
+        if (total_q > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq, enc_seq.p, total_q, 0u); launches++; }
+        thr = (total_w + 15) / 16;
+        blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
+        if (total_w > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref, enc_ref.p, total_w, 0x80u); launches++; }
+    }
+    PairIO io{enc_seq.p, enc_ref.p, d_so, d_ro};
+    const int max_rows = std::min(kVariants[kNumVariants - 1].rows,
+                                  scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
+    const int max_cols = (1 << 24) - 2;
+    CK(cudaMemsetAsync(d_hist, 0, 64 * sizeof(int), st));
+    fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, d_so, d_ro, vt, max_rows, max_cols,
+                                                           keys.p, vals.p, d_hist, res.p);
+    launches++;
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 26, st));
+    launches += 3;
+    CK(cudaMemcpyAsync(h_hist, d_hist, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(ev[2], st));
+    CK(cudaStreamSynchronize(st));
+
+    // ---- forward score pass
+    {
+        int64_t start = 0;
+        for (int v = 0; v < kNumVariants; v++) {
+            int cnt = h_hist[v];
+            if (cnt > 0) {
+                kVariants[v].fwd(vals_alt.p + start, cnt, io, nullptr, fwd.p, sc, st);
+                launches++;
+                stats.forward_cells_padded += 0;  // filled below from host offsets when available
+            }
+            start += cnt;
+        }
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ev[3], st));
+
+    // ---- reverse score pass
+    CK(cudaMemsetAsync(d_hist, 0, 64 * sizeof(int), st));
+    rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd.p, res.p, vt, keys.p, vals.p, d_hist);
+    launches++;
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 26, st));
+    launches += 3;
+    CK(cudaMemcpyAsync(h_hist, d_hist, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    {
+        int64_t start = 0;
+        for (int v = 0; v < kNumVariants; v++) {
+            int cnt = h_hist[v];
+            if (cnt > 0) {
+                kVariants[v].rev(vals_alt.p + start, cnt, io, fwd.p, rev.p, sc, st);
+                launches++;
+            }
+            start += cnt;
+        }
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ev[4], st));
+
+    // ---- traceback (+ retry rounds when the scratch pool runs out)
+    {
+        CK(cudaMemsetAsync(d_counters, 0, 8 * sizeof(unsigned long long), st));
+        TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+        int* retry_count = reinterpret_cast<int*>(d_counters + 2);
+        const int* list = nullptr;  // first round: every pair (sorted order of the reverse pass)
+        int cnt = (int)n;
+        list = vals_alt.p;
+        int* retry_out = retry_a.p;
+        for (int round = 0; round < 64 && cnt > 0; round++) {
+            sw_traceback_kernel<<<(cnt + 127) / 128, 128, 0, st>>>(list, cnt, io, fwd.p, rev.p, tc, pool, res.p,
+                                                                  cig.p, (unsigned long long)cigar_cap,
+                                                                  d_counters + 1, retry_out, retry_count);
+            launches++;
+            CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            int nretry = *reinterpret_cast<int*>(h_counters + 2);
+            if (nretry == 0) { cnt = 0; break; }
+            if (nretry == cnt && round > 0) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
+            // reset pool + retry counter, keep cigar counter
+            CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
+            CK(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned long long), st));
+            list = retry_out;
+            retry_out = (retry_out == retry_a.p) ? retry_b.p : retry_a.p;
+            cnt = nretry;
+        }
+        if (cnt > 0) { set_error("traceback did not converge"); return CUDASW_ENOMEM; }
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ev[5], st));
+
+    // ---- D2H
+    unsigned long long used = h_counters[1];
+    if (cigar_used) *cigar_used = (int64_t)used;
+    CK(cudaMemcpyAsync(out, res.p, (size_t)n * sizeof(cudasw_result), cudaMemcpyDeviceToHost, st));
+    unsigned long long ncopy = std::min<unsigned long long>(used, (unsigned long long)cigar_cap);
+    if (ncopy) CK(cudaMemcpyAsync(cigar_blob, cig.p, (size_t)ncopy * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(ev[6], st));
+    CK(cudaStreamSynchronize(st));
+    stats.d2h_bytes = (uint64_t)n * sizeof(cudasw_result) + ncopy * 4;
+
+    stats.pairs = (uint64_t)n;
+    stats.kernel_launches = launches;
+    cudaEventElapsedTime(&stats.ms_h2d, ev[0], ev[1]);
+    cudaEventElapsedTime(&stats.ms_pack, ev[1], ev[2]);
+    cudaEventElapsedTime(&stats.ms_forward, ev[2], ev[3]);
+    cudaEventElapsedTime(&stats.ms_reverse, ev[3], ev[4]);
+    cudaEventElapsedTime(&stats.ms_traceback, ev[4], ev[5]);
+    cudaEventElapsedTime(&stats.ms_d2h, ev[5], ev[6]);
+    cudaEventElapsedTime(&stats.ms_total, ev[0], ev[6]);
+    if (h_seq_off && h_ref_off) {
+        uint64_t cells = 0, padded = 0;
+        for (int64_t i = 0; i < n; i++) {
+            int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
+            if (q <= 0 || w <= 0) continue;
+            cells += (uint64_t)q * (uint64_t)w;
+            if (q <= max_rows) {
+                int v = 0;
+                while (v < kNumVariants - 1 && kVariants[v].rows < q) v++;
+                padded += (uint64_t)kVariants[v].rows * (uint64_t)(w + 2 * kVariants[v].G - 1);
+            }
+        }
+        stats.cells = cells;
+        stats.forward_cells_padded = padded;
+    }
+    if (used > (unsigned long long)cigar_cap) {
+        set_error("cigar buffer too small");
+        return CUDASW_ENOMEM;
+    }
+    return CUDASW_OK;
+}
+
+extern "C" int cudasw_align_batch(cudasw_t* h, int64_t n, const uint8_t* seq_blob,
+                                  const int64_t* seq_off, const uint8_t* ref_blob,
+                                  const int64_t* ref_off, cudasw_result* out, uint32_t* cigar_blob,
+                                  int64_t cigar_cap, int64_t* cigar_used) {
+    if (!h) return CUDASW_EINVAL;
+    if (n > 0 && (!seq_blob || !seq_off || !ref_blob || !ref_off)) { h->error = "null input"; return CUDASW_EINVAL; }
+    if (n > 0 && (seq_off[0] != 0 || ref_off[0] != 0)) { h->error = "offsets must start at 0"; return CUDASW_EINVAL; }
+    int64_t tq = n > 0 ? seq_off[n] : 0, tw = n > 0 ? ref_off[n] : 0;
+    return h->run(n, nullptr, nullptr, nullptr, nullptr, tq, tw, out, cigar_blob, cigar_cap, cigar_used, true,
+                  seq_blob, seq_off, ref_blob, ref_off);
+}
+
+extern "C" int cudasw_align_batch_device(cudasw_t* h, int64_t n, const uint8_t* d_seq_blob,
+                                         const int64_t* d_seq_off, const uint8_t* d_ref_blob,
+                                         const int64_t* d_ref_off, const int64_t* h_seq_off,
+                                         const int64_t* h_ref_off, cudasw_result* out,
+                                         uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used) {
+    if (!h) return CUDASW_EINVAL;
+    if (n > 0 && (!d_seq_blob || !d_seq_off || !d_ref_blob || !d_ref_off || !h_seq_off || !h_ref_off)) {
+        h->error = "null input";
+        return CUDASW_EINVAL;
+    }
+    int64_t tq = n > 0 ? h_seq_off[n] : 0, tw = n > 0 ? h_ref_off[n] : 0;
+    return h->run(n, d_seq_blob, d_seq_off, d_ref_blob, d_ref_off, tq, tw, out, cigar_blob, cigar_cap, cigar_used,
+                  false, nullptr, h_seq_off, nullptr, h_ref_off);
+}
+
+extern "C" int cudasw_device_alloc(cudasw_t* h, size_t bytes, void** dptr) {
+    if (!h || !dptr) return CUDASW_EINVAL;
+    if (cudaSetDevice(h->device) != cudaSuccess) return CUDASW_ECUDA;
+    cudaError_t e = cudaMalloc(dptr, bytes ? bytes : 1);
+    if (e != cudaSuccess) { h->error = cudaGetErrorString(e); return CUDASW_ENOMEM; }
+    return CUDASW_OK;
+}
+extern "C" int cudasw_device_free(cudasw_t* h, void* dptr) {
+    if (!h) return CUDASW_EINVAL;
+    cudaSetDevice(h->device);
+    return cudaFree(dptr) == cudaSuccess ? CUDASW_OK : CUDASW_ECUDA;
+}
+extern "C" int cudasw_upload(cudasw_t* h, void* dptr, const void* src, size_t bytes) {
+    if (!h || !dptr || !src) return CUDASW_EINVAL;
+    cudaSetDevice(h->device);
+    cudaError_t e = cudaMemcpyAsync(dptr, src, bytes, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) { h->error = cudaGetErrorString(e); return CUDASW_ECUDA; }
+    return CUDASW_OK;
+}
+extern "C" int cudasw_host_alloc(size_t bytes, void** hptr) {
+    if (!hptr) return CUDASW_EINVAL;
+    return cudaMallocHost(hptr, bytes ? bytes : 1) == cudaSuccess ? CUDASW_OK : CUDASW_ENOMEM;
+}
+extern "C" int cudasw_host_free(void* hptr) { return cudaFreeHost(hptr) == cudaSuccess ? CUDASW_OK : CUDASW_ECUDA; }
+
+extern "C" int cudasw_get_stats(cudasw_t* h, cudasw_stats* out) {
+    if (!h || !out) return CUDASW_EINVAL;
+    *out = h->stats;
+    return CUDASW_OK;
+}
+
+// ---- async trio (StreamingAligner.java:10-44 contract)
+extern "C" int cudasw_submit(cudasw_t* h, const uint8_t* seq, int64_t seq_len, const uint8_t* ref,
+                             int64_t ref_len, int64_t* ticket) {
+    if (!h || !ticket || seq_len < 0 || ref_len < 0 || (seq_len && !seq) || (ref_len && !ref)) return CUDASW_EINVAL;
+    std::lock_guard<std::mutex> lock(h->mu);
+    h->pend_seq.insert(h->pend_seq.end(), seq, seq + seq_len);
+    h->pend_ref.insert(h->pend_ref.end(), ref, ref + ref_len);
+    h->pend_seq_off.push_back((int64_t)h->pend_seq.size());
+    h->pend_ref_off.push_back((int64_t)h->pend_ref.size());
+    *ticket = h->next_ticket++;
+    h->pend_tickets.push_back(*ticket);
+    return CUDASW_OK;
+}
+
+extern "C" int cudasw_flush(cudasw_t* h) {
+    if (!h) return CUDASW_EINVAL;
+    std::vector<uint8_t> seq, ref;
+    std::vector<int64_t> so, ro, tickets;
+    {
+        std::lock_guard<std::mutex> lock(h->mu);
+        if (h->pend_tickets.empty()) return CUDASW_OK;
+        seq.swap(h->pend_seq); ref.swap(h->pend_ref);
+        so.swap(h->pend_seq_off); ro.swap(h->pend_ref_off);
+        tickets.swap(h->pend_tickets);
+        h->pend_seq_off.assign(1, 0);
+        h->pend_ref_off.assign(1, 0);
+    }
+    int64_t n = (int64_t)tickets.size();
+    std::vector<cudasw_result> res(n);
+    int64_t cap = (int64_t)seq.size() + 4 * n + 16, used = 0;
+    std::vector<uint32_t> cig(cap);
+    if (seq.empty()) seq.push_back(0);
+    if (ref.empty()) ref.push_back(0);
+    int rc = cudasw_align_batch(h, n, seq.data(), so.data(), ref.data(), ro.data(), res.data(), cig.data(), cap, &used);
+    std::lock_guard<std::mutex> lock(h->mu);
+    for (int64_t i = 0; i < n; i++) {
+        cudasw::Done d;
+        d.r = res[i];
+        if (rc != CUDASW_OK && d.r.status == CUDASW_OK) d.r.status = rc;
+        if (rc == CUDASW_OK && d.r.status == CUDASW_OK)
+            d.cigar.assign(cig.begin() + d.r.cigar_off, cig.begin() + d.r.cigar_off + d.r.cigar_len);
+        d.r.cigar_off = 0;
+        h->done.emplace(tickets[i], std::move(d));
+    }
+    return rc;
+}
+
+extern "C" int64_t cudasw_outstanding(cudasw_t* h) {
+    if (!h) return 0;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return (int64_t)h->pend_tickets.size();
+}
+extern "C" int64_t cudasw_processed(cudasw_t* h) {
+    if (!h) return 0;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return (int64_t)h->done.size();
+}
+
+extern "C" int cudasw_poll(cudasw_t* h, int64_t ticket, cudasw_result* res, uint32_t* cigar,
+                           int32_t cigar_cap, int32_t* cigar_len) {
+    if (!h || !res) return CUDASW_EINVAL;
+    std::lock_guard<std::mutex> lock(h->mu);
+    auto it = h->done.find(ticket);
+    if (it == h->done.end()) {
+        for (int64_t t : h->pend_tickets)
+            if (t == ticket) return 0;
+        return CUDASW_EINVAL;
+    }
+    int32_t need = (int32_t)it->second.cigar.size();
+    if (cigar_len) *cigar_len = need;
+    if (need > cigar_cap || (need && !cigar)) return CUDASW_ENOMEM;
+    *res = it->second.r;
+    if (need) memcpy(cigar, it->second.cigar.data(), (size_t)need * 4);
+    h->done.erase(it);
+    return 1;
+}
+
+extern "C" int cudasw_cigar_string(const uint32_t* ops, int32_t n_ops, char* buf, int32_t cap) {
+    static const char kOps[] = "MIDNSHP=X";
+    if (!buf || cap <= 0 || (n_ops && !ops)) return CUDASW_EINVAL;
+    int32_t o = 0;
+    for (int32_t i = 0; i < n_ops; i++) {
+        char tmp[16];
+        uint32_t op = ops[i] & 15u;
+        int k = snprintf(tmp, sizeof tmp, "%u%c", ops[i] >> 4, op < 9 ? kOps[op] : '?');
+        if (o + k >= cap) return CUDASW_EINVAL;
+        memcpy(buf + o, tmp, (size_t)k);
+        o += k;
+    }
+    buf[o] = 0;
+    return o;
+}

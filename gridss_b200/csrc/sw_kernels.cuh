@@ -1,0 +1,499 @@
+// sw_kernels.cuh - sm_100a device code of the batched Smith-Waterman engine.
+//
+// Replaces the native hot loops behind GRIDSS's Aligner.align_smith_waterman
+// (alignment/SswJniAligner.java:42-61 -> libsswjni.so: sw_sse2_byte / sw_sse2_word / banded_sw,
+// SURVEY.md §8a A4). Nothing here is translated from SSW: the score pass is an inter-task
+// register-resident wavefront (one pair per G-lane group, two virtual lanes per thread packed as
+// s16x2 DPX operands), not Farrar's striped layout.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/cudasw.h"
+
+namespace cusw {
+
+// ------------------------------------------------------------------------------------------
+// Encoded sequence bytes.
+//   code: A0 C1 G2 T3 N4 (SswJniAligner.clean, SswJniAligner.java:71-79), window pad 5, query pad 6
+//   query byte  = code * 0x11            (both nibbles = code)
+//   window byte = code * 0x11 ^ 0x80     (high nibble additionally carries PRMT's sign-replicate bit)
+// so that (query ^ window) is directly the PRMT selector pair {x | 8, x}, x = qcode ^ wcode, and
+//   prmt(pool) yields the int8 substitution score pool[x] sign-extended to s16.
+// x == 0 <=> equal symbols (match, N vs N included); x in 1..3 <=> both ACGT (mismatch);
+// x in 4..7 <=> exactly one N (ambiguous)  [SswJniAligner.createMatrix, SswJniAligner.java:19-33].
+// ------------------------------------------------------------------------------------------
+constexpr uint32_t kQueryPad = 6u * 0x11u;
+constexpr uint32_t kWindowPad = (5u * 0x11u) ^ 0x80u;
+
+__device__ __forceinline__ uint32_t base_code(uint32_t c) {
+    c &= 0xDFu;  // upper-case letters; non-letters never land on A/C/G/T
+    return c == 'A' ? 0u : c == 'C' ? 1u : c == 'G' ? 2u : c == 'T' ? 3u : 4u;
+}
+
+// Elementwise encode of a whole blob (layout unchanged, so per-pair offsets still apply).
+// HBM-bound: 1 byte in, 1 byte out; 16-byte vector accesses.
+__global__ void __launch_bounds__(256) encode_kernel(const uint8_t* __restrict__ in,
+                                                     uint8_t* __restrict__ out, int64_t n,
+                                                     uint32_t xor_mask) {
+    int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 16;
+    for (; i < n; i += stride) {
+        if (i + 16 <= n && ((reinterpret_cast<uintptr_t>(in + i) | reinterpret_cast<uintptr_t>(out + i)) & 15) == 0) {
+            uint4 v = *reinterpret_cast<const uint4*>(in + i);
+            uint32_t wds[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                uint32_t r = 0;
+#pragma unroll
+                for (int b = 0; b < 4; b++)
+                    r |= ((base_code((wds[k] >> (8 * b)) & 0xFFu) * 0x11u) ^ xor_mask) << (8 * b);
+                wds[k] = r;
+            }
+            *reinterpret_cast<uint4*>(out + i) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+        } else {
+            for (int64_t k = i; k < n && k < i + 16; k++)
+                out[k] = (uint8_t)((base_code(in[k]) * 0x11u) ^ xor_mask);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Score-pass variants: a pair occupies a group of G lanes; each thread owns two virtual lanes of
+// R query rows each, so one group covers 2*G*R rows.
+// ------------------------------------------------------------------------------------------
+struct ScoreConst {
+    uint32_t poolA, poolB;  // PRMT byte pool: pool[x] = substitution score of symbol-xor x
+    uint32_t BB;            // bias B = gap_open in both halves (stored value = true value + B)
+    uint32_t GO2;           // gap_open in both halves
+    uint32_t NGE2;          // -gap_extend in both halves (two's complement per half)
+    int32_t B;
+};
+
+struct PairIO {
+    const uint8_t* enc_seq;
+    const uint8_t* enc_ref;
+    const int64_t* seq_off;
+    const int64_t* ref_off;
+};
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t s) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(s));
+    return d;
+}
+
+// Sort keys. Forward: (variant, window length); reverse: (variant, columns to walk).
+// variant_of() is shared with the host dispatch table (cudasw.cu).
+struct VariantTable {
+    int n;
+    int rows[48];  // rows covered by variant v (ascending)
+};
+
+__device__ __forceinline__ int variant_of(const VariantTable& vt, int q) {
+    int v = 0;
+    while (v < vt.n - 1 && vt.rows[v] < q) v++;
+    return v;
+}
+
+// keys for the forward pass; hist[v] counts pairs per variant; slot vt.n counts invalid pairs
+__global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
+                                const int64_t* __restrict__ ref_off, VariantTable vt, int max_rows,
+                                int max_cols, uint32_t* __restrict__ keys, int* __restrict__ vals,
+                                int* __restrict__ hist, cudasw_result* __restrict__ res) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    int64_t q = seq_off[p + 1] - seq_off[p];
+    int64_t w = ref_off[p + 1] - ref_off[p];
+    cudasw_result r;
+    r.score = 0; r.ref_begin = -1; r.ref_end = -1; r.read_begin = 0; r.read_end = 0;
+    r.cigar_off = 0; r.cigar_len = 0; r.status = CUDASW_OK;
+    int v;
+    if (q <= 0 || w <= 0) { r.status = CUDASW_EINVAL; v = vt.n; }
+    else if (q > max_rows || w > max_cols) { r.status = CUDASW_ETOOLARGE; v = vt.n; }
+    else v = variant_of(vt, (int)q);
+    res[p] = r;
+    uint32_t wq = (uint32_t)(w >> 4);
+    if (wq > 0xFFFFFu) wq = 0xFFFFFu;
+    keys[p] = ((uint32_t)v << 20) | wq;
+    vals[p] = p;
+    atomicAdd(&hist[v], 1);
+}
+
+// keys for the reverse pass (needs the forward result): rows = read_end+1, columns walked ~ rows
+__global__ void rev_keys_kernel(int n, const int4* __restrict__ fwd,
+                                const cudasw_result* __restrict__ res, VariantTable vt,
+                                uint32_t* __restrict__ keys, int* __restrict__ vals,
+                                int* __restrict__ hist) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    int4 f = fwd[p];
+    int v;
+    uint32_t k2 = 0;
+    if (res[p].status != CUDASW_OK || f.x <= 0) v = vt.n;  // nothing to walk back
+    else {
+        v = variant_of(vt, f.z + 1);
+        k2 = (uint32_t)min(f.y + 1, f.z + 1 + 64) >> 4;
+        if (k2 > 0xFFFFFu) k2 = 0xFFFFFu;
+    }
+    keys[p] = ((uint32_t)v << 20) | k2;
+    vals[p] = p;
+    atomicAdd(&hist[v], 1);
+}
+
+// ------------------------------------------------------------------------------------------
+// The score pass (forward: phase 1 of ssw_align; REV: phase 2, the reverse pass with early stop).
+//
+// Recurrences, in biased form v' = v + B with B = gap_open so that every
+// stored half-word is >= 0 and `H - gap_open` is a plain 32-bit subtract:
+//     H = max(0, Hdiag + s, E, F);  E' = max(E - ge, H - go);  F' = max(F - ge, H - go)
+// Per packed cell pair: LOP3 (selector), PRMT (score), VIMNMX3, VIADDMNMX, IADD, 2x VIADDMNMX,
+// + 1/2 VIMNMX3 for the column maximum.
+//
+// Wavefront: virtual lane v = 2*lig + half owns rows [v*R, (v+1)*R) and is at column t - v at
+// step t. The low half hands its bottom row to the high half in-thread; the high half hands it
+// to the next lane's low half by one shuffle per value.
+//
+// Tie-breaks (ssw.c:283-306 per SURVEY.md): result = first column that strictly raises the running
+// maximum, then the smallest row holding it. Each virtual lane keeps (best, col, row) with strict
+// improvement; the group reduces with the key (score, -col, -row).
+// ------------------------------------------------------------------------------------------
+template <int G, int R, bool REV>
+__global__ void __launch_bounds__(128)
+sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4* __restrict__ fwd,
+                int4* __restrict__ out, ScoreConst sc) {
+    constexpr int GPB = 128 / G;
+    const int lig = threadIdx.x % G;
+    const int gidx = blockIdx.x * GPB + threadIdx.x / G;
+    const bool active = gidx < njobs;
+
+    int q = 0, w = 0, target = -1, pair = -1;
+    const uint8_t* qptr = io.enc_seq;
+    const uint8_t* rptr = io.enc_ref;
+    if (active) {
+        pair = order[gidx];
+        int64_t qo = io.seq_off[pair], ro = io.ref_off[pair];
+        if (REV) {
+            int4 f = fwd[pair];
+            target = f.x;
+            w = f.y + 1;
+            q = f.z + 1;
+            qptr += qo + f.z;
+            rptr += ro + f.y;
+        } else {
+            q = (int)(io.seq_off[pair + 1] - qo);
+            w = (int)(io.ref_off[pair + 1] - ro);
+            qptr += qo;
+            rptr += ro;
+        }
+    }
+    constexpr int STEP = REV ? -1 : 1;
+
+    // query rows -> PRMT selector halves (low byte: low virtual lane, high byte: high one)
+    uint32_t Q[R];
+    {
+        const int r0 = (2 * lig) * R;
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            int a = r0 + k, b = r0 + R + k;
+            uint32_t qa = a < q ? (uint32_t)qptr[(int64_t)a * STEP] : kQueryPad;
+            uint32_t qb = b < q ? (uint32_t)qptr[(int64_t)b * STEP] : kQueryPad;
+            Q[k] = qa | (qb << 8);
+        }
+    }
+    uint32_t H[R], E[R];
+#pragma unroll
+    for (int k = 0; k < R; k++) { H[k] = sc.BB; E[k] = 0u; }
+
+    uint32_t best = sc.BB;
+    int col_lo = -1, col_hi = -1, row_lo = 0, row_hi = 0;
+    uint32_t Hout = sc.BB, Fout = 0u, Hdiag_top = sc.BB;
+    uint32_t Rsel = kWindowPad | (kWindowPad << 8);
+
+    int t_end = active ? w + 2 * G - 1 : 0;
+    int t_end_warp = __reduce_max_sync(0xffffffffu, t_end);
+
+    // prefetch the window byte of step 0
+    int c = -2 * lig;  // column of the low virtual lane at step t
+    uint32_t rb_next = ((unsigned)c < (unsigned)w) ? (uint32_t)rptr[(int64_t)c * STEP] : kWindowPad;
+
+    for (int t = 0; t < t_end_warp; ++t, ++c) {
+        // ---- inputs from the virtual lane above
+        uint32_t rH = __shfl_up_sync(0xffffffffu, Hout, 1, G);
+        uint32_t rF = __shfl_up_sync(0xffffffffu, Fout, 1, G);
+        if (lig == 0) { rH = sc.BB; rF = 0u; }  // row -1 of the matrix: H = 0, F = -inf
+        const uint32_t Hin = prmt(rH, Hout, 0x5432u);  // lo <- upper lane's hi half, hi <- own lo half
+        uint32_t F = prmt(rF, Fout, 0x5432u);
+
+        // ---- window bytes: lo half column c, hi half column c-1
+        const uint32_t rb = rb_next;
+        {
+            int cn = c + 1;
+            rb_next = kWindowPad;
+            if ((unsigned)cn < (unsigned)w) rb_next = (uint32_t)rptr[(int64_t)cn * STEP];
+        }
+        Rsel = prmt(Rsel, rb, 0x3204u);  // byte1 <- old byte0, byte0 <- new
+
+        uint32_t diag = Hdiag_top;
+        Hdiag_top = Hin;
+        uint32_t cm = sc.BB;
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const uint32_t s = prmt(sc.poolA, sc.poolB, Q[k] ^ Rsel);
+            const uint32_t m = __vimax3_s16x2(E[k], F, sc.BB);
+            const uint32_t h = __viaddmax_s16x2(diag, s, m);
+            diag = H[k];
+            H[k] = h;
+            const uint32_t hg = h - sc.GO2;
+            E[k] = __viaddmax_s16x2(E[k], sc.NGE2, hg);
+            F = __viaddmax_s16x2(F, sc.NGE2, hg);
+            if (k & 1) cm = __vimax3_s16x2(cm, H[k - 1], h);
+        }
+        if (R & 1) cm = __vmaxs2(cm, H[R - 1]);
+        Hout = H[R - 1];
+        Fout = F;
+
+        // ---- running best with strict improvement
+        // (not __vibmax_s16x2: its header asm lets the output alias input `a`, which turns both
+        //  predicates into constants when best is updated in place)
+        const uint32_t nb = __vmaxs2(best, cm);
+        if (nb != best) {
+            const uint32_t changed = nb ^ best;
+            if (changed & 0xFFFFu) {
+                col_lo = c;
+                const uint32_t v = nb & 0xFFFFu;
+#pragma unroll
+                for (int k = R - 1; k >= 0; k--)
+                    if ((H[k] & 0xFFFFu) == v) row_lo = k;
+            }
+            if (changed >> 16) {
+                col_hi = c - 1;
+                const uint32_t v = nb >> 16;
+#pragma unroll
+                for (int k = R - 1; k >= 0; k--)
+                    if ((H[k] >> 16) == v) row_hi = k;
+            }
+        }
+        best = nb;
+
+        if (REV) {
+            // early stop (ssw.c:296): once a lane holds `target`, later lanes may still find it in an
+            // earlier column, so run on until the last virtual lane has passed this column.
+            if ((t & 3) == 3) {
+                const int tg = target + sc.B;
+                bool found = ((int)(best & 0xFFFFu) == tg) || ((int)(best >> 16) == tg);
+                if (found) t_end = min(t_end, t + 2 * G + 1);
+                // all lanes of a group must agree on t_end
+#pragma unroll
+                for (int o = G / 2; o > 0; o >>= 1)
+                    t_end = min(t_end, __shfl_xor_sync(0xffffffffu, t_end, o));
+                t_end_warp = __reduce_max_sync(0xffffffffu, t_end);
+            }
+        }
+    }
+
+    // ---- group reduction: max score, then min column, then min row
+    const int rbase = (2 * lig) * R;
+    unsigned long long klo = ((unsigned long long)(best & 0xFFFFu) << 40) |
+                             ((unsigned long long)(0xFFFFFFu - (uint32_t)(col_lo + 1)) << 16) |
+                             (unsigned long long)(0xFFFFu - (uint32_t)(rbase + row_lo));
+    unsigned long long khi = ((unsigned long long)(best >> 16) << 40) |
+                             ((unsigned long long)(0xFFFFFFu - (uint32_t)(col_hi + 1)) << 16) |
+                             (unsigned long long)(0xFFFFu - (uint32_t)(rbase + R + row_hi));
+    unsigned long long key = klo > khi ? klo : khi;
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+        unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+        key = other > key ? other : key;
+    }
+    if (active && lig == 0) {
+        int score = (int)(key >> 40) - sc.B;
+        int col = (int)(0xFFFFFFu - (uint32_t)((key >> 16) & 0xFFFFFFu)) - 1;
+        int row = (int)(0xFFFFu - (uint32_t)(key & 0xFFFFu));
+        out[pair] = make_int4(score, col, row, 0);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Phase 3: banded traceback (banded_sw, ssw.c:557-734). One thread per pair.
+// The band rule, the zero borders (including the `edge` quirk, ssw.c:596), every tie-break and the
+// `while (i > 0)` walk are reproduced; state is laid out differently: one in-place rolling row of
+// (H, E) pairs and ONE direction byte per cell (bits 0-2: H source 1..5, bit 3: E opened,
+// bit 4: F opened) addressed with the reference's flat cell index, so even an out-of-band step of
+// the walk lands on the same neighbouring cell. Only the last band iteration's directions exist
+// here; a walk that leaves the cells written by it is reported as CUDASW_EUNDEF.
+// ------------------------------------------------------------------------------------------
+struct TbConst {
+    int32_t match, mismatch, ambiguous, go, ge;
+};
+
+struct TbPool {
+    uint8_t* base;
+    unsigned long long cap;
+    unsigned long long* used;
+};
+
+__device__ __forceinline__ int tb_sub(const TbConst& tc, uint32_t qb, uint32_t rb) {
+    uint32_t x = (qb ^ rb) & 7u;
+    return x == 0 ? tc.match : (x < 4 ? tc.mismatch : tc.ambiguous);
+}
+
+// Walks the direction matrix. When `outp` != nullptr writes ops (reversed order resolved by index).
+// Returns number of M/I/D ops, or a negative status.
+__device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, int readLen,
+                       int refLen, uint32_t* outp, int total_ops) {
+    int i = readLen - 1, j = refLen - 1;
+    int e = 0, l = 0, state = 2;
+    int op = 0, prev_op = 0;  // 0 = M, 1 = I, 2 = D
+    while (i > 0) {
+        const int xi = max(i - band, 0);
+        const int jj = j - xi;
+        const int lo = max(i - band, 0) - xi, hi = min(i + band, refLen - 1) - xi;
+        if (jj < lo || jj > hi) return CUDASW_EUNDEF;
+        const uint32_t b = dir[(int64_t)width_d * i + jj];
+        int dv = state == 2 ? (int)(b & 7u) : state == 0 ? (2 + (int)((b >> 3) & 1u)) : (4 + (int)((b >> 4) & 1u));
+        switch (dv) {
+            case 1: --i; --j; state = 2; op = 0; break;
+            case 2: --i; state = 0; op = 1; break;
+            case 3: --i; state = 2; op = 1; break;
+            case 4: --j; state = 1; op = 2; break;
+            case 5: --j; state = 2; op = 2; break;
+            default: return CUDASW_EUNDEF;
+        }
+        if (op == prev_op) ++e;
+        else {
+            ++l;
+            if (outp) outp[total_ops - l] = ((uint32_t)e << 4) | (uint32_t)prev_op;
+            prev_op = op;
+            e = 1;
+        }
+    }
+    if (op == 0) {
+        ++l;
+        if (outp) outp[total_ops - l] = ((uint32_t)(e + 1) << 4) | 0u;
+    } else {
+        l += 2;
+        if (outp) {
+            outp[total_ops - (l - 1)] = ((uint32_t)e << 4) | (uint32_t)op;
+            outp[total_ops - l] = (1u << 4) | 0u;
+        }
+    }
+    return l;
+}
+
+__global__ void __launch_bounds__(128)
+sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* __restrict__ fwd,
+                    const int4* __restrict__ rev, TbConst tc, TbPool pool,
+                    cudasw_result* __restrict__ res, uint32_t* __restrict__ cig,
+                    unsigned long long cig_cap, unsigned long long* __restrict__ cig_used,
+                    int* __restrict__ retry_list, int* __restrict__ retry_count) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= n) return;
+    const int pair = list ? list[tid] : tid;
+    cudasw_result r = res[pair];
+    if (r.status != CUDASW_OK) return;
+    const int q = (int)(io.seq_off[pair + 1] - io.seq_off[pair]);
+    const int4 f = fwd[pair];
+    const int score = f.x;
+
+    int nbody = 0, lead = 0, tail = 0;
+    int ref_begin = -1, read_begin = 0, ref_end = f.y, read_end = f.z;
+    const uint8_t* dirp = nullptr;
+    int width_d = 0, band = 0, readLen = 0, refLen = 0;
+
+    if (score <= 0) {
+        // no positive cell -> start -1, "1M" + (q-1)S
+        ref_end = -1; read_end = 0;
+        nbody = 1;
+    } else {
+        const int4 rv = rev[pair];
+        if (rv.x != score) { res[pair].status = CUDASW_ECUDA; return; }  // internal inconsistency
+        ref_begin = ref_end - rv.y;
+        read_begin = read_end - rv.z;
+        refLen = ref_end - ref_begin + 1;
+        readLen = read_end - read_begin + 1;
+        const uint8_t* ref = io.enc_ref + io.ref_off[pair] + ref_begin;
+        const uint8_t* read = io.enc_seq + io.seq_off[pair] + read_begin;
+        band = abs(refLen - readLen) + 1;
+        int mx = 0;
+        for (;;) {
+            width_d = 2 * band + 1;
+            const int width = 2 * band + 3;
+            const long long ndir = (long long)width_d * readLen;
+            if (ndir * 3 >= (1ll << 31)) { res[pair].status = CUDASW_ETOOLARGE; return; }
+            const unsigned long long need = (((unsigned long long)width * 8ull + 15ull) & ~15ull) +
+                                            (((unsigned long long)ndir + 15ull) & ~15ull);
+            if (need > pool.cap) { res[pair].status = CUDASW_ETOOLARGE; return; }
+            const unsigned long long off = atomicAdd(pool.used, need);
+            if (off + need > pool.cap) {
+                retry_list[atomicAdd(retry_count, 1)] = pair;
+                return;
+            }
+            int2* he = reinterpret_cast<int2*>(pool.base + off);
+            uint8_t* dir = pool.base + off + (((unsigned long long)width * 8ull + 15ull) & ~15ull);
+            dirp = dir;
+            for (int k = 0; k < width; k++) he[k] = make_int2(0, 0);
+            for (int i = 0; i < readLen; i++) {
+                const int beg = max(i - band, 0);
+                const int end = min(i + band, refLen - 1);
+                const int edge = min(end + 1, width - 1);
+                const int xi = beg;
+                const int xp = max(i - 1 - band, 0);
+                he[0] = make_int2(0, 0);
+                he[edge] = make_int2(0, 0);
+                int fgap = 0, hleft = 0;
+                int hdiag = he[beg - xp].x;
+                const uint32_t qb = read[i];
+                uint8_t* drow = dir + (long long)width_d * i - xi;
+                for (int j = beg; j <= end; j++) {
+                    const int2 up = he[j - xp + 1];
+                    int t1 = i == 0 ? -tc.go : up.x - tc.go;
+                    int t2 = i == 0 ? -tc.ge : up.y - tc.ge;
+                    const int E = max(t1, t2);
+                    const uint32_t dE = t1 > t2 ? 1u : 0u;
+                    t1 = hleft - tc.go;
+                    t2 = fgap - tc.ge;
+                    fgap = max(t1, t2);
+                    const uint32_t dF = t1 > t2 ? 1u : 0u;
+                    const int e1 = max(E, 0), f1 = max(fgap, 0);
+                    const int g = max(e1, f1);
+                    const int d = hdiag + tb_sub(tc, qb, ref[j]);
+                    const int h = max(g, d);
+                    mx = max(mx, h);
+                    const uint32_t dH = (g <= d) ? 1u : (e1 > f1 ? 2u + dE : 4u + dF);
+                    drow[j] = (uint8_t)(dH | (dE << 3) | (dF << 4));
+                    hdiag = up.x;
+                    he[j - xi + 1] = make_int2(h, E);
+                    hleft = h;
+                }
+            }
+            if (mx >= score) break;
+            band *= 2;
+        }
+        nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0);
+        if (nbody < 0) { res[pair].status = nbody; return; }
+    }
+    lead = read_begin != 0;
+    tail = (q - read_end - 1) != 0;
+    const int nops = nbody + lead + tail;
+    const unsigned long long coff = atomicAdd(cig_used, (unsigned long long)nops);
+    r.score = score;
+    r.ref_begin = ref_begin;
+    r.ref_end = ref_end;
+    r.read_begin = read_begin;
+    r.read_end = read_end;
+    r.cigar_len = nops;
+    r.cigar_off = (int32_t)coff;
+    if (coff + (unsigned long long)nops <= cig_cap && coff < 0x7fffffffull) {
+        uint32_t* o = cig + coff;
+        if (lead) *o++ = ((uint32_t)read_begin << 4) | CUDASW_CIGAR_S;
+        if (score <= 0) *o = (1u << 4) | CUDASW_CIGAR_M;
+        else tb_walk(dirp, width_d, band, readLen, refLen, o, nbody);
+        if (tail) o[nbody] = ((uint32_t)(q - read_end - 1) << 4) | CUDASW_CIGAR_S;
+    } else {
+        r.status = CUDASW_ENOMEM;
+    }
+    res[pair] = r;
+}
+
+}  // namespace cusw

@@ -1,0 +1,82 @@
+"""CPU: the C-ABI library loads, exports every symbol include/cudasw.h declares, and refuses to run
+without a GPU (no CPU fallback). No compute calls here."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "cudasw.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(cudasw_[a-z_]+)\s*\(", src)))
+
+
+def test_header_declares_expected_entry_points():
+    names = _declared()
+    for must in ("cudasw_create", "cudasw_destroy", "cudasw_align_batch", "cudasw_align_batch_device",
+                 "cudasw_submit", "cudasw_flush", "cudasw_poll", "cudasw_last_error"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    import gridss_b200 as g
+    from gridss_b200 import aligner
+
+    lib = g.load_library()
+    names = _declared()
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/cudasw.h but not exported"
+    assert sorted(n for n, _, _ in aligner.ABI) == names
+
+
+def test_result_struct_layout_matches_header():
+    import gridss_b200 as g
+
+    assert g.RESULT_DTYPE.itemsize == 32
+    assert g.RESULT_DTYPE.names == ("score", "ref_begin", "ref_end", "read_begin", "read_end", "cigar_off", "cigar_len", "status")
+
+
+def test_cigar_string_host_helper():
+    import numpy as np
+
+    import gridss_b200 as g
+
+    lib = g.load_library()
+    ops = np.array([(4 << 4) | 4, (78 << 4) | 0, (1 << 4) | 2, (3 << 4) | 1, (45 << 4) | 4], dtype=np.uint32)
+    buf = ctypes.create_string_buffer(64)
+    n = lib.cudasw_cigar_string(ops.ctypes.data, len(ops), buf, 64)
+    assert buf.value[:n] == b"4S78M1D3I45S"
+    assert g.cigar_string(ops) == "4S78M1D3I45S"
+    assert lib.cudasw_cigar_string(ops.ctypes.data, len(ops), buf, 4) < 0
+
+
+def test_no_cpu_fallback_without_gpu():
+    import gridss_b200 as g
+
+    lib = g.load_library()
+    if lib.cudasw_device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(g.CudaSwError):
+        g.CudaAligner()
+
+
+def test_scoring_validation_mirrors_reference():
+    import gridss_b200 as g
+
+    # ssw.Aligner.align: "Gap open and extension penalties must ..." / "Scoring matrix values must fit into signed 8-bit"
+    for bad in ((1, -4, -4, 256, 1), (1, -4, -4, 6, -1), (200, -4, -4, 6, 1)):
+        with pytest.raises(ValueError):
+            g.CudaAligner(*bad)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "gridss_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                txt = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "oracle" not in txt.replace("SURVEY", ""), f"{f} mentions the oracle"

@@ -1,0 +1,177 @@
+"""GPU: the CUDA path (through the C ABI) against the oracle restatement, bit-exact
+(score, start, end, read begin/end, CIGAR). The oracle itself is pinned in test_oracle.py."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+FIELDS = ["score", "ref_begin", "ref_end", "read_begin", "read_end", "cigar_len", "status"]
+
+
+def _cig(res, cig, i):
+    r = res[i]
+    return tuple(int(x) for x in cig[r["cigar_off"]: r["cigar_off"] + r["cigar_len"]])
+
+
+def _compare_blobs(aligner_obj, oracle, sb, so, rb, ro, scoring=(1, -4, -4, 6, 1), threads=16):
+    m = oracle.model_align_blobs(sb, so, rb, ro, scoring, threads=threads)
+    res, cig = aligner_obj.align_blobs(sb, so, rb, ro)
+    bad = []
+    undef = 0
+    for i in range(len(res)):
+        if m.res[i]["status"] == -5 or res[i]["status"] == -5:
+            undef += 1
+            continue
+        a = tuple(int(res[i][f]) for f in FIELDS)
+        b = tuple(int(m.res[i][f]) for f in FIELDS)
+        ca = _cig(res, cig, i)
+        cb = tuple(int(x) for x in m.cig[m.res[i]["cigar_off"]: m.res[i]["cigar_off"] + m.res[i]["cigar_len"]])
+        if a != b or ca != cb:
+            bad.append((i, a, b, ca[:6], cb[:6]))
+    return bad, undef
+
+
+def _compare(aligner_obj, oracle, seqs, refs, scoring=(1, -4, -4, 6, 1)):
+    from gridss_b200.aligner import pack
+
+    sb, so = pack(seqs)
+    rb, ro = pack(refs)
+    return _compare_blobs(aligner_obj, oracle, sb, so, rb, ro, scoring)
+
+
+def test_reference_golden_vectors(aligner):
+    g = json.load(open(os.path.join(HERE, "golden", "golden_reference_tests.json")))
+    for x in g:
+        a = aligner.align_smith_waterman(x["seq"].encode("latin1"), x["ref"].encode("latin1"))
+        assert (a.score, a.getStartPosition(), a.getCigar()) == (x["score"], x["start"], x["cigar"]), x["cite"]
+
+
+def test_sswjni_golden_fuzz(aligner):
+    import gridss_b200 as gb
+
+    g = json.load(open(os.path.join(HERE, "golden", "golden_sswjni_fuzz.json")))
+    by_sc = {}
+    for x in g:
+        by_sc.setdefault(tuple(x["scoring"]), []).append(x)
+    for sc, xs in by_sc.items():
+        al = aligner if sc == (1, -4, -4, 6, 1) else gb.AlignerFactory.create(*sc)
+        out = al.align_batch([x["seq"].encode("latin1") for x in xs], [x["ref"].encode("latin1") for x in xs])
+        for a, x in zip(out, xs):
+            assert (a.score, a.getStartPosition(), a.getCigar()) == (x["score"], x["start"], x["cigar"]), (x["kind"], sc)
+
+
+@pytest.mark.parametrize("kind", ["random", "mutated", "two_letter", "homopolymer", "dinuc", "tandem", "subst_block",
+                                  "with_n", "zero", "tiny", "q_gt_w", "indel_heavy"])
+def test_adversarial_vs_oracle(aligner, oracle, synth, kind):
+    for seed, qmax, wmax in ((1, 200, 400), (2, 700, 1500)):
+        seqs, refs = synth.adversarial(kind, 1500, seed=seed, qmax=qmax, wmax=wmax)
+        bad, undef = _compare(aligner, oracle, seqs, refs)
+        assert bad == [], bad[:5]
+        assert undef == 0
+
+
+@pytest.mark.parametrize("cfg,n", [(1, 10000), (2, 4000), (3, 1500), (4, 4000)])
+def test_synthetic_configs_vs_oracle(aligner, oracle, synth, cfg, n):
+    sb, so, rb, ro = synth.generate(cfg, n)
+    bad, undef = _compare_blobs(aligner, oracle, sb, so, rb, ro)
+    assert bad == [], bad[:5]
+    assert undef == 0
+
+
+@pytest.mark.parametrize("sc", [(2, -6, -1, 5, 3), (1, -1, -1, 2, 1), (3, -2, -5, 4, 0), (5, -4, -2, 10, 1)])
+def test_other_scoring_vs_oracle(oracle, synth, sc):
+    import gridss_b200 as gb
+
+    al = gb.AlignerFactory.create(*sc)
+    for kind in ("mutated", "with_n", "indel_heavy", "subst_block"):
+        seqs, refs = synth.adversarial(kind, 800, seed=9)
+        bad, undef = _compare(al, oracle, seqs, refs, sc)
+        assert bad == [], (kind, bad[:5])
+    al.close()
+
+
+def test_every_variant_boundary(aligner, oracle):
+    """query lengths straddling every (G, R) variant's row capacity"""
+    rng = np.random.default_rng(3)
+    seqs, refs = [], []
+    for rows in (16, 24, 32, 40, 48, 64, 80, 96, 128, 160, 192, 256, 320, 384, 512, 640, 768, 1024, 1280, 1536, 2048):
+        for q in (rows - 1, rows, rows + 1):
+            if q > 2048:
+                continue
+            w = int(rng.integers(q, 3 * q + 50))
+            r = bytes(rng.choice(list(b"ACGT"), size=w).tolist())
+            st = int(rng.integers(0, w - q + 1))
+            s = bytearray(r[st:st + q])
+            for k in range(max(1, q // 30)):
+                s[int(rng.integers(0, q))] = int(rng.choice(list(b"ACGT")))
+            seqs.append(bytes(s))
+            refs.append(r)
+    bad, undef = _compare(aligner, oracle, seqs, refs)
+    assert bad == [] and undef == 0, bad[:5]
+
+
+def test_empty_and_oversize_inputs(aligner):
+    import gridss_b200 as gb
+    from gridss_b200.aligner import pack
+
+    with pytest.raises(ValueError):
+        aligner.align_smith_waterman(b"", b"ACGT")  # SswJniAligner.java:45-47
+    with pytest.raises(ValueError):
+        aligner.align_smith_waterman(b"ACGT", b"")  # SswJniAligner.java:48-50
+    # per-pair status: one bad pair does not fail the batch
+    sb, so = pack([b"ACGT", b"", b"A" * 40000, b"GGGG"])
+    rb, ro = pack([b"ACGT", b"ACGT", b"A" * 50, b"CCGGGGCC"])
+    res, cig = aligner.align_blobs(sb, so, rb, ro)
+    assert [int(x) for x in res["status"]] == [0, gb.aligner.CUDASW_EINVAL, gb.aligner.CUDASW_ETOOLARGE, 0]
+    assert int(res[3]["ref_begin"]) == 2
+    # empty batch
+    res, cig = aligner.align_blobs(np.zeros(1, np.uint8), np.zeros(1, np.int64), np.zeros(1, np.uint8), np.zeros(1, np.int64))
+    assert len(res) == 0
+
+
+def test_async_trio_matches_sync(aligner, synth):
+    import gridss_b200 as gb
+
+    seqs, refs = synth.adversarial("mutated", 300, seed=77)
+    sync = aligner.align_batch(seqs, refs)
+    b = gb.BatchingAligner(aligner, batch_size=128)
+    for s, r in zip(seqs, refs):
+        b.asyncAlign(s, r)
+    b.flush()
+    assert b.outstandingAlignmentRecord() == 0
+    got = [b.getAlignment() for _ in seqs]
+    assert got == sync
+    with pytest.raises(RuntimeError):
+        b.getAlignment()
+
+
+def test_device_resident_entry_point(aligner, oracle, synth):
+    torch = pytest.importorskip("torch")
+    sb, so, rb, ro = synth.generate(2, 2000)
+    d = [torch.from_numpy(x).cuda() for x in (sb, so, rb, ro)]
+    torch.cuda.synchronize()
+    res, cig = aligner.align_blobs_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), d[3].data_ptr(), so, ro)
+    res2, cig2 = aligner.align_blobs(sb, so, rb, ro)
+    for f in FIELDS:
+        assert np.array_equal(res[f], res2[f])
+    assert all(_cig(res, cig, i) == _cig(res2, cig2, i) for i in range(len(res)))
+
+
+def test_order_invariance_and_idempotence(aligner, synth):
+    """size-independent properties: results do not depend on batch composition or order"""
+    sb, so, rb, ro = synth.generate(4, 20000)
+    res, cig = aligner.align_blobs(sb, so, rb, ro)
+    res2, cig2 = aligner.align_blobs(sb, so, rb, ro)
+    assert np.array_equal(res[FIELDS], res2[FIELDS])
+    idx = np.random.default_rng(0).permutation(20000)[:3000]
+    seqs = [bytes(sb[so[i]:so[i + 1]]) for i in idx]
+    refs = [bytes(rb[ro[i]:ro[i + 1]]) for i in idx]
+    out = aligner.align_batch(seqs, refs)
+    for a, i in zip(out, idx):
+        assert a.getStartPosition() == int(res[i]["ref_begin"])
+        assert a.score == int(res[i]["score"])
+        from gridss_b200 import cigar_string
+        assert a.getCigar() == cigar_string(_cig(res, cig, i))
