@@ -1,0 +1,58 @@
+/* JNI glue: libcudaswjni.so = this file + -lcudasw. Replaces Java_ssw_Aligner_align (libsswjni.so 0xcac).
+ * gcc -shared -fPIC -I$JAVA_HOME/include -I$JAVA_HOME/include/linux -I../../include cudaswjni.c -L../../gridss_b200 -lcudasw -o libcudaswjni.so */
+#include <jni.h>
+#include <stdlib.h>
+#include "cudasw.h"
+
+JNIEXPORT jlong JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_create(JNIEnv* env, jclass c, jint match, jint mismatch,
+        jint ambiguous, jint gapOpen, jint gapExtend, jint device) {
+    cudasw_scoring sc = {match, mismatch, ambiguous, gapOpen, gapExtend};
+    cudasw_t* h = NULL;
+    int rc = cudasw_create(&sc, device, &h);
+    if (rc == CUDASW_EINVAL) {
+        (*env)->ThrowNew(env, (*env)->FindClass(env, "java/lang/IllegalArgumentException"), cudasw_last_error(NULL));
+        return 0;
+    }
+    return rc == CUDASW_OK ? (jlong)(intptr_t)h : 0;
+}
+JNIEXPORT void JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_destroy(JNIEnv* env, jclass c, jlong h) {
+    cudasw_destroy((cudasw_t*)(intptr_t)h);
+}
+JNIEXPORT jstring JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_lastError(JNIEnv* env, jclass c, jlong h) {
+    return (*env)->NewStringUTF(env, cudasw_last_error((cudasw_t*)(intptr_t)h));
+}
+JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_alignBatch(JNIEnv* env, jclass c, jlong h, jint n,
+        jbyteArray seqBlob, jlongArray seqOff, jbyteArray refBlob, jlongArray refOff, jintArray startOut,
+        jobjectArray cigarOut, jintArray statusOut) {
+    cudasw_result* res = (cudasw_result*)malloc(sizeof(cudasw_result) * (size_t)(n > 0 ? n : 1));
+    jsize qbytes = (*env)->GetArrayLength(env, seqBlob);
+    int64_t cap = (int64_t)qbytes + 4 * (int64_t)n + 16, used = 0;
+    uint32_t* cig = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)cap);
+    /* critical sections: no copies of the blobs (the reference's GetByteArrayElements copies, .so 0xcde-0xe94) */
+    jbyte* s = (*env)->GetPrimitiveArrayCritical(env, seqBlob, NULL);
+    jbyte* r = (*env)->GetPrimitiveArrayCritical(env, refBlob, NULL);
+    jlong* so = (*env)->GetPrimitiveArrayCritical(env, seqOff, NULL);
+    jlong* ro = (*env)->GetPrimitiveArrayCritical(env, refOff, NULL);
+    int rc = cudasw_align_batch((cudasw_t*)(intptr_t)h, n, (const uint8_t*)s, (const int64_t*)so, (const uint8_t*)r,
+                                (const int64_t*)ro, res, cig, cap, &used);
+    (*env)->ReleasePrimitiveArrayCritical(env, refOff, ro, JNI_ABORT);
+    (*env)->ReleasePrimitiveArrayCritical(env, seqOff, so, JNI_ABORT);
+    (*env)->ReleasePrimitiveArrayCritical(env, refBlob, r, JNI_ABORT);
+    (*env)->ReleasePrimitiveArrayCritical(env, seqBlob, s, JNI_ABORT);
+    if (rc == CUDASW_OK) {
+        jint* st = (*env)->GetIntArrayElements(env, startOut, NULL);
+        jint* status = (*env)->GetIntArrayElements(env, statusOut, NULL);
+        char buf[1 << 16];
+        for (jint i = 0; i < n; i++) {
+            st[i] = res[i].ref_begin;
+            status[i] = res[i].status;
+            if (res[i].status == 0 && cudasw_cigar_string(cig + res[i].cigar_off, res[i].cigar_len, buf, sizeof buf) >= 0)
+                (*env)->SetObjectArrayElement(env, cigarOut, i, (*env)->NewStringUTF(env, buf));
+        }
+        (*env)->ReleaseIntArrayElements(env, startOut, st, 0);
+        (*env)->ReleaseIntArrayElements(env, statusOut, status, 0);
+    }
+    free(cig);
+    free(res);
+    return rc;
+}
