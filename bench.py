@@ -266,7 +266,7 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {
-                "bound": "int32_alu", "kernel": "sw_score_kernel<8,20,false> (forward score pass)",
+                "bound": "int32_alu", "kernel": "sw_score_kernel<G=%d,R=%d,REV=false> (forward score pass)" % al.variant_for(Q_LEN)[:2],
                 "achieved": achieved_laneops / 1e12, "peak": peak_laneops / 1e12, "unit": "T lane-op/s",
                 "frac": achieved_laneops / peak_laneops, "traffic": None,
                 "gcups_kernel": fwd_cups / 1e9, "int_ops_per_cell": INT_OPS_PER_CELL, "packing": 2,

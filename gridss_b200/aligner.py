@@ -93,6 +93,7 @@ ABI = [
     ("cudasw_processed", _i64, [_vp]),
     ("cudasw_poll", ctypes.c_int, [_vp, _i64, _vp, _vp, _i32, ctypes.POINTER(_i32)]),
     ("cudasw_get_stats", ctypes.c_int, [_vp, ctypes.POINTER(Stats)]),
+    ("cudasw_variant_for", ctypes.c_int, [_vp, _i32, ctypes.POINTER(_i32), ctypes.POINTER(_i32), ctypes.POINTER(_i32)]),
     ("cudasw_last_error", ctypes.c_char_p, [_vp]),
     ("cudasw_device_count", ctypes.c_int, []),
     ("cudasw_version", ctypes.c_char_p, []),
@@ -278,6 +279,12 @@ class CudaAligner(Aligner):
                 raise CudaSwError(f"pair failed with status {int(r['status'])}")
             out.append(Alignment(int(r["ref_begin"]), cigar_string(cig[r["cigar_off"] : r["cigar_off"] + r["cigar_len"]]), int(r["score"])))
         return out
+
+    def variant_for(self, query_len: int) -> tuple[int, int, int]:
+        """(lanes per pair, rows per virtual lane, strips) of the score kernel a query length maps to."""
+        g, r, s = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+        self._lib.cudasw_variant_for(self._h, query_len, ctypes.byref(g), ctypes.byref(r), ctypes.byref(s))
+        return g.value, r.value, s.value
 
     def stats(self) -> dict:
         st = Stats()

@@ -17,13 +17,18 @@
 #include <unordered_map>
 #include <vector>
 
+#define CUSW_MAIN_TU 1  // non-template kernels are emitted in this translation unit only
 #include "sw_kernels.cuh"
+#include "variants.h"
 
 using namespace cusw;
 
 namespace {
 
 thread_local std::string g_create_error;
+std::vector<cusw::Variant> g_var;
+int g_nvar = 0;
+std::once_flag g_var_once;
 
 #define CK(expr)                                                                              \
     do {                                                                                      \
@@ -33,30 +38,6 @@ thread_local std::string g_create_error;
             return CUDASW_ECUDA;                                                              \
         }                                                                                     \
     } while (0)
-
-typedef void (*score_launch_fn)(const int*, int, PairIO, const int4*, int4*, ScoreConst, cudaStream_t);
-
-template <int G, int R, bool REV>
-void launch_score(const int* order, int njobs, PairIO io, const int4* fwd, int4* out, ScoreConst sc,
-                  cudaStream_t st) {
-    constexpr int GPB = 128 / G;
-    int blocks = (njobs + GPB - 1) / GPB;
-    sw_score_kernel<G, R, REV><<<blocks, 128, 0, st>>>(order, njobs, io, fwd, out, sc);
-}
-
-struct Variant {
-    int G, R, rows;
-    score_launch_fn fwd, rev;
-};
-
-#define V(G, R) Variant{G, R, 2 * G * R, launch_score<G, R, false>, launch_score<G, R, true>}
-const Variant kVariants[] = {
-    V(1, 8),   V(1, 12),  V(1, 16),  V(1, 20),  V(1, 24),  V(2, 16),  V(2, 20),
-    V(2, 24),  V(4, 16),  V(4, 20),  V(4, 24),  V(8, 16),  V(8, 20),  V(8, 24),
-    V(16, 16), V(16, 20), V(16, 24), V(32, 16), V(32, 20), V(32, 24), V(32, 32),
-};
-#undef V
-constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
 template <typename T>
 struct DevBuf {
@@ -103,7 +84,7 @@ struct cudasw {
     DevBuf<uint32_t> cig;
     DevBuf<uint8_t> cub_tmp;
     DevBuf<uint8_t> tb_pool;
-    int* d_hist = nullptr;  // 64 ints
+    int* d_hist = nullptr;  // 128 ints
     unsigned long long* d_counters = nullptr;  // [0] pool used, [1] cigar used, [2] retry count(int)
     int* h_hist = nullptr;                     // pinned
     unsigned long long* h_counters = nullptr;  // pinned
@@ -171,6 +152,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
         g_create_error = "device index out of range";
         return CUDASW_EINVAL;
     }
+    std::call_once(g_var_once, [] { g_var = cusw::collect_variants(); g_nvar = (int)g_var.size(); });
     cudasw_t* h = new cudasw();
     h->device = device;
     h->scoring = sc;
@@ -184,10 +166,10 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
         return fail(cudaGetErrorString(e));
     for (auto& ev : h->ev)
         if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(cudaGetErrorString(e));
-    if ((e = cudaMalloc(&h->d_hist, 64 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_hist, 128 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
-    if ((e = cudaMallocHost(&h->h_hist, 64 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMallocHost(&h->h_hist, 128 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMallocHost(&h->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
 
@@ -199,9 +181,16 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     h->sc.BB = pack2(sc.gap_open);
     h->sc.GO2 = pack2(sc.gap_open);
     h->sc.NGE2 = pack2(-sc.gap_extend);
+    h->sc.ge = sc.gap_extend;
+    h->sc.match = sc.match;
     h->tc = TbConst{sc.match, sc.mismatch, sc.ambiguous, sc.gap_open, sc.gap_extend};
-    h->vt.n = kNumVariants;
-    for (int i = 0; i < kNumVariants; i++) h->vt.rows[i] = kVariants[i].rows;
+    if (g_nvar > 100) { cudasw_destroy(h); g_create_error = "too many variants"; return CUDASW_EINVAL; }
+    h->vt.n = g_nvar;
+    h->vt.n_single = 0;
+    for (int i = 0; i < g_nvar; i++) {
+        h->vt.rows[i] = g_var[i].rows;
+        if (!g_var[i].multi) h->vt.n_single = i + 1;
+    }
 
     // self-test, like AlignerFactory's "A" vs "A" probe (AlignerFactory.java:74-84)
     {
@@ -266,7 +255,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n));
     CK(cig.ensure((size_t)std::max<int64_t>(cigar_cap, 1)));
     size_t cub_bytes = 0;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 26, st));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
     CK(cub_tmp.ensure(cub_bytes + 16));
     if (!tb_pool.p) {
         size_t free_b = 0, total_b = 0;
@@ -309,26 +298,29 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         if (total_w > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref, enc_ref.p, total_w, 0x80u); launches++; }
     }
     PairIO io{enc_seq.p, enc_ref.p, d_so, d_ro};
-    const int max_rows = std::min(kVariants[kNumVariants - 1].rows,
+    const bool have_multi = g_var[g_nvar - 1].multi;
+    const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
                                   scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
     const int max_cols = (1 << 24) - 2;
-    CK(cudaMemsetAsync(d_hist, 0, 64 * sizeof(int), st));
+    CK(cudaMemsetAsync(d_hist, 0, 128 * sizeof(int), st));
     fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, d_so, d_ro, vt, max_rows, max_cols,
                                                            keys.p, vals.p, d_hist, res.p);
     launches++;
-    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 26, st));
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
     launches += 3;
-    CK(cudaMemcpyAsync(h_hist, d_hist, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(ev[2], st));
     CK(cudaStreamSynchronize(st));
 
-    // ---- forward score pass
+    // ---- forward score pass (strip-mined variants borrow the traceback pool for their boundary rows)
+    CK(cudaMemsetAsync(d_counters, 0, 8 * sizeof(unsigned long long), st));
+    StripPool spool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
     {
         int64_t start = 0;
-        for (int v = 0; v < kNumVariants; v++) {
+        for (int v = 0; v < g_nvar; v++) {
             int cnt = h_hist[v];
             if (cnt > 0) {
-                kVariants[v].fwd(vals_alt.p + start, cnt, io, nullptr, fwd.p, sc, st);
+                g_var[v].fwd(vals_alt.p + start, cnt, io, nullptr, fwd.p, sc, spool, st);
                 launches++;
                 stats.forward_cells_padded += 0;  // filled below from host offsets when available
             }
@@ -339,19 +331,20 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(cudaEventRecord(ev[3], st));
 
     // ---- reverse score pass
-    CK(cudaMemsetAsync(d_hist, 0, 64 * sizeof(int), st));
+    CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(d_hist, 0, 128 * sizeof(int), st));
     rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd.p, res.p, vt, keys.p, vals.p, d_hist);
     launches++;
-    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 26, st));
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
     launches += 3;
-    CK(cudaMemcpyAsync(h_hist, d_hist, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     {
         int64_t start = 0;
-        for (int v = 0; v < kNumVariants; v++) {
+        for (int v = 0; v < g_nvar; v++) {
             int cnt = h_hist[v];
             if (cnt > 0) {
-                kVariants[v].rev(vals_alt.p + start, cnt, io, fwd.p, rev.p, sc, st);
+                g_var[v].rev(vals_alt.p + start, cnt, io, fwd.p, rev.p, sc, spool, st);
                 launches++;
             }
             start += cnt;
@@ -417,9 +410,9 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
             if (q <= 0 || w <= 0) continue;
             cells += (uint64_t)q * (uint64_t)w;
             if (q <= max_rows) {
-                int v = 0;
-                while (v < kNumVariants - 1 && kVariants[v].rows < q) v++;
-                padded += (uint64_t)kVariants[v].rows * (uint64_t)(w + 2 * kVariants[v].G - 1);
+                int v = variant_of(vt, (int)q);
+                uint64_t strips = ((uint64_t)q + g_var[v].rows - 1) / g_var[v].rows;
+                padded += strips * (uint64_t)g_var[v].rows * (uint64_t)(w + 2 * g_var[v].G - 1);
             }
         }
         stats.cells = cells;
@@ -488,6 +481,15 @@ extern "C" int cudasw_host_free(void* hptr) { return cudaFreeHost(hptr) == cudaS
 extern "C" int cudasw_get_stats(cudasw_t* h, cudasw_stats* out) {
     if (!h || !out) return CUDASW_EINVAL;
     *out = h->stats;
+    return CUDASW_OK;
+}
+
+extern "C" int cudasw_variant_for(cudasw_t* h, int32_t q, int32_t* lanes, int32_t* rpl, int32_t* strips) {
+    if (!h || q <= 0) return CUDASW_EINVAL;
+    int v = variant_of(h->vt, q);
+    if (lanes) *lanes = g_var[v].G;
+    if (rpl) *rpl = g_var[v].R;
+    if (strips) *strips = (q + g_var[v].rows - 1) / g_var[v].rows;
     return CUDASW_OK;
 }
 

@@ -31,6 +31,7 @@ __device__ __forceinline__ uint32_t base_code(uint32_t c) {
     return c == 'A' ? 0u : c == 'C' ? 1u : c == 'G' ? 2u : c == 'T' ? 3u : 4u;
 }
 
+#ifdef CUSW_MAIN_TU
 // Elementwise encode of a whole blob (layout unchanged, so per-pair offsets still apply).
 // HBM-bound: 1 byte in, 1 byte out; 16-byte vector accesses.
 __global__ void __launch_bounds__(256) encode_kernel(const uint8_t* __restrict__ in,
@@ -58,6 +59,8 @@ __global__ void __launch_bounds__(256) encode_kernel(const uint8_t* __restrict__
     }
 }
 
+#endif  // CUSW_MAIN_TU
+
 // ------------------------------------------------------------------------------------------
 // Score-pass variants: a pair occupies a group of G lanes; each thread owns two virtual lanes of
 // R query rows each, so one group covers 2*G*R rows.
@@ -67,7 +70,8 @@ struct ScoreConst {
     uint32_t BB;            // bias B = gap_open in both halves (stored value = true value + B)
     uint32_t GO2;           // gap_open in both halves
     uint32_t NGE2;          // -gap_extend in both halves (two's complement per half)
-    int32_t B;
+    int32_t B;      // = gap_open
+    int32_t ge, match;
 };
 
 struct PairIO {
@@ -86,16 +90,25 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t s) {
 // Sort keys. Forward: (variant, window length); reverse: (variant, columns to walk).
 // variant_of() is shared with the host dispatch table (cudasw.cu).
 struct VariantTable {
-    int n;
-    int rows[48];  // rows covered by variant v (ascending)
+    int n;          // all variants
+    int n_single;   // the first n_single are single-strip, ascending by rows
+    int rows[100];  // rows covered by variant v (rows per strip for the strip-mined ones)
 };
 
-__device__ __forceinline__ int variant_of(const VariantTable& vt, int q) {
-    int v = 0;
-    while (v < vt.n - 1 && vt.rows[v] < q) v++;
-    return v;
+__host__ __device__ __forceinline__ int variant_of(const VariantTable& vt, int q) {
+    for (int v = 0; v < vt.n_single; v++)
+        if (vt.rows[v] >= q) return v;
+    // strip-mined: least padded rows, ties to the later (taller strips) variant
+    int bestv = vt.n - 1;
+    long long bestpad = -1;
+    for (int v = vt.n_single; v < vt.n; v++) {
+        long long padded = (long long)((q + vt.rows[v] - 1) / vt.rows[v]) * vt.rows[v];
+        if (bestpad < 0 || padded <= bestpad) { bestpad = padded; bestv = v; }
+    }
+    return bestv;
 }
 
+#ifdef CUSW_MAIN_TU
 // keys for the forward pass; hist[v] counts pairs per variant; slot vt.n counts invalid pairs
 __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
                                 const int64_t* __restrict__ ref_off, VariantTable vt, int max_rows,
@@ -114,7 +127,7 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
     else v = variant_of(vt, (int)q);
     res[p] = r;
     uint32_t wq = (uint32_t)(w >> 4);
-    if (wq > 0xFFFFFu) wq = 0xFFFFFu;
+    if (wq > 0xFFFFFu) wq = 0xFFFFFu;  // 2^24 columns max / 16
     keys[p] = ((uint32_t)v << 20) | wq;
     vals[p] = p;
     atomicAdd(&hist[v], 1);
@@ -122,7 +135,7 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
 
 // keys for the reverse pass (needs the forward result): rows = read_end+1, columns walked ~ rows
 __global__ void rev_keys_kernel(int n, const int4* __restrict__ fwd,
-                                const cudasw_result* __restrict__ res, VariantTable vt,
+                                cudasw_result* __restrict__ res, VariantTable vt,
                                 uint32_t* __restrict__ keys, int* __restrict__ vals,
                                 int* __restrict__ hist) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -130,6 +143,7 @@ __global__ void rev_keys_kernel(int n, const int4* __restrict__ fwd,
     int4 f = fwd[p];
     int v;
     uint32_t k2 = 0;
+    if (res[p].status == CUDASW_OK && f.w != 0) res[p].status = CUDASW_ENOMEM;  // strip buffers exhausted
     if (res[p].status != CUDASW_OK || f.x <= 0) v = vt.n;  // nothing to walk back
     else {
         v = variant_of(vt, f.z + 1);
@@ -140,6 +154,8 @@ __global__ void rev_keys_kernel(int n, const int4* __restrict__ fwd,
     vals[p] = p;
     atomicAdd(&hist[v], 1);
 }
+
+#endif  // CUSW_MAIN_TU
 
 // ------------------------------------------------------------------------------------------
 // The score pass (forward: phase 1 of ssw_align; REV: phase 2, the reverse pass with early stop).
@@ -158,11 +174,23 @@ __global__ void rev_keys_kernel(int n, const int4* __restrict__ fwd,
 // maximum, then the smallest row holding it. Each virtual lane keeps (best, col, row) with strict
 // improvement; the group reduces with the key (score, -col, -row).
 // ------------------------------------------------------------------------------------------
-template <int G, int R, bool REV>
+// MULTI (G == 32 only): the query is strip-mined into blocks of 2*G*R rows processed one after the
+// other by the same warp; the bottom row (H, F) of a strip is written per column to a boundary
+// buffer in global memory (one 32-bit word per column) and read back by lane 0 of the next strip.
+// This is the long-contig path (BASELINE.json C5: 10 kb contigs vs 20 kb windows).
+struct StripPool {
+    uint8_t* base;
+    unsigned long long cap;
+    unsigned long long* used;
+};
+
+template <int G, int R, bool REV, bool MULTI>
 __global__ void __launch_bounds__(128)
 sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4* __restrict__ fwd,
-                int4* __restrict__ out, ScoreConst sc) {
+                int4* __restrict__ out, ScoreConst sc, StripPool sp) {
+    static_assert(!MULTI || G == 32, "strip mining uses one warp per pair");
     constexpr int GPB = 128 / G;
+    constexpr int S = 2 * G * R;  // rows per strip
     const int lig = threadIdx.x % G;
     const int gidx = blockIdx.x * GPB + threadIdx.x / G;
     const bool active = gidx < njobs;
@@ -180,6 +208,14 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             q = f.z + 1;
             qptr += qo + f.z;
             rptr += ro + f.y;
+            // An alignment of `target` inside q rows spans at most q + D columns, D = the deletions its
+            // score budget can pay for; columns beyond cannot hold the first cell reaching `target`.
+            if (sc.ge > 0) {
+                long long budget = (long long)q * sc.match - target - sc.B;
+                long long dmax = budget >= 0 ? budget / sc.ge + 1 : 0;
+                long long lim = (long long)q + dmax + 1;
+                if (lim < w) w = (int)lim;
+            }
         } else {
             q = (int)(io.seq_off[pair + 1] - qo);
             w = (int)(io.ref_off[pair + 1] - ro);
@@ -189,10 +225,34 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     }
     constexpr int STEP = REV ? -1 : 1;
 
+    // strip-mining state
+    int nstrips = 1;
+    uint32_t* bnd_in = nullptr;
+    uint32_t* bnd_out = nullptr;
+    bool failed = false;
+    if (MULTI) {
+        nstrips = active ? (q + S - 1) / S : 0;
+        if (nstrips > 1) {
+            unsigned long long off = 0;
+            const unsigned long long need = (((unsigned long long)w * 4ull + 15ull) & ~15ull) * 2ull;
+            if (lig == 0) off = atomicAdd(sp.used, need);
+            off = __shfl_sync(0xffffffffu, off, 0);
+            if (off + need > sp.cap) { failed = true; nstrips = 0; }
+            else {
+                bnd_in = reinterpret_cast<uint32_t*>(sp.base + off);
+                bnd_out = reinterpret_cast<uint32_t*>(sp.base + off + need / 2);
+            }
+        }
+    }
+    unsigned long long key = 0;  // running (score, -col, -row) maximum of this thread's virtual lanes
+
+    for (int strip = 0; strip < (MULTI ? nstrips : 1); ++strip) {
+    const int row0 = strip * S;
+
     // query rows -> PRMT selector halves (low byte: low virtual lane, high byte: high one)
     uint32_t Q[R];
     {
-        const int r0 = (2 * lig) * R;
+        const int r0 = row0 + (2 * lig) * R;
 #pragma unroll
         for (int k = 0; k < R; k++) {
             int a = r0 + k, b = r0 + R + k;
@@ -213,15 +273,25 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     int t_end = active ? w + 2 * G - 1 : 0;
     int t_end_warp = __reduce_max_sync(0xffffffffu, t_end);
 
-    // prefetch the window byte of step 0
+    // prefetch the window byte (and, when strip-mining, the boundary word) of step 0
     int c = -2 * lig;  // column of the low virtual lane at step t
     uint32_t rb_next = ((unsigned)c < (unsigned)w) ? (uint32_t)rptr[(int64_t)c * STEP] : kWindowPad;
+    uint32_t top_next = 0u;  // lane 0 only: (H | F << 16) of the row above this strip at column c
+    const bool read_top = MULTI && strip > 0 && lig == 0;
+    const bool write_bot = MULTI && strip + 1 < nstrips && lig == G - 1;
+    if (MULTI) {
+        top_next = sc.BB & 0xFFFFu;
+        if (read_top && (unsigned)c < (unsigned)w) top_next = bnd_in[c];
+    }
 
     for (int t = 0; t < t_end_warp; ++t, ++c) {
         // ---- inputs from the virtual lane above
         uint32_t rH = __shfl_up_sync(0xffffffffu, Hout, 1, G);
         uint32_t rF = __shfl_up_sync(0xffffffffu, Fout, 1, G);
-        if (lig == 0) { rH = sc.BB; rF = 0u; }  // row -1 of the matrix: H = 0, F = -inf
+        if (lig == 0) {  // row above the strip: matrix row -1 (H = 0, F = -inf) or the previous strip
+            rH = sc.BB; rF = 0u;
+            if (MULTI) { rH = top_next << 16; rF = top_next & 0xFFFF0000u; }
+        }
         const uint32_t Hin = prmt(rH, Hout, 0x5432u);  // lo <- upper lane's hi half, hi <- own lo half
         uint32_t F = prmt(rF, Fout, 0x5432u);
 
@@ -231,6 +301,10 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             int cn = c + 1;
             rb_next = kWindowPad;
             if ((unsigned)cn < (unsigned)w) rb_next = (uint32_t)rptr[(int64_t)cn * STEP];
+            if (MULTI) {
+                top_next = sc.BB & 0xFFFFu;
+                if (read_top && (unsigned)cn < (unsigned)w) top_next = bnd_in[cn];
+            }
         }
         Rsel = prmt(Rsel, rb, 0x3204u);  // byte1 <- old byte0, byte0 <- new
 
@@ -252,6 +326,10 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         if (R & 1) cm = __vmaxs2(cm, H[R - 1]);
         Hout = H[R - 1];
         Fout = F;
+        if (MULTI) {
+            // bottom row of the strip (hi half = last virtual lane, column c-1) -> boundary buffer
+            if (write_bot && (unsigned)(c - 1) < (unsigned)w) bnd_out[c - 1] = (Hout >> 16) | (Fout & 0xFFFF0000u);
+        }
 
         // ---- running best with strict improvement
         // (not __vibmax_s16x2: its header asm lets the output alias input `a`, which turns both
@@ -292,15 +370,39 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         }
     }
 
-    // ---- group reduction: max score, then min column, then min row
-    const int rbase = (2 * lig) * R;
-    unsigned long long klo = ((unsigned long long)(best & 0xFFFFu) << 40) |
-                             ((unsigned long long)(0xFFFFFFu - (uint32_t)(col_lo + 1)) << 16) |
-                             (unsigned long long)(0xFFFFu - (uint32_t)(rbase + row_lo));
-    unsigned long long khi = ((unsigned long long)(best >> 16) << 40) |
-                             ((unsigned long long)(0xFFFFFFu - (uint32_t)(col_hi + 1)) << 16) |
-                             (unsigned long long)(0xFFFFu - (uint32_t)(rbase + R + row_hi));
-    unsigned long long key = klo > khi ? klo : khi;
+    // ---- fold this strip's virtual lanes into the running key: max score, then min column, then min row
+    {
+        const int rbase = row0 + (2 * lig) * R;
+        unsigned long long klo = ((unsigned long long)(best & 0xFFFFu) << 40) |
+                                 ((unsigned long long)(0xFFFFFFu - (uint32_t)(col_lo + 1)) << 16) |
+                                 (unsigned long long)(0xFFFFu - (uint32_t)(rbase + row_lo));
+        unsigned long long khi = ((unsigned long long)(best >> 16) << 40) |
+                                 ((unsigned long long)(0xFFFFFFu - (uint32_t)(col_hi + 1)) << 16) |
+                                 (unsigned long long)(0xFFFFu - (uint32_t)(rbase + R + row_hi));
+        const unsigned long long k2 = klo > khi ? klo : khi;
+        key = k2 > key ? k2 : key;
+    }
+    if (MULTI) {
+        // later strips read what this one wrote (same warp, different lanes)
+        __syncwarp();
+        uint32_t* tmp = bnd_in; bnd_in = bnd_out; bnd_out = tmp;
+        if (REV) {
+            // columns past the first one that reached `target` cannot matter any more
+            unsigned long long kk = key;
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) {
+                unsigned long long other = __shfl_xor_sync(0xffffffffu, kk, o);
+                kk = other > kk ? other : kk;
+            }
+            if ((int)(kk >> 40) == target + sc.B) {
+                int colf = (int)(0xFFFFFFu - (uint32_t)((kk >> 16) & 0xFFFFFFu)) - 1;
+                w = min(w, colf + 1);
+            }
+        }
+    }
+    }  // strips
+
+    // ---- group reduction
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) {
         unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
@@ -310,10 +412,11 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         int score = (int)(key >> 40) - sc.B;
         int col = (int)(0xFFFFFFu - (uint32_t)((key >> 16) & 0xFFFFFFu)) - 1;
         int row = (int)(0xFFFFu - (uint32_t)(key & 0xFFFFu));
-        out[pair] = make_int4(score, col, row, 0);
+        out[pair] = make_int4(score, col, row, failed ? 1 : 0);
     }
 }
 
+#ifdef CUSW_MAIN_TU
 // ------------------------------------------------------------------------------------------
 // Phase 3: banded traceback (banded_sw, ssw.c:557-734). One thread per pair.
 // The band rule, the zero borders (including the `edge` quirk, ssw.c:596), every tie-break and the
@@ -407,6 +510,7 @@ sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* 
         nbody = 1;
     } else {
         const int4 rv = rev[pair];
+        if (rv.w != 0) { res[pair].status = CUDASW_ENOMEM; return; }     // strip buffers exhausted
         if (rv.x != score) { res[pair].status = CUDASW_ECUDA; return; }  // internal inconsistency
         ref_begin = ref_end - rv.y;
         read_begin = read_end - rv.z;
@@ -495,5 +599,7 @@ sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* 
     }
     res[pair] = r;
 }
+
+#endif  // CUSW_MAIN_TU
 
 }  // namespace cusw

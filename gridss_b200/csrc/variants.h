@@ -1,0 +1,31 @@
+// variants.h - the (G, R) instantiation table of sw_score_kernel, split over several translation
+// units (score_variants.cu compiled once per G) so the build parallelises.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <vector>
+
+#include "sw_kernels.cuh"
+
+namespace cusw {
+
+typedef void (*score_launch_fn)(const int*, int, PairIO, const int4*, int4*, ScoreConst, StripPool, cudaStream_t);
+
+struct Variant {
+    int G, R, rows;  // rows = 2*G*R; for multi (strip-mined) variants rows per strip
+    bool multi;
+    score_launch_fn fwd, rev;
+};
+
+// defined in score_variants.cu, one per -DSCORE_G
+void variants_g1(std::vector<Variant>&);
+void variants_g2(std::vector<Variant>&);
+void variants_g4(std::vector<Variant>&);
+void variants_g8(std::vector<Variant>&);
+void variants_g16(std::vector<Variant>&);
+void variants_g32(std::vector<Variant>&);
+
+// single-strip variants ascending by rows, then the strip-mined ones; for equal rows the larger R (fewer lanes) wins; CUDASW_VARIANTS="8x19,4x38" restricts
+std::vector<Variant> collect_variants();
+
+}  // namespace cusw

@@ -125,6 +125,9 @@ int cudasw_poll(cudasw_t* h, int64_t ticket, cudasw_result* res, uint32_t* cigar
                 int32_t cigar_cap, int32_t* cigar_len);
 
 int cudasw_get_stats(cudasw_t* h, cudasw_stats* out);
+/* Which score-pass kernel variant a query of `query_len` rows is dispatched to: lanes per pair (G),
+ * rows per virtual lane (R), strips (1 unless strip-mined). For reporting (bench.py roofline line). */
+int cudasw_variant_for(cudasw_t* h, int32_t query_len, int32_t* lanes, int32_t* rows_per_lane, int32_t* strips);
 const char* cudasw_last_error(cudasw_t* h); /* h may be NULL: last create() error */
 int cudasw_device_count(void);
 const char* cudasw_version(void);

@@ -175,3 +175,34 @@ def test_order_invariance_and_idempotence(aligner, synth):
         assert a.score == int(res[i]["score"])
         from gridss_b200 import cigar_string
         assert a.getCigar() == cigar_string(_cig(res, cig, i))
+
+
+def test_long_queries_strip_mined(aligner, oracle, synth):
+    """queries longer than one 2048-row strip go through the strip-mined warp kernel (C5 path)"""
+    rng = np.random.default_rng(11)
+    seqs, refs = [], []
+    for q in (2049, 2500, 2561, 3000, 4096, 4097, 5121, 6500):
+        w = int(q * rng.uniform(1.0, 2.0)) + 10
+        r = rng.choice(list(b"ACGT"), size=w).astype(np.uint8)
+        st = int(rng.integers(0, w - q + 1))
+        s = r[st:st + q].copy()
+        for k in range(q // 40):
+            s[int(rng.integers(0, q))] = int(rng.choice(list(b"ACGT")))
+        s = bytearray(s.tobytes())
+        # a few indels
+        for k in range(3):
+            p = int(rng.integers(50, len(s) - 50))
+            if rng.random() < 0.5:
+                del s[p:p + int(rng.integers(1, 20))]
+            else:
+                s[p:p] = bytes(rng.choice(list(b"ACGT"), size=int(rng.integers(1, 20))).tolist())
+        seqs.append(bytes(s))
+        refs.append(r.tobytes())
+    bad, undef = _compare(aligner, oracle, seqs, refs)
+    assert bad == [] and undef == 0, bad[:3]
+
+
+def test_c5_long_contigs_vs_oracle(aligner, oracle, synth):
+    sb, so, rb, ro = synth.generate(5, 6)
+    bad, undef = _compare_blobs(aligner, oracle, sb, so, rb, ro)
+    assert bad == [] and undef == 0, bad[:3]
