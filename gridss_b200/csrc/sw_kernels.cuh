@@ -336,21 +336,17 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         //  predicates into constants when best is updated in place)
         const uint32_t nb = __vmaxs2(best, cm);
         if (nb != best) {
+            // first row of each half whose H equals the new maximum = number of rows whose running
+            // prefix maximum is still below it; both halves at once, 2 ALU + 2 FMA-pipe ops per row
+            uint32_t pm = sc.BB, cnt = 0u;
+#pragma unroll
+            for (int k = 0; k < R; k++) {
+                pm = __vmaxs2(pm, H[k]);
+                cnt += __vminu2(nb - pm, 0x00010001u);  // nb >= pm per half: plain subtract is exact
+            }
             const uint32_t changed = nb ^ best;
-            if (changed & 0xFFFFu) {
-                col_lo = c;
-                const uint32_t v = nb & 0xFFFFu;
-#pragma unroll
-                for (int k = R - 1; k >= 0; k--)
-                    if ((H[k] & 0xFFFFu) == v) row_lo = k;
-            }
-            if (changed >> 16) {
-                col_hi = c - 1;
-                const uint32_t v = nb >> 16;
-#pragma unroll
-                for (int k = R - 1; k >= 0; k--)
-                    if ((H[k] >> 16) == v) row_hi = k;
-            }
+            if (changed & 0xFFFFu) { col_lo = c; row_lo = (int)(cnt & 0xFFFFu); }
+            if (changed >> 16) { col_hi = c - 1; row_hi = (int)(cnt >> 16); }
         }
         best = nb;
 
