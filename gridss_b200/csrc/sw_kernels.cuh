@@ -261,9 +261,12 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             Q[k] = qa | (qb << 8);
         }
     }
-    uint32_t H[R], E[R];
+    // H ping-pongs between two register arrays (HA -> HB -> HA ...) so that `diag = old H[k]` needs no
+    // register moves; the step loop is therefore unrolled by two and the trip count rounded up to even
+    // (an extra step only sees pad columns, which can never strictly improve a maximum).
+    uint32_t HA[R], HB[R], E[R];
 #pragma unroll
-    for (int k = 0; k < R; k++) { H[k] = sc.BB; E[k] = 0u; }
+    for (int k = 0; k < R; k++) { HA[k] = sc.BB; HB[k] = sc.BB; E[k] = 0u; }
 
     uint32_t best = sc.BB;
     int col_lo = -1, col_hi = -1, row_lo = 0, row_hi = 0;
@@ -271,7 +274,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     uint32_t Rsel = kWindowPad | (kWindowPad << 8);
 
     int t_end = active ? w + 2 * G - 1 : 0;
-    int t_end_warp = __reduce_max_sync(0xffffffffu, t_end);
+    int t_end_warp = (__reduce_max_sync(0xffffffffu, t_end) + 1) & ~1;
 
     // prefetch the window byte (and, when strip-mining, the boundary word) of step 0
     int c = -2 * lig;  // column of the low virtual lane at step t
@@ -284,7 +287,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         if (read_top && (unsigned)c < (unsigned)w) top_next = bnd_in[c];
     }
 
-    for (int t = 0; t < t_end_warp; ++t, ++c) {
+    auto step = [&](const uint32_t (&Ho)[R], uint32_t (&Hn)[R]) {
         // ---- inputs from the virtual lane above
         uint32_t rH = __shfl_up_sync(0xffffffffu, Hout, 1, G);
         uint32_t rF = __shfl_up_sync(0xffffffffu, Fout, 1, G);
@@ -316,15 +319,15 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             const uint32_t s = prmt(sc.poolA, sc.poolB, Q[k] ^ Rsel);
             const uint32_t m = __vimax3_s16x2(E[k], F, sc.BB);
             const uint32_t h = __viaddmax_s16x2(diag, s, m);
-            diag = H[k];
-            H[k] = h;
+            diag = Ho[k];
+            Hn[k] = h;
             const uint32_t hg = h - sc.GO2;
             E[k] = __viaddmax_s16x2(E[k], sc.NGE2, hg);
             F = __viaddmax_s16x2(F, sc.NGE2, hg);
-            if (k & 1) cm = __vimax3_s16x2(cm, H[k - 1], h);
+            if (k & 1) cm = __vimax3_s16x2(cm, Hn[k - 1], h);
         }
-        if (R & 1) cm = __vmaxs2(cm, H[R - 1]);
-        Hout = H[R - 1];
+        if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
+        Hout = Hn[R - 1];
         Fout = F;
         if (MULTI) {
             // bottom row of the strip (hi half = last virtual lane, column c-1) -> boundary buffer
@@ -337,11 +340,11 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         const uint32_t nb = __vmaxs2(best, cm);
         if (nb != best) {
             // first row of each half whose H equals the new maximum = number of rows whose running
-            // prefix maximum is still below it; both halves at once, 2 ALU + 2 FMA-pipe ops per row
+            // prefix maximum is still below it; both halves at once
             uint32_t pm = sc.BB, cnt = 0u;
 #pragma unroll
             for (int k = 0; k < R; k++) {
-                pm = __vmaxs2(pm, H[k]);
+                pm = __vmaxs2(pm, Hn[k]);
                 cnt += __vminu2(nb - pm, 0x00010001u);  // nb >= pm per half: plain subtract is exact
             }
             const uint32_t changed = nb ^ best;
@@ -349,19 +352,24 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             if (changed >> 16) { col_hi = c - 1; row_hi = (int)(cnt >> 16); }
         }
         best = nb;
+        ++c;
+    };
 
+    for (int t = 0; t < t_end_warp; t += 2) {
+        step(HA, HB);
+        step(HB, HA);
         if (REV) {
             // early stop (ssw.c:296): once a lane holds `target`, later lanes may still find it in an
             // earlier column, so run on until the last virtual lane has passed this column.
-            if ((t & 3) == 3) {
+            if ((t & 2) == 2) {
                 const int tg = target + sc.B;
                 bool found = ((int)(best & 0xFFFFu) == tg) || ((int)(best >> 16) == tg);
-                if (found) t_end = min(t_end, t + 2 * G + 1);
+                if (found) t_end = min(t_end, t + 1 + 2 * G + 1);
                 // all lanes of a group must agree on t_end
 #pragma unroll
                 for (int o = G / 2; o > 0; o >>= 1)
                     t_end = min(t_end, __shfl_xor_sync(0xffffffffu, t_end, o));
-                t_end_warp = __reduce_max_sync(0xffffffffu, t_end);
+                t_end_warp = (__reduce_max_sync(0xffffffffu, t_end) + 1) & ~1;
             }
         }
     }
