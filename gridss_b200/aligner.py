@@ -230,13 +230,20 @@ class CudaAligner(Aligner):
         return self.align_batch([seq], [ref])[0]
 
     # -- batched entry points
-    def align_blobs(self, seq_blob, seq_off, ref_blob, ref_off, cigar_cap: int | None = None):
-        """Host blobs (numpy uint8 + int64 offsets) -> (RESULT_DTYPE[n], uint32 cigar blob)."""
+    def align_blobs(self, seq_blob, seq_off, ref_blob, ref_off, cigar_cap: int | None = None, res=None, cig=None):
+        """Host blobs (numpy uint8 + int64 offsets) -> (RESULT_DTYPE[n], uint32 cigar blob).
+
+        `res` / `cig` may supply preallocated output arrays (e.g. views of pinned memory)."""
         n = len(seq_off) - 1
-        res = np.zeros(n, dtype=RESULT_DTYPE)
+        if res is None:
+            res = np.zeros(n, dtype=RESULT_DTYPE)
+        assert len(res) >= n
         cap = int(cigar_cap if cigar_cap is not None else max(64, 24 * n))
+        if cig is not None:
+            cap = len(cig)
         while True:
-            cig = np.zeros(cap, dtype=np.uint32)
+            if cig is None or len(cig) < cap:
+                cig = np.zeros(cap, dtype=np.uint32)
             used = ctypes.c_int64(0)
             rc = self._lib.cudasw_align_batch(
                 self._h, n, seq_blob.ctypes.data, seq_off.ctypes.data, ref_blob.ctypes.data,

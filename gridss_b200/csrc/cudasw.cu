@@ -69,6 +69,9 @@ struct cudasw {
     TbConst tc{};
     VariantTable vt{};
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;  // H2D of the next chunk while the current one computes
+    std::vector<cudaEvent_t> h2d_done;
+    std::vector<int16_t> var_by_q;  // host copy of variant_of() for the stats
     cudaEvent_t ev[8]{};
     std::mutex mu;
     std::string error;
@@ -102,6 +105,10 @@ struct cudasw {
     std::unordered_map<int64_t, Done> done;
 
     void set_error(const std::string& s) { error = s; }
+    int process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so, const uint8_t* d_ref,
+                      const int64_t* d_ro, int64_t q_lo, int64_t q_hi, int64_t w_lo, int64_t w_hi, int64_t cigar_cap,
+                      uint64_t* launches_out);
+    int finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out);
     int run(int64_t n, const uint8_t* d_seq, const int64_t* d_seq_off, const uint8_t* d_ref,
             const int64_t* d_ref_off, int64_t total_q, int64_t total_w, cudasw_result* out,
             uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used, bool inputs_on_host,
@@ -164,6 +171,8 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess)
         return fail(cudaGetErrorString(e));
+    if ((e = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking)) != cudaSuccess)
+        return fail(cudaGetErrorString(e));
     for (auto& ev : h->ev)
         if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_hist, 128 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
@@ -215,6 +224,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     h->raw_seq.release(); h->raw_ref.release(); h->enc_seq.release(); h->enc_ref.release();
     h->seq_off.release(); h->ref_off.release(); h->keys.release(); h->keys_alt.release();
     h->vals.release(); h->vals_alt.release(); h->retry_a.release(); h->retry_b.release();
@@ -226,8 +236,143 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     if (h->h_counters) cudaFreeHost(h->h_counters);
     for (auto& ev : h->ev)
         if (ev) cudaEventDestroy(ev);
+    for (auto& ev : h->h2d_done) cudaEventDestroy(ev);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
+}
+
+// One chunk of pairs [first, first+cnt): encode -> bin -> forward -> bin -> reverse -> traceback.
+// Blob offsets are absolute, so a chunk is just a shifted view of the per-pair arrays.
+int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so,
+                          const uint8_t* d_ref, const int64_t* d_ro, int64_t q_lo, int64_t q_hi,
+                          int64_t w_lo, int64_t w_hi, int64_t cigar_cap, uint64_t* launches_out) {
+    cudaStream_t st = stream;
+    uint64_t launches = 0;
+    const int64_t n = cnt;
+    CK(cudaEventRecord(ev[1], st));
+    // ---- encode + forward binning
+    {
+        const int64_t tq = q_hi - q_lo, tw = w_hi - w_lo;
+        int64_t thr = (tq + 15) / 16;
+        int blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
+        if (tq > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u); launches++; }
+        thr = (tw + 15) / 16;
+        blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
+        if (tw > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u); launches++; }
+    }
+    PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
+    int4* fwd_c = fwd.p + first;
+    cudasw_result* res_c = res.p + first;
+    const bool have_multi = g_var[g_nvar - 1].multi;
+    const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
+                                  scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
+    const int max_cols = (1 << 24) - 2;
+    size_t cub_bytes = cub_tmp.cap;
+    CK(cudaMemsetAsync(d_hist, 0, 128 * sizeof(int), st));
+    fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
+                                                           keys.p, vals.p, d_hist, res_c);
+    launches++;
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
+    launches += 3;
+    CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(ev[2], st));
+    CK(cudaStreamSynchronize(st));
+
+    // ---- forward score pass (strip-mined variants borrow the traceback pool for their boundary rows)
+    CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
+    StripPool spool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+    {
+        int64_t start = 0;
+        for (int v = 0; v < g_nvar; v++) {
+            int c = h_hist[v];
+            if (c > 0) {
+                g_var[v].fwd(vals_alt.p + start, c, io, nullptr, fwd_c, sc, spool, st);
+                launches++;
+            }
+            start += c;
+        }
+    }
+    CK(cudaGetLastError());
+
+    // the stream is idle up to the forward launches (synchronised above); fold the pack time in now
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev[1], ev[2]); stats.ms_pack += ms;
+    *launches_out += launches;
+    return CUDASW_OK;
+}
+
+// Reverse pass + traceback over the whole batch (all of it is encoded and forward-scored by now).
+int cudasw::finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out) {
+    cudaStream_t st = stream;
+    uint64_t launches = 0;
+    PairIO io{enc_seq.p, enc_ref.p, d_so, d_ro};
+    int4* fwd_c = fwd.p;
+    int4* rev_c = rev.p;
+    cudasw_result* res_c = res.p;
+    size_t cub_bytes = cub_tmp.cap;
+    StripPool spool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+    CK(cudaEventRecord(ev[3], st));
+
+    // ---- reverse score pass
+    CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(d_hist, 0, 128 * sizeof(int), st));
+    rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, vt, keys.p, vals.p, d_hist);
+    launches++;
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
+    launches += 3;
+    CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    {
+        int64_t start = 0;
+        for (int v = 0; v < g_nvar; v++) {
+            int c = h_hist[v];
+            if (c > 0) {
+                g_var[v].rev(vals_alt.p + start, c, io, fwd_c, rev_c, sc, spool, st);
+                launches++;
+            }
+            start += c;
+        }
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ev[4], st));
+
+    // ---- traceback (+ retry rounds when the scratch pool runs out); the CIGAR counter [1] runs on across chunks
+    {
+        CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
+        CK(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned long long), st));
+        TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+        int* retry_count = reinterpret_cast<int*>(d_counters + 2);
+        const int* list = vals_alt.p;  // first round: every pair (sorted order of the reverse pass)
+        int c = (int)n;
+        int* retry_out = retry_a.p;
+        for (int round = 0; round < 64 && c > 0; round++) {
+            sw_traceback_kernel<<<(c + 127) / 128, 128, 0, st>>>(list, c, io, fwd_c, rev_c, tc, pool, res_c,
+                                                                cig.p, (unsigned long long)cigar_cap,
+                                                                d_counters + 1, retry_out, retry_count);
+            launches++;
+            CK(cudaEventRecord(ev[5], st));
+            CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            int nretry = *reinterpret_cast<int*>(h_counters + 2);
+            if (nretry == 0) { c = 0; break; }
+            if (nretry == c && round > 0) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
+            // reset pool + retry counter, keep cigar counter
+            CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
+            CK(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned long long), st));
+            list = retry_out;
+            retry_out = (retry_out == retry_a.p) ? retry_b.p : retry_a.p;
+            c = nretry;
+        }
+        if (c > 0) { set_error("traceback did not converge"); return CUDASW_ENOMEM; }
+    }
+    CK(cudaGetLastError());
+    // the stream is idle here (synchronised above): fold this chunk's phase times into the batch stats
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev[3], ev[4]); stats.ms_reverse += ms;
+    cudaEventElapsedTime(&ms, ev[4], ev[5]); stats.ms_traceback += ms;
+    *launches_out += launches;
+    return CUDASW_OK;
 }
 
 int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
@@ -247,6 +392,52 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     cudaStream_t st = stream;
     uint64_t launches = 0;
 
+    // ---- chunk plan: pair ranges of about chunk_bytes of sequence each. With host inputs the H2D copy of
+    // chunk i+1 (copy stream) overlaps the kernels of chunk i (compute stream).
+    struct Chunk { int64_t first, cnt, q_lo, q_hi, w_lo, w_hi; };
+    std::vector<Chunk> chunks;
+    {
+        // chunk sizes grow geometrically (64 MB, 128 MB, ... capped at 1 GB): the first copy is the only one the
+        // kernels have to wait for, and each later copy hides behind the (slower) kernels of the chunk before it
+        int64_t target = inputs_on_host ? (int64_t)64 << 20 : (int64_t)1 << 60;  // resident inputs: nothing to overlap
+        int64_t target_max = (int64_t)1 << 30;
+        if (const char* e = getenv("CUDASW_CHUNK_MB")) target = target_max = std::max<int64_t>(1, atoll(e)) << 20;
+        const int64_t max_pairs = 8 << 20;  // keeps the per-chunk sort/bin arrays small
+        int64_t first = 0;
+        while (first < n) {
+            int64_t last = first;
+            if (h_seq_off && h_ref_off) {
+                // largest `last` with bytes(first..last) <= target (offsets are monotone: binary search)
+                int64_t lo = first + 1, hi = std::min(n, first + max_pairs);
+                const int64_t base = h_seq_off[first] + h_ref_off[first];
+                while (lo < hi) {
+                    int64_t mid = lo + (hi - lo + 1) / 2;
+                    if (h_seq_off[mid] + h_ref_off[mid] - base <= target) lo = mid; else hi = mid - 1;
+                }
+                last = lo;
+            } else {
+                last = n;
+            }
+            // an offset array that is not monotone is caught per pair by fwd_keys_kernel (EINVAL); clamp here
+            Chunk c{first, last - first, 0, 0, 0, 0};
+            if (h_seq_off && h_ref_off) {
+                c.q_lo = h_seq_off[first]; c.q_hi = h_seq_off[last];
+                c.w_lo = h_ref_off[first]; c.w_hi = h_ref_off[last];
+                if (c.q_lo < 0 || c.q_hi < c.q_lo || c.q_hi > total_q || c.w_lo < 0 || c.w_hi < c.w_lo || c.w_hi > total_w) {
+                    set_error("offsets must be non-decreasing from 0");
+                    return CUDASW_EINVAL;
+                }
+            } else {
+                c.q_hi = total_q; c.w_hi = total_w;
+            }
+            chunks.push_back(c);
+            first = last;
+            target = std::min(target * 2, std::max(target, target_max));
+        }
+    }
+    int64_t max_cnt = 0;
+    for (auto& c : chunks) max_cnt = std::max(max_cnt, c.cnt);
+
     // ---- capacity
     CK(enc_seq.ensure((size_t)total_q + 16));
     CK(enc_ref.ensure((size_t)total_w + 16));
@@ -254,9 +445,11 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(retry_a.ensure(n)); CK(retry_b.ensure(n));
     CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n));
     CK(cig.ensure((size_t)std::max<int64_t>(cigar_cap, 1)));
-    size_t cub_bytes = 0;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
-    CK(cub_tmp.ensure(cub_bytes + 16));
+    {
+        size_t cub_bytes = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
+        CK(cub_tmp.ensure(cub_bytes + 16));
+    }
     if (!tb_pool.p) {
         size_t free_b = 0, total_b = 0;
         CK(cudaMemGetInfo(&free_b, &total_b));
@@ -267,9 +460,15 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         CK(tb_pool.ensure(want));
         tb_pool_bytes = want;
     }
+    while (h2d_done.size() < chunks.size()) {
+        cudaEvent_t e;
+        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h2d_done.push_back(e);
+    }
 
     CK(cudaEventRecord(ev[0], st));
-    // ---- H2D
+    CK(cudaMemsetAsync(d_counters, 0, 8 * sizeof(unsigned long long), st));
+    // ---- H2D: everything is queued on the copy stream now, one event per chunk
     const uint8_t* d_seq = d_seq_in;
     const uint8_t* d_ref = d_ref_in;
     const int64_t* d_so = d_seq_off_in;
@@ -279,109 +478,33 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         CK(raw_ref.ensure((size_t)total_w + 16));
         CK(seq_off.ensure(n + 1));
         CK(ref_off.ensure(n + 1));
-        CK(cudaMemcpyAsync(raw_seq.p, h_seq, (size_t)total_q, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(raw_ref.p, h_ref, (size_t)total_w, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(seq_off.p, h_seq_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(ref_off.p, h_ref_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaEventRecord(ev[7], st));
+        CK(cudaStreamWaitEvent(copy_stream, ev[7], 0));  // the previous batch's kernels no longer read raw_*
+        CK(cudaMemcpyAsync(seq_off.p, h_seq_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
+        CK(cudaMemcpyAsync(ref_off.p, h_ref_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
+        for (size_t i = 0; i < chunks.size(); i++) {
+            const Chunk& c = chunks[i];
+            if (c.q_hi > c.q_lo) CK(cudaMemcpyAsync(raw_seq.p + c.q_lo, h_seq + c.q_lo, (size_t)(c.q_hi - c.q_lo), cudaMemcpyHostToDevice, copy_stream));
+            if (c.w_hi > c.w_lo) CK(cudaMemcpyAsync(raw_ref.p + c.w_lo, h_ref + c.w_lo, (size_t)(c.w_hi - c.w_lo), cudaMemcpyHostToDevice, copy_stream));
+            CK(cudaEventRecord(h2d_done[i], copy_stream));
+        }
         d_seq = raw_seq.p; d_ref = raw_ref.p; d_so = seq_off.p; d_ro = ref_off.p;
         stats.h2d_bytes = (uint64_t)total_q + (uint64_t)total_w + (uint64_t)(n + 1) * 16;
     }
-    CK(cudaEventRecord(ev[1], st));
 
-    // ---- encode + forward binning
-    {
-        int64_t thr = (total_q + 15) / 16;
-        int blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
-        if (total_q > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq, enc_seq.p, total_q, 0u); launches++; }
-        thr = (total_w + 15) / 16;
-        blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
-        if (total_w > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref, enc_ref.p, total_w, 0x80u); launches++; }
-    }
-    PairIO io{enc_seq.p, enc_ref.p, d_so, d_ro};
-    const bool have_multi = g_var[g_nvar - 1].multi;
-    const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
-                                  scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
-    const int max_cols = (1 << 24) - 2;
-    CK(cudaMemsetAsync(d_hist, 0, 128 * sizeof(int), st));
-    fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, d_so, d_ro, vt, max_rows, max_cols,
-                                                           keys.p, vals.p, d_hist, res.p);
-    launches++;
-    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
-    launches += 3;
-    CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CK(cudaEventRecord(ev[2], st));
-    CK(cudaStreamSynchronize(st));
-
-    // ---- forward score pass (strip-mined variants borrow the traceback pool for their boundary rows)
-    CK(cudaMemsetAsync(d_counters, 0, 8 * sizeof(unsigned long long), st));
-    StripPool spool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
-    {
-        int64_t start = 0;
-        for (int v = 0; v < g_nvar; v++) {
-            int cnt = h_hist[v];
-            if (cnt > 0) {
-                g_var[v].fwd(vals_alt.p + start, cnt, io, nullptr, fwd.p, sc, spool, st);
-                launches++;
-                stats.forward_cells_padded += 0;  // filled below from host offsets when available
-            }
-            start += cnt;
+    for (size_t i = 0; i < chunks.size(); i++) {
+        const Chunk& c = chunks[i];
+        if (inputs_on_host) CK(cudaStreamWaitEvent(st, h2d_done[i], 0));
+        int rc = process_chunk(c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, cigar_cap, &launches);
+        if (rc != CUDASW_OK) {
+            cudaStreamSynchronize(copy_stream);  // do not leave copies in flight over the caller's buffers
+            return rc;
         }
     }
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(ev[3], st));
-
-    // ---- reverse score pass
-    CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
-    CK(cudaMemsetAsync(d_hist, 0, 128 * sizeof(int), st));
-    rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd.p, res.p, vt, keys.p, vals.p, d_hist);
-    launches++;
-    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
-    launches += 3;
-    CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
     {
-        int64_t start = 0;
-        for (int v = 0; v < g_nvar; v++) {
-            int cnt = h_hist[v];
-            if (cnt > 0) {
-                g_var[v].rev(vals_alt.p + start, cnt, io, fwd.p, rev.p, sc, spool, st);
-                launches++;
-            }
-            start += cnt;
-        }
+        int rc = finish_batch(n, d_so, d_ro, cigar_cap, &launches);
+        if (rc != CUDASW_OK) return rc;
     }
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(ev[4], st));
-
-    // ---- traceback (+ retry rounds when the scratch pool runs out)
-    {
-        CK(cudaMemsetAsync(d_counters, 0, 8 * sizeof(unsigned long long), st));
-        TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
-        int* retry_count = reinterpret_cast<int*>(d_counters + 2);
-        const int* list = nullptr;  // first round: every pair (sorted order of the reverse pass)
-        int cnt = (int)n;
-        list = vals_alt.p;
-        int* retry_out = retry_a.p;
-        for (int round = 0; round < 64 && cnt > 0; round++) {
-            sw_traceback_kernel<<<(cnt + 127) / 128, 128, 0, st>>>(list, cnt, io, fwd.p, rev.p, tc, pool, res.p,
-                                                                  cig.p, (unsigned long long)cigar_cap,
-                                                                  d_counters + 1, retry_out, retry_count);
-            launches++;
-            CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-            CK(cudaStreamSynchronize(st));
-            int nretry = *reinterpret_cast<int*>(h_counters + 2);
-            if (nretry == 0) { cnt = 0; break; }
-            if (nretry == cnt && round > 0) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
-            // reset pool + retry counter, keep cigar counter
-            CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
-            CK(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned long long), st));
-            list = retry_out;
-            retry_out = (retry_out == retry_a.p) ? retry_b.p : retry_a.p;
-            cnt = nretry;
-        }
-        if (cnt > 0) { set_error("traceback did not converge"); return CUDASW_ENOMEM; }
-    }
-    CK(cudaGetLastError());
     CK(cudaEventRecord(ev[5], st));
 
     // ---- D2H
@@ -396,21 +519,27 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
 
     stats.pairs = (uint64_t)n;
     stats.kernel_launches = launches;
-    cudaEventElapsedTime(&stats.ms_h2d, ev[0], ev[1]);
-    cudaEventElapsedTime(&stats.ms_pack, ev[1], ev[2]);
-    cudaEventElapsedTime(&stats.ms_forward, ev[2], ev[3]);
-    cudaEventElapsedTime(&stats.ms_reverse, ev[3], ev[4]);
-    cudaEventElapsedTime(&stats.ms_traceback, ev[4], ev[5]);
     cudaEventElapsedTime(&stats.ms_d2h, ev[5], ev[6]);
     cudaEventElapsedTime(&stats.ms_total, ev[0], ev[6]);
+    // H2D time not hidden behind kernels = total minus everything else
+    cudaEventElapsedTime(&stats.ms_forward, ev[0], ev[3]);
+    stats.ms_forward -= stats.ms_pack;  // chunk loop = pack + forward kernels (+ any H2D wait, reported as ms_h2d when known)
+    stats.ms_h2d = std::max(0.f, stats.ms_total - stats.ms_pack - stats.ms_forward - stats.ms_reverse - stats.ms_traceback - stats.ms_d2h);
     if (h_seq_off && h_ref_off) {
+        const bool have_multi = g_var[g_nvar - 1].multi;
+        const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
+                                      scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
+        if (var_by_q.empty()) {
+            var_by_q.resize(32768);
+            for (int q = 1; q < 32768; q++) var_by_q[q] = (int16_t)variant_of(vt, q);
+        }
         uint64_t cells = 0, padded = 0;
         for (int64_t i = 0; i < n; i++) {
             int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
             if (q <= 0 || w <= 0) continue;
             cells += (uint64_t)q * (uint64_t)w;
             if (q <= max_rows) {
-                int v = variant_of(vt, (int)q);
+                int v = var_by_q[(size_t)q];
                 uint64_t strips = ((uint64_t)q + g_var[v].rows - 1) / g_var[v].rows;
                 padded += strips * (uint64_t)g_var[v].rows * (uint64_t)(w + 2 * g_var[v].G - 1);
             }

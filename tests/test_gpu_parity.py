@@ -206,3 +206,17 @@ def test_c5_long_contigs_vs_oracle(aligner, oracle, synth):
     sb, so, rb, ro = synth.generate(5, 6)
     bad, undef = _compare_blobs(aligner, oracle, sb, so, rb, ro)
     assert bad == [] and undef == 0, bad[:3]
+
+
+def test_chunked_pipeline_matches_oracle(aligner, oracle, synth, monkeypatch):
+    """host batches are split into chunks whose H2D overlaps the previous chunk's kernels; force many small chunks"""
+    monkeypatch.setenv("CUDASW_CHUNK_MB", "1")
+    sb, so, rb, ro = synth.generate(4, 4000)
+    bad, undef = _compare_blobs(aligner, oracle, sb, so, rb, ro)
+    assert bad == [] and undef == 0, bad[:5]
+    res, cig = aligner.align_blobs(sb, so, rb, ro)
+    monkeypatch.delenv("CUDASW_CHUNK_MB")
+    res2, cig2 = aligner.align_blobs(sb, so, rb, ro)
+    for f in ("score", "ref_begin", "ref_end", "read_begin", "read_end", "cigar_len", "status"):
+        assert np.array_equal(res[f], res2[f])
+    assert all(_cig(res, cig, i) == _cig(res2, cig2, i) for i in range(len(res)))
