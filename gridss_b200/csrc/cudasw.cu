@@ -189,6 +189,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     h->sc.B = sc.gap_open;
     h->sc.BB = pack2(sc.gap_open);
     h->sc.GO2 = pack2(sc.gap_open);
+    h->sc.GOBB = pack2(2 * sc.gap_open);
     h->sc.NGE2 = pack2(-sc.gap_extend);
     h->sc.ge = sc.gap_extend;
     h->sc.match = sc.match;

@@ -69,6 +69,7 @@ struct ScoreConst {
     uint32_t poolA, poolB;  // PRMT byte pool: pool[x] = substitution score of symbol-xor x
     uint32_t BB;            // bias B = gap_open in both halves (stored value = true value + B)
     uint32_t GO2;           // gap_open in both halves
+    uint32_t GOBB;          // BB + GO2: the biased value of H == gap_open (quiet-step threshold)
     uint32_t NGE2;          // -gap_extend in both halves (two's complement per half)
     int32_t B;      // = gap_open
     int32_t ge, match;
@@ -270,7 +271,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 
     uint32_t best = sc.BB;
     int col_lo = -1, col_hi = -1, row_lo = 0, row_hi = 0;
-    uint32_t Hout = sc.BB, Fout = 0u, Hdiag_top = sc.BB;
+    uint32_t Hout = sc.BB, Fout = 0u, Hdiag_top = sc.BB, Emax = 0u;
     uint32_t Rsel = kWindowPad | (kWindowPad << 8);
 
     int t_end = active ? w + 2 * G - 1 : 0;
@@ -296,7 +297,8 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             if (MULTI) { rH = top_next << 16; rF = top_next & 0xFFFF0000u; }
         }
         const uint32_t Hin = prmt(rH, Hout, 0x5432u);  // lo <- upper lane's hi half, hi <- own lo half
-        uint32_t F = prmt(rF, Fout, 0x5432u);
+        const uint32_t Fin = prmt(rF, Fout, 0x5432u);
+        uint32_t F = 0u;  // stays dead through a quiet step
 
         // ---- window bytes: lo half column c, hi half column c-1
         const uint32_t rb = rb_next;
@@ -311,22 +313,52 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         }
         Rsel = prmt(Rsel, rb, 0x3204u);  // byte1 <- old byte0, byte0 <- new
 
-        uint32_t diag = Hdiag_top;
+        const uint32_t diag0 = Hdiag_top;
         Hdiag_top = Hin;
         uint32_t cm = sc.BB;
+
+        // ---- quiet step (speculative): when every E of this warp and every incoming F is dead (<= 0) and no
+        // cell of the step exceeds gap_open, no gap can be open or opened, so H = max(0, Hdiag + s) and E, F
+        // keep being dead: 3.5 instead of 7.5 instructions per cell pair. Dead values never reach an H (H >= 0)
+        // and every live E/F is re-derived from an H > gap_open, so skipping their updates is exact.
+        // Emax is the exact maximum of this thread's E[] (the max distributes over the E recurrence).
+        bool quiet = false;
+        {
+            const uint32_t live = __vimax3_s16x2(Emax, Fin, sc.BB);
+            if (__all_sync(0xffffffffu, live == sc.BB)) {
+                uint32_t diag = diag0;
 #pragma unroll
-        for (int k = 0; k < R; k++) {
-            const uint32_t s = prmt(sc.poolA, sc.poolB, Q[k] ^ Rsel);
-            const uint32_t m = __vimax3_s16x2(E[k], F, sc.BB);
-            const uint32_t h = __viaddmax_s16x2(diag, s, m);
-            diag = Ho[k];
-            Hn[k] = h;
-            const uint32_t hg = h - sc.GO2;
-            E[k] = __viaddmax_s16x2(E[k], sc.NGE2, hg);
-            F = __viaddmax_s16x2(F, sc.NGE2, hg);
-            if (k & 1) cm = __vimax3_s16x2(cm, Hn[k - 1], h);
+                for (int k = 0; k < R; k++) {
+                    const uint32_t s = prmt(sc.poolA, sc.poolB, Q[k] ^ Rsel);
+                    const uint32_t h = __viaddmax_s16x2(diag, s, sc.BB);
+                    diag = Ho[k];
+                    Hn[k] = h;
+                    if (k & 1) cm = __vimax3_s16x2(cm, Hn[k - 1], h);
+                }
+                if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
+                // verified after the fact: had any h exceeded gap_open, the step is redone in full from Ho
+                quiet = __all_sync(0xffffffffu, __vmaxs2(cm, sc.GOBB) == sc.GOBB);
+            }
         }
-        if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
+        if (!quiet) {
+            uint32_t diag = diag0;
+            cm = sc.BB;
+            F = Fin;
+#pragma unroll
+            for (int k = 0; k < R; k++) {
+                const uint32_t s = prmt(sc.poolA, sc.poolB, Q[k] ^ Rsel);
+                const uint32_t m = __vimax3_s16x2(E[k], F, sc.BB);
+                const uint32_t h = __viaddmax_s16x2(diag, s, m);
+                diag = Ho[k];
+                Hn[k] = h;
+                const uint32_t hg = h - sc.GO2;
+                E[k] = __viaddmax_s16x2(E[k], sc.NGE2, hg);
+                F = __viaddmax_s16x2(F, sc.NGE2, hg);
+                if (k & 1) cm = __vimax3_s16x2(cm, Hn[k - 1], h);
+            }
+            if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
+            Emax = __viaddmax_s16x2(Emax, sc.NGE2, cm - sc.GO2);
+        }
         Hout = Hn[R - 1];
         Fout = F;
         if (MULTI) {
