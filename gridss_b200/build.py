@@ -32,7 +32,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and up_to_date():
         return OUT
     os.makedirs(OBJ, exist_ok=True)
-    extra = ["-Xptxas", "-v"] if verbose else []
+    extra = (["-Xptxas", "-v"] if verbose else []) + os.environ.get("CUDASW_NVCC_EXTRA", "").split()
     jobs = [(os.path.join(OBJ, "cudasw.o"), [os.path.join(CSRC, "cudasw.cu")]),
             (os.path.join(OBJ, "variants.o"), [os.path.join(CSRC, "variants.cu")])]
     for g in GROUPS:

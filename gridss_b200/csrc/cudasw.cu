@@ -88,6 +88,7 @@ struct cudasw {
     DevBuf<uint8_t> cub_tmp;
     DevBuf<uint8_t> tb_pool;
     int* d_hist = nullptr;  // 128 ints
+    uint32_t* d_pool = nullptr;  // {poolA, poolB}
     unsigned long long* d_counters = nullptr;  // [0] pool used, [1] cigar used, [2] retry count(int)
     int* h_hist = nullptr;                     // pinned
     unsigned long long* h_counters = nullptr;  // pinned
@@ -187,6 +188,12 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     h->sc.poolA = b(sc.match) | (b(sc.mismatch) << 8) | (b(sc.mismatch) << 16) | (b(sc.mismatch) << 24);
     h->sc.poolB = b(sc.ambiguous) * 0x01010101u;
     h->sc.B = sc.gap_open;
+    {
+        uint32_t pool[2] = {h->sc.poolA, h->sc.poolB};
+        if ((e = cudaMalloc(&h->d_pool, sizeof pool)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        if ((e = cudaMemcpy(h->d_pool, pool, sizeof pool, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        h->sc.pool_dev = h->d_pool;
+    }
     h->sc.BB = pack2(sc.gap_open);
     h->sc.GO2 = pack2(sc.gap_open);
     h->sc.GOBB = pack2(2 * sc.gap_open);
@@ -232,6 +239,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
     h->cub_tmp.release(); h->tb_pool.release();
     if (h->d_hist) cudaFree(h->d_hist);
+    if (h->d_pool) cudaFree(h->d_pool);
     if (h->d_counters) cudaFree(h->d_counters);
     if (h->h_hist) cudaFreeHost(h->h_hist);
     if (h->h_counters) cudaFreeHost(h->h_counters);
@@ -507,6 +515,9 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         if (rc != CUDASW_OK) return rc;
     }
     CK(cudaEventRecord(ev[5], st));
+#ifdef CUSW_STEP_STATS
+    fprintf(stderr, "[cudasw step stats, forward+reverse warp-steps] quiet %llu, quiet attempt failed %llu, full %llu\n", h_counters[4], h_counters[5], h_counters[6]);
+#endif
 
     // ---- D2H
     unsigned long long used = h_counters[1];

@@ -73,6 +73,7 @@ struct ScoreConst {
     uint32_t NGE2;          // -gap_extend in both halves (two's complement per half)
     int32_t B;      // = gap_open
     int32_t ge, match;
+    const uint32_t* pool_dev;  // {poolA, poolB} in device memory (same values)
 };
 
 struct PairIO {
@@ -225,6 +226,12 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         }
     }
     constexpr int STEP = REV ? -1 : 1;
+    // the PRMT pool lives in ordinary per-thread registers: read through a volatile load so that ptxas neither
+    // keeps it in uniform registers nor re-materialises a copy in front of every PRMT of the row loops
+    uint32_t cPA, cPB;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(cPA) : "l"(sc.pool_dev));
+    asm volatile("ld.volatile.global.u32 %0, [%1+4];" : "=r"(cPB) : "l"(sc.pool_dev));
+    const uint32_t cBB = sc.BB, cGO2 = sc.GO2, cNGE2 = sc.NGE2;
 
     // strip-mining state
     int nstrips = 1;
@@ -293,7 +300,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         uint32_t rH = __shfl_up_sync(0xffffffffu, Hout, 1, G);
         uint32_t rF = __shfl_up_sync(0xffffffffu, Fout, 1, G);
         if (lig == 0) {  // row above the strip: matrix row -1 (H = 0, F = -inf) or the previous strip
-            rH = sc.BB; rF = 0u;
+            rH = cBB; rF = 0u;
             if (MULTI) { rH = top_next << 16; rF = top_next & 0xFFFF0000u; }
         }
         const uint32_t Hin = prmt(rH, Hout, 0x5432u);  // lo <- upper lane's hi half, hi <- own lo half
@@ -307,7 +314,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             rb_next = kWindowPad;
             if ((unsigned)cn < (unsigned)w) rb_next = (uint32_t)rptr[(int64_t)cn * STEP];
             if (MULTI) {
-                top_next = sc.BB & 0xFFFFu;
+                top_next = cBB & 0xFFFFu;
                 if (read_top && (unsigned)cn < (unsigned)w) top_next = bnd_in[cn];
             }
         }
@@ -315,7 +322,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 
         const uint32_t diag0 = Hdiag_top;
         Hdiag_top = Hin;
-        uint32_t cm = sc.BB;
+        uint32_t cm = cBB;
 
         // ---- quiet step (speculative): when every E of this warp and every incoming F is dead (<= 0) and no
         // cell of the step exceeds gap_open, no gap can be open or opened, so H = max(0, Hdiag + s) and E, F
@@ -323,14 +330,20 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         // and every live E/F is re-derived from an H > gap_open, so skipping their updates is exact.
         // Emax is the exact maximum of this thread's E[] (the max distributes over the E recurrence).
         bool quiet = false;
+#ifdef CUSW_STEP_STATS
+        bool tried = false;
+#endif
         {
-            const uint32_t live = __vimax3_s16x2(Emax, Fin, sc.BB);
-            if (__all_sync(0xffffffffu, live == sc.BB)) {
+            const uint32_t live = __vimax3_s16x2(Emax, Fin, cBB);
+            if (__all_sync(0xffffffffu, live == cBB)) {
+#ifdef CUSW_STEP_STATS
+                tried = true;
+#endif
                 uint32_t diag = diag0;
 #pragma unroll
                 for (int k = 0; k < R; k++) {
-                    const uint32_t s = prmt(sc.poolA, sc.poolB, Q[k] ^ Rsel);
-                    const uint32_t h = __viaddmax_s16x2(diag, s, sc.BB);
+                    const uint32_t s = prmt(cPA, cPB, Q[k] ^ Rsel);
+                    const uint32_t h = __viaddmax_s16x2(diag, s, cBB);
                     diag = Ho[k];
                     Hn[k] = h;
                     if (k & 1) cm = __vimax3_s16x2(cm, Hn[k - 1], h);
@@ -342,23 +355,26 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         }
         if (!quiet) {
             uint32_t diag = diag0;
-            cm = sc.BB;
+            cm = cBB;
             F = Fin;
 #pragma unroll
             for (int k = 0; k < R; k++) {
-                const uint32_t s = prmt(sc.poolA, sc.poolB, Q[k] ^ Rsel);
-                const uint32_t m = __vimax3_s16x2(E[k], F, sc.BB);
+                const uint32_t s = prmt(cPA, cPB, Q[k] ^ Rsel);
+                const uint32_t m = __vimax3_s16x2(E[k], F, cBB);
                 const uint32_t h = __viaddmax_s16x2(diag, s, m);
                 diag = Ho[k];
                 Hn[k] = h;
-                const uint32_t hg = h - sc.GO2;
-                E[k] = __viaddmax_s16x2(E[k], sc.NGE2, hg);
-                F = __viaddmax_s16x2(F, sc.NGE2, hg);
+                const uint32_t hg = h - cGO2;
+                E[k] = __viaddmax_s16x2(E[k], cNGE2, hg);
+                F = __viaddmax_s16x2(F, cNGE2, hg);
                 if (k & 1) cm = __vimax3_s16x2(cm, Hn[k - 1], h);
             }
             if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
-            Emax = __viaddmax_s16x2(Emax, sc.NGE2, cm - sc.GO2);
+            Emax = __viaddmax_s16x2(Emax, cNGE2, cm - cGO2);
         }
+#ifdef CUSW_STEP_STATS
+        if ((threadIdx.x & 31) == 0) atomicAdd(sp.used + (quiet ? 4 : tried ? 5 : 6), 1ull);
+#endif
         Hout = Hn[R - 1];
         Fout = F;
         if (MULTI) {
@@ -373,7 +389,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         if (nb != best) {
             // first row of each half whose H equals the new maximum = number of rows whose running
             // prefix maximum is still below it; both halves at once
-            uint32_t pm = sc.BB, cnt = 0u;
+            uint32_t pm = cBB, cnt = 0u;
 #pragma unroll
             for (int k = 0; k < R; k++) {
                 pm = __vmaxs2(pm, Hn[k]);
