@@ -71,6 +71,10 @@ struct cudasw {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;  // H2D of the next chunk while the current one computes
     std::vector<cudaEvent_t> h2d_done;
+    static constexpr int kAux = 4;  // variant kernels of one pass run side by side (mixed-length batches)
+    cudaStream_t aux[kAux]{};
+    cudaEvent_t fork_ev = nullptr, join_ev[kAux]{};
+    int launch_variants(bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool, uint64_t* launches);
     std::vector<int16_t> var_by_q;  // host copy of variant_of() for the stats
     cudaEvent_t ev[8]{};
     std::mutex mu;
@@ -176,6 +180,11 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
         return fail(cudaGetErrorString(e));
     for (auto& ev : h->ev)
         if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(cudaGetErrorString(e));
+    for (auto& a : h->aux)
+        if ((e = cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking)) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaEventCreateWithFlags(&h->fork_ev, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
+    for (auto& j : h->join_ev)
+        if ((e = cudaEventCreateWithFlags(&j, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_hist, 128 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
@@ -246,9 +255,46 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     for (auto& ev : h->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : h->h2d_done) cudaEventDestroy(ev);
+    for (auto& a : h->aux) if (a) { cudaStreamSynchronize(a); cudaStreamDestroy(a); }
+    if (h->fork_ev) cudaEventDestroy(h->fork_ev);
+    for (auto& j : h->join_ev) if (j) cudaEventDestroy(j);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
+}
+
+// Launches the score kernel of every variant that has pairs in h_hist (sorted order in `order`). With several
+// variants the launches are spread over auxiliary streams so that small launches overlap (fork/join by events).
+int cudasw::launch_variants(bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool,
+                            uint64_t* launches) {
+    cudaStream_t st = stream;
+    int nonempty = 0;
+    for (int v = 0; v < g_nvar; v++) nonempty += h_hist[v] > 0;
+    const bool spread = nonempty > 1;
+    if (spread) CK(cudaEventRecord(fork_ev, st));
+    bool used[kAux] = {};
+    int64_t start = 0;
+    int k = 0;
+    for (int v = 0; v < g_nvar; v++) {
+        const int c = h_hist[v];
+        if (c > 0) {
+            cudaStream_t s = st;
+            if (spread) {
+                const int a = k++ % kAux;
+                s = aux[a];
+                if (!used[a]) { CK(cudaStreamWaitEvent(s, fork_ev, 0)); used[a] = true; }
+            }
+            (reverse ? g_var[v].rev : g_var[v].fwd)(order + start, c, io, fwd_c, out_c, sc, spool, s);
+            (*launches)++;
+        }
+        start += c;
+    }
+    for (int a = 0; a < kAux; a++)
+        if (used[a]) {
+            CK(cudaEventRecord(join_ev[a], aux[a]));
+            CK(cudaStreamWaitEvent(st, join_ev[a], 0));
+        }
+    return CUDASW_OK;
 }
 
 // One chunk of pairs [first, first+cnt): encode -> bin -> forward -> bin -> reverse -> traceback.
@@ -291,17 +337,7 @@ int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, cons
     // ---- forward score pass (strip-mined variants borrow the traceback pool for their boundary rows)
     CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
     StripPool spool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
-    {
-        int64_t start = 0;
-        for (int v = 0; v < g_nvar; v++) {
-            int c = h_hist[v];
-            if (c > 0) {
-                g_var[v].fwd(vals_alt.p + start, c, io, nullptr, fwd_c, sc, spool, st);
-                launches++;
-            }
-            start += c;
-        }
-    }
+    { int rc = launch_variants(false, vals_alt.p, io, nullptr, fwd_c, spool, &launches); if (rc != CUDASW_OK) return rc; }
     CK(cudaGetLastError());
 
     // the stream is idle up to the forward launches (synchronised above); fold the pack time in now
@@ -332,43 +368,46 @@ int cudasw::finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, in
     launches += 3;
     CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    {
-        int64_t start = 0;
-        for (int v = 0; v < g_nvar; v++) {
-            int c = h_hist[v];
-            if (c > 0) {
-                g_var[v].rev(vals_alt.p + start, c, io, fwd_c, rev_c, sc, spool, st);
-                launches++;
-            }
-            start += c;
-        }
-    }
+    { int rc = launch_variants(true, vals_alt.p, io, fwd_c, rev_c, spool, &launches); if (rc != CUDASW_OK) return rc; }
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[4], st));
 
-    // ---- traceback (+ retry rounds when the scratch pool runs out); the CIGAR counter [1] runs on across chunks
+    // ---- traceback (+ retry rounds when the scratch pool runs out); the CIGAR counter [1] runs on across rounds.
+    // Short narrow-band pairs: one thread each; long / wide-band pairs are handed to the warp-cooperative kernel.
     {
-        CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
-        CK(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned long long), st));
+        long long wide_cells = 4096;
+        if (const char* e = getenv("CUDASW_TB_WIDE_CELLS")) wide_cells = atoll(e);
         TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
         int* retry_count = reinterpret_cast<int*>(d_counters + 2);
-        const int* list = vals_alt.p;  // first round: every pair (sorted order of the reverse pass)
+        int* wide_count = reinterpret_cast<int*>(d_counters + 3);
+        int* wide_list = reinterpret_cast<int*>(keys.p);  // the sort buffers are free by now
+        const int* list = vals_alt.p;                      // first round: every pair (sorted order of the reverse pass)
         int c = (int)n;
         int* retry_out = retry_a.p;
         for (int round = 0; round < 64 && c > 0; round++) {
+            CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));      // pool
+            CK(cudaMemsetAsync(d_counters + 2, 0, 2 * sizeof(unsigned long long), st));  // retry + wide counters
             sw_traceback_kernel<<<(c + 127) / 128, 128, 0, st>>>(list, c, io, fwd_c, rev_c, tc, pool, res_c,
                                                                 cig.p, (unsigned long long)cigar_cap,
-                                                                d_counters + 1, retry_out, retry_count);
+                                                                d_counters + 1, retry_out, retry_count,
+                                                                wide_cells, wide_list, wide_count);
             launches++;
             CK(cudaEventRecord(ev[5], st));
             CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
+            const int nwide = *reinterpret_cast<int*>(h_counters + 3);
+            if (nwide > 0) {
+                sw_traceback_warp_kernel<<<(nwide + 3) / 4, 128, 0, st>>>(wide_list, nwide, io, fwd_c, rev_c, tc, pool,
+                                                                          res_c, cig.p, (unsigned long long)cigar_cap,
+                                                                          d_counters + 1, retry_out, retry_count);
+                launches++;
+                CK(cudaEventRecord(ev[5], st));
+                CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+            }
             int nretry = *reinterpret_cast<int*>(h_counters + 2);
             if (nretry == 0) { c = 0; break; }
             if (nretry == c && round > 0) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
-            // reset pool + retry counter, keep cigar counter
-            CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
-            CK(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned long long), st));
             list = retry_out;
             retry_out = (retry_out == retry_a.p) ? retry_b.p : retry_a.p;
             c = nretry;

@@ -536,12 +536,42 @@ __device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, i
     return l;
 }
 
+// Reserves CIGAR words for one pair and writes soft clips + body (SswJniAligner.java:52-59).
+__device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begin, int ref_end, int read_begin,
+                                        int read_end, int nbody, const uint8_t* dirp, int width_d, int band,
+                                        int readLen, int refLen, cudasw_result r, cudasw_result* __restrict__ res,
+                                        uint32_t* __restrict__ cig, unsigned long long cig_cap,
+                                        unsigned long long* __restrict__ cig_used) {
+    const int lead = read_begin != 0;
+    const int tail = (q - read_end - 1) != 0;
+    const int nops = nbody + lead + tail;
+    const unsigned long long coff = atomicAdd(cig_used, (unsigned long long)nops);
+    r.score = score;
+    r.ref_begin = ref_begin;
+    r.ref_end = ref_end;
+    r.read_begin = read_begin;
+    r.read_end = read_end;
+    r.cigar_len = nops;
+    r.cigar_off = (int32_t)coff;
+    if (coff + (unsigned long long)nops <= cig_cap && coff < 0x7fffffffull) {
+        uint32_t* o = cig + coff;
+        if (lead) *o++ = ((uint32_t)read_begin << 4) | CUDASW_CIGAR_S;
+        if (score <= 0) *o = (1u << 4) | CUDASW_CIGAR_M;
+        else tb_walk(dirp, width_d, band, readLen, refLen, o, nbody);
+        if (tail) o[nbody] = ((uint32_t)(q - read_end - 1) << 4) | CUDASW_CIGAR_S;
+    } else {
+        r.status = CUDASW_ENOMEM;
+    }
+    res[pair] = r;
+}
+
 __global__ void __launch_bounds__(128)
 sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* __restrict__ fwd,
                     const int4* __restrict__ rev, TbConst tc, TbPool pool,
                     cudasw_result* __restrict__ res, uint32_t* __restrict__ cig,
                     unsigned long long cig_cap, unsigned long long* __restrict__ cig_used,
-                    int* __restrict__ retry_list, int* __restrict__ retry_count) {
+                    int* __restrict__ retry_list, int* __restrict__ retry_count,
+                    long long wide_cells, int* __restrict__ wide_list, int* __restrict__ wide_count) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= n) return;
     const int pair = list ? list[tid] : tid;
@@ -551,7 +581,7 @@ sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* 
     const int4 f = fwd[pair];
     const int score = f.x;
 
-    int nbody = 0, lead = 0, tail = 0;
+    int nbody = 0;
     int ref_begin = -1, read_begin = 0, ref_end = f.y, read_end = f.z;
     const uint8_t* dirp = nullptr;
     int width_d = 0, band = 0, readLen = 0, refLen = 0;
@@ -571,6 +601,10 @@ sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* 
         const uint8_t* ref = io.enc_ref + io.ref_off[pair] + ref_begin;
         const uint8_t* read = io.enc_seq + io.seq_off[pair] + read_begin;
         band = abs(refLen - readLen) + 1;
+        if ((long long)readLen * (2 * band + 1) > wide_cells) {  // long or wide-band pair: one warp each (tb_warp.cuh)
+            wide_list[atomicAdd(wide_count, 1)] = pair;
+            return;
+        }
         int mx = 0;
         for (;;) {
             width_d = 2 * band + 1;
@@ -629,29 +663,88 @@ sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* 
         nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0);
         if (nbody < 0) { res[pair].status = nbody; return; }
     }
-    lead = read_begin != 0;
-    tail = (q - read_end - 1) != 0;
-    const int nops = nbody + lead + tail;
-    const unsigned long long coff = atomicAdd(cig_used, (unsigned long long)nops);
-    r.score = score;
-    r.ref_begin = ref_begin;
-    r.ref_end = ref_end;
-    r.read_begin = read_begin;
-    r.read_end = read_end;
-    r.cigar_len = nops;
-    r.cigar_off = (int32_t)coff;
-    if (coff + (unsigned long long)nops <= cig_cap && coff < 0x7fffffffull) {
-        uint32_t* o = cig + coff;
-        if (lead) *o++ = ((uint32_t)read_begin << 4) | CUDASW_CIGAR_S;
-        if (score <= 0) *o = (1u << 4) | CUDASW_CIGAR_M;
-        else tb_walk(dirp, width_d, band, readLen, refLen, o, nbody);
-        if (tail) o[nbody] = ((uint32_t)(q - read_end - 1) << 4) | CUDASW_CIGAR_S;
-    } else {
-        r.status = CUDASW_ENOMEM;
-    }
-    res[pair] = r;
+    tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen, r,
+            res, cig, cig_cap, cig_used);
 }
 
 #endif  // CUSW_MAIN_TU
 
 }  // namespace cusw
+
+#ifdef CUSW_MAIN_TU
+#include "tb_warp.cuh"
+namespace cusw {
+
+// One warp per pair of `list` (the pairs sw_traceback_kernel handed over): banded DP by tb_dp_warp, then lane 0
+// walks the direction matrix and emits the CIGAR exactly like the one-thread kernel.
+__global__ void __launch_bounds__(128)
+sw_traceback_warp_kernel(const int* __restrict__ list, int n, PairIO io, const int4* __restrict__ fwd,
+                         const int4* __restrict__ rev, TbConst tc, TbPool pool, cudasw_result* __restrict__ res,
+                         uint32_t* __restrict__ cig, unsigned long long cig_cap,
+                         unsigned long long* __restrict__ cig_used, int* __restrict__ retry_list,
+                         int* __restrict__ retry_count) {
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (wid >= n) return;
+    const int pair = list[wid];
+    const cudasw_result r = res[pair];
+    if (r.status != CUDASW_OK) return;
+    const int q = (int)(io.seq_off[pair + 1] - io.seq_off[pair]);
+    const int4 f = fwd[pair];
+    const int4 rv = rev[pair];
+    const int score = f.x;
+    const int ref_end = f.y, read_end = f.z;
+    const int ref_begin = ref_end - rv.y, read_begin = read_end - rv.z;
+    const int refLen = ref_end - ref_begin + 1, readLen = read_end - read_begin + 1;
+    const uint8_t* ref = io.enc_ref + io.ref_off[pair] + ref_begin;
+    const uint8_t* read = io.enc_seq + io.seq_off[pair] + read_begin;
+    int band = abs(refLen - readLen) + 1;
+    int mx = 0, width_d = 0;
+    const uint8_t* dirp = nullptr;
+    for (;;) {
+        width_d = 2 * band + 1;
+        const long long ndir = (long long)width_d * readLen;
+        int status = CUDASW_OK;
+        const int nd = (width_d + 31) / 32;
+        const unsigned long long row_bytes = nd > 16 ? (((unsigned long long)width_d * 8ull + 15ull) & ~15ull) : 0ull;
+        const unsigned long long need = row_bytes + (((unsigned long long)ndir + 15ull) & ~15ull);
+        unsigned long long off = 0;
+        if (ndir * 3 >= (1ll << 31) || need > pool.cap) status = CUDASW_ETOOLARGE;
+        else {
+            if (lane == 0) off = atomicAdd(pool.used, need);
+            off = __shfl_sync(0xffffffffu, off, 0);
+            if (off + need > pool.cap) status = 1;  // scratch exhausted: try again in the next round
+        }
+        if (status != CUDASW_OK) {
+            if (lane == 0) {
+                if (status == 1) retry_list[atomicAdd(retry_count, 1)] = pair;
+                else res[pair].status = status;
+            }
+            return;
+        }
+        int2* row = reinterpret_cast<int2*>(pool.base + off);
+        uint8_t* dir = pool.base + off + row_bytes;
+        dirp = dir;
+        int m;
+        if (nd <= 1) m = tb_dp_warp<1>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        else if (nd <= 2) m = tb_dp_warp<2>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        else if (nd <= 4) m = tb_dp_warp<4>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        else if (nd <= 8) m = tb_dp_warp<8>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        else if (nd <= 16) m = tb_dp_warp<16>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        else m = tb_dp_warp<0>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        mx = max(mx, m);  // the reference never resets its running maximum between band widths
+        if (mx >= score) break;
+        band *= 2;
+    }
+    __syncwarp();  // every lane's direction bytes are visible to lane 0
+    if (lane == 0) {
+        const int nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0);
+        if (nbody < 0) { res[pair].status = nbody; return; }
+        tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen,
+                r, res, cig, cig_cap, cig_used);
+    }
+}
+
+}  // namespace cusw
+#endif  // CUSW_MAIN_TU
+

@@ -220,3 +220,36 @@ def test_chunked_pipeline_matches_oracle(aligner, oracle, synth, monkeypatch):
     for f in ("score", "ref_begin", "ref_end", "read_begin", "read_end", "cigar_len", "status"):
         assert np.array_equal(res[f], res2[f])
     assert all(_cig(res, cig, i) == _cig(res2, cig2, i) for i in range(len(res)))
+
+
+@pytest.mark.parametrize("kind", ["random", "mutated", "two_letter", "homopolymer", "dinuc", "tandem", "subst_block",
+                                  "with_n", "zero", "tiny", "q_gt_w", "indel_heavy"])
+def test_warp_traceback_forced(aligner, oracle, synth, kind, monkeypatch):
+    """every pair through the warp-cooperative traceback kernel (normally only long / wide-band pairs take it)"""
+    monkeypatch.setenv("CUDASW_TB_WIDE_CELLS", "0")
+    for seed, qmax, wmax in ((5, 120, 300), (6, 700, 1500)):
+        seqs, refs = synth.adversarial(kind, 800, seed=seed, qmax=qmax, wmax=wmax)
+        bad, undef = _compare(aligner, oracle, seqs, refs)
+        assert bad == [], bad[:5]
+        assert undef == 0
+
+
+def test_warp_traceback_wide_bands(aligner, oracle, monkeypatch):
+    """long indels force band doubling up to the memory-backed state (more than 16 diagonals per lane)"""
+    monkeypatch.setenv("CUDASW_TB_WIDE_CELLS", "0")
+    rng = np.random.default_rng(21)
+    seqs, refs = [], []
+    for gap in (40, 90, 200, 300, 450, 700):
+        for kind in ("del", "ins"):
+            a = rng.choice(list(b"ACGT"), size=400).astype(np.uint8).tobytes()
+            b = rng.choice(list(b"ACGT"), size=400).astype(np.uint8).tobytes()
+            g = rng.choice(list(b"ACGT"), size=gap).astype(np.uint8).tobytes()
+            flank = rng.choice(list(b"ACGT"), size=100).astype(np.uint8).tobytes()
+            if kind == "del":   # reference has extra bases
+                seqs.append(a + b)
+                refs.append(flank + a + g + b + flank)
+            else:               # query has extra bases
+                seqs.append(a + g + b)
+                refs.append(flank + a + b + flank)
+    bad, undef = _compare(aligner, oracle, seqs, refs)
+    assert bad == [] and undef == 0, bad[:3]

@@ -58,6 +58,16 @@ def generate(cfg: int, n: int, first: int = 0, seed: int | None = None, threads:
 # ---------------------------------------------------------------------------------------------
 # adversarial sets (SURVEY.md §8c "Volume parity plan"): python, small
 # ---------------------------------------------------------------------------------------------
+def lengths(cfg: int, n: int, first: int = 0, seed: int | None = None):
+    """-> (seq_off i64[n+1], ref_off i64[n+1]) without generating the bases (to size pinned buffers)."""
+    lib = _get()
+    seed = SEEDS[cfg] if seed is None else seed
+    so = np.zeros(n + 1, dtype=np.int64)
+    ro = np.zeros(n + 1, dtype=np.int64)
+    lib.synth_lengths(cfg, seed, first, n, so.ctypes.data, ro.ctypes.data)
+    return so, ro
+
+
 def _rand(rng, n, alphabet=b"ACGT"):
     return bytes(rng.choice(np.frombuffer(alphabet, dtype=np.uint8), size=n).tolist())
 
