@@ -373,38 +373,46 @@ int cudasw::finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, in
     CK(cudaEventRecord(ev[4], st));
 
     // ---- traceback (+ retry rounds when the scratch pool runs out); the CIGAR counter [1] runs on across rounds.
-    // Short narrow-band pairs: one thread each; long / wide-band pairs are handed to the warp-cooperative kernel.
+    // Pairs are sorted by estimated banded cells: the widest go to the warp-cooperative kernel (one warp each, on
+    // an auxiliary stream), the rest to the one-thread-per-pair kernel in descending cost order.
     {
-        long long wide_cells = 4096;
+        long long wide_cells = 2048;  // measured on B200: profiles/tb_sweep_r01.txt
         if (const char* e = getenv("CUDASW_TB_WIDE_CELLS")) wide_cells = atoll(e);
         TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
         int* retry_count = reinterpret_cast<int*>(d_counters + 2);
         int* wide_count = reinterpret_cast<int*>(d_counters + 3);
-        int* wide_list = reinterpret_cast<int*>(keys.p);  // the sort buffers are free by now
-        const int* list = vals_alt.p;                      // first round: every pair (sorted order of the reverse pass)
+        const int* list = nullptr;  // first round: every pair
         int c = (int)n;
         int* retry_out = retry_a.p;
         for (int round = 0; round < 64 && c > 0; round++) {
             CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));      // pool
             CK(cudaMemsetAsync(d_counters + 2, 0, 2 * sizeof(unsigned long long), st));  // retry + wide counters
-            sw_traceback_kernel<<<(c + 127) / 128, 128, 0, st>>>(list, c, io, fwd_c, rev_c, tc, pool, res_c,
-                                                                cig.p, (unsigned long long)cigar_cap,
-                                                                d_counters + 1, retry_out, retry_count,
-                                                                wide_cells, wide_list, wide_count);
+            tb_keys_kernel<<<(c + 255) / 256, 256, 0, st>>>(list, c, fwd_c, rev_c, res_c, wide_cells, keys.p, vals.p, wide_count);
             launches++;
-            CK(cudaEventRecord(ev[5], st));
+            CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, c, 0, 22, st));
+            launches += 3;
             CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
             const int nwide = *reinterpret_cast<int*>(h_counters + 3);
             if (nwide > 0) {
-                sw_traceback_warp_kernel<<<(nwide + 3) / 4, 128, 0, st>>>(wide_list, nwide, io, fwd_c, rev_c, tc, pool,
-                                                                          res_c, cig.p, (unsigned long long)cigar_cap,
-                                                                          d_counters + 1, retry_out, retry_count);
+                CK(cudaEventRecord(fork_ev, st));
+                CK(cudaStreamWaitEvent(aux[0], fork_ev, 0));
+                sw_traceback_warp_kernel<<<(nwide + 3) / 4, 128, 0, aux[0]>>>(vals_alt.p, nwide, io, fwd_c, rev_c, tc, pool,
+                                                                              res_c, cig.p, (unsigned long long)cigar_cap,
+                                                                              d_counters + 1, retry_out, retry_count);
                 launches++;
-                CK(cudaEventRecord(ev[5], st));
-                CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-                CK(cudaStreamSynchronize(st));
+                CK(cudaEventRecord(join_ev[0], aux[0]));
             }
+            if (c > nwide) {
+                sw_traceback_kernel<<<(c - nwide + 127) / 128, 128, 0, st>>>(vals_alt.p + nwide, c - nwide, io, fwd_c, rev_c, tc,
+                                                                            pool, res_c, cig.p, (unsigned long long)cigar_cap,
+                                                                            d_counters + 1, retry_out, retry_count);
+                launches++;
+            }
+            if (nwide > 0) CK(cudaStreamWaitEvent(st, join_ev[0], 0));
+            CK(cudaEventRecord(ev[5], st));
+            CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
             int nretry = *reinterpret_cast<int*>(h_counters + 2);
             if (nretry == 0) { c = 0; break; }
             if (nretry == c && round > 0) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }

@@ -536,6 +536,30 @@ __device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, i
     return l;
 }
 
+// Sort keys for the traceback: estimated banded cells readLen * (2*band0 + 1), descending, so that the threads
+// of a warp get pairs of similar cost and the long ones start first; counts the pairs handed to the warp kernel.
+constexpr uint32_t kTbKeyMax = (1u << 22) - 1u;
+__global__ void tb_keys_kernel(const int* __restrict__ list, int n, const int4* __restrict__ fwd,
+                               const int4* __restrict__ rev, const cudasw_result* __restrict__ res,
+                               long long wide_cells, uint32_t* __restrict__ keys, int* __restrict__ vals,
+                               int* __restrict__ wide_count) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= n) return;
+    const int pair = list ? list[tid] : tid;
+    long long cost = 0;
+    if (res[pair].status == CUDASW_OK && fwd[pair].x > 0) {
+        const int4 rv = rev[pair];
+        const int refLen = rv.y + 1, readLen = rv.z + 1;
+        cost = (long long)readLen * (2 * (abs(refLen - readLen) + 1) + 1);
+        if (cost > wide_cells) atomicAdd(wide_count, 1);
+        else if (cost > (long long)kTbKeyMax - 1) cost = kTbKeyMax - 1;  // below every warp-kernel pair
+    }
+    // warp-kernel pairs sort first (key 0 side), then by descending cost
+    uint32_t k = cost > wide_cells ? 0u : kTbKeyMax - (uint32_t)cost;
+    keys[tid] = k;
+    vals[tid] = pair;
+}
+
 // Reserves CIGAR words for one pair and writes soft clips + body (SswJniAligner.java:52-59).
 __device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begin, int ref_end, int read_begin,
                                         int read_end, int nbody, const uint8_t* dirp, int width_d, int band,
@@ -570,8 +594,7 @@ sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* 
                     const int4* __restrict__ rev, TbConst tc, TbPool pool,
                     cudasw_result* __restrict__ res, uint32_t* __restrict__ cig,
                     unsigned long long cig_cap, unsigned long long* __restrict__ cig_used,
-                    int* __restrict__ retry_list, int* __restrict__ retry_count,
-                    long long wide_cells, int* __restrict__ wide_list, int* __restrict__ wide_count) {
+                    int* __restrict__ retry_list, int* __restrict__ retry_count) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= n) return;
     const int pair = list ? list[tid] : tid;
@@ -601,10 +624,6 @@ sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* 
         const uint8_t* ref = io.enc_ref + io.ref_off[pair] + ref_begin;
         const uint8_t* read = io.enc_seq + io.seq_off[pair] + read_begin;
         band = abs(refLen - readLen) + 1;
-        if ((long long)readLen * (2 * band + 1) > wide_cells) {  // long or wide-band pair: one warp each (tb_warp.cuh)
-            wide_list[atomicAdd(wide_count, 1)] = pair;
-            return;
-        }
         int mx = 0;
         for (;;) {
             width_d = 2 * band + 1;
