@@ -197,18 +197,22 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     h->sc.poolA = b(sc.match) | (b(sc.mismatch) << 8) | (b(sc.mismatch) << 16) | (b(sc.mismatch) << 24);
     h->sc.poolB = b(sc.ambiguous) * 0x01010101u;
     h->sc.B = sc.gap_open;
-    {
-        uint32_t pool[2] = {h->sc.poolA, h->sc.poolB};
-        if ((e = cudaMalloc(&h->d_pool, sizeof pool)) != cudaSuccess) return fail(cudaGetErrorString(e));
-        if ((e = cudaMemcpy(h->d_pool, pool, sizeof pool, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(cudaGetErrorString(e));
-        h->sc.pool_dev = h->d_pool;
-    }
     h->sc.BB = pack2(sc.gap_open);
     h->sc.GO2 = pack2(sc.gap_open);
     h->sc.GOBB = pack2(2 * sc.gap_open);
     h->sc.NGE2 = pack2(-sc.gap_extend);
     h->sc.ge = sc.gap_extend;
     h->sc.match = sc.match;
+    {
+        uint32_t pool[32 * 8];
+        for (int l = 0; l < 32; l++) {
+            const uint32_t one[8] = {h->sc.poolA, h->sc.poolB, h->sc.BB, h->sc.GO2, h->sc.NGE2, h->sc.GOBB, 0u, 0u};
+            memcpy(pool + 8 * l, one, sizeof one);
+        }
+        if ((e = cudaMalloc(&h->d_pool, sizeof pool)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        if ((e = cudaMemcpy(h->d_pool, pool, sizeof pool, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        h->sc.pool_dev = h->d_pool;
+    }
     h->tc = TbConst{sc.match, sc.mismatch, sc.ambiguous, sc.gap_open, sc.gap_extend};
     if (g_nvar > 100) { cudasw_destroy(h); g_create_error = "too many variants"; return CUDASW_EINVAL; }
     h->vt.n = g_nvar;
@@ -219,6 +223,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     }
 
     // self-test, like AlignerFactory's "A" vs "A" probe (AlignerFactory.java:74-84)
+#ifndef CUSW_EXPERIMENT_NO_SELFTEST
     {
         const uint8_t a[1] = {'A'};
         const int64_t off[2] = {0, 1};
@@ -233,6 +238,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
             return CUDASW_ECUDA;
         }
     }
+#endif
     *out = h;
     return CUDASW_OK;
 }

@@ -73,7 +73,7 @@ struct ScoreConst {
     uint32_t NGE2;          // -gap_extend in both halves (two's complement per half)
     int32_t B;      // = gap_open
     int32_t ge, match;
-    const uint32_t* pool_dev;  // {poolA, poolB} in device memory (same values)
+    const uint32_t* pool_dev;  // 32 x {poolA, poolB, BB, GO2, NGE2, GOBB, 0, 0} in device memory (same values, one copy per lane)
 };
 
 struct PairIO {
@@ -186,6 +186,19 @@ struct StripPool {
     unsigned long long* used;
 };
 
+// Row (per half) of the first H equal to `target` = number of rows whose running prefix maximum is still below
+// it. Requires target >= every H[k] per half, so the plain 32-bit subtract is exact in both halves.
+template <int R>
+__device__ __forceinline__ uint32_t first_row_of(const uint32_t (&H)[R], uint32_t target, uint32_t floor2) {
+    uint32_t pm = floor2, cnt = 0u;
+#pragma unroll
+    for (int k = 0; k < R; k++) {
+        pm = __vmaxs2(pm, H[k]);
+        cnt += __vminu2(target - pm, 0x00010001u);
+    }
+    return cnt;
+}
+
 template <int G, int R, bool REV, bool MULTI>
 __global__ void __launch_bounds__(128)
 sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4* __restrict__ fwd,
@@ -228,10 +241,14 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     constexpr int STEP = REV ? -1 : 1;
     // the PRMT pool lives in ordinary per-thread registers: read through a volatile load so that ptxas neither
     // keeps it in uniform registers nor re-materialises a copy in front of every PRMT of the row loops
-    uint32_t cPA, cPB;
-    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(cPA) : "l"(sc.pool_dev));
-    asm volatile("ld.volatile.global.u32 %0, [%1+4];" : "=r"(cPB) : "l"(sc.pool_dev));
-    const uint32_t cBB = sc.BB, cGO2 = sc.GO2, cNGE2 = sc.NGE2;
+    uint32_t cPA, cPB, cBB, cGO2, cNGE2, cGOBB;
+    const uint32_t* cptr = sc.pool_dev + 8 * (threadIdx.x & 31);  // one copy per lane: ptxas cannot prove uniformity
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(cPA) : "l"(cptr));
+    asm volatile("ld.volatile.global.u32 %0, [%1+4];" : "=r"(cPB) : "l"(cptr));
+    asm volatile("ld.volatile.global.u32 %0, [%1+8];" : "=r"(cBB) : "l"(cptr));
+    asm volatile("ld.volatile.global.u32 %0, [%1+12];" : "=r"(cGO2) : "l"(cptr));
+    asm volatile("ld.volatile.global.u32 %0, [%1+16];" : "=r"(cNGE2) : "l"(cptr));
+    asm volatile("ld.volatile.global.u32 %0, [%1+20];" : "=r"(cGOBB) : "l"(cptr));
 
     // strip-mining state
     int nstrips = 1;
@@ -278,6 +295,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 
     uint32_t best = sc.BB;
     int col_lo = -1, col_hi = -1, row_lo = 0, row_hi = 0;
+    bool pend_lo = false, pend_hi = false;  // column recorded, row search still owed
     uint32_t Hout = sc.BB, Fout = 0u, Hdiag_top = sc.BB, Emax = 0u;
     uint32_t Rsel = kWindowPad | (kWindowPad << 8);
 
@@ -342,7 +360,11 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
                 uint32_t diag = diag0;
 #pragma unroll
                 for (int k = 0; k < R; k++) {
+#ifdef CUSW_EXP_PROFILE
+                    const uint32_t s = prmt(Q[k], QB[k], Rsel);
+#else
                     const uint32_t s = prmt(cPA, cPB, Q[k] ^ Rsel);
+#endif
                     const uint32_t h = __viaddmax_s16x2(diag, s, cBB);
                     diag = Ho[k];
                     Hn[k] = h;
@@ -350,7 +372,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
                 }
                 if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
                 // verified after the fact: had any h exceeded gap_open, the step is redone in full from Ho
-                quiet = __all_sync(0xffffffffu, __vmaxs2(cm, sc.GOBB) == sc.GOBB);
+                quiet = __all_sync(0xffffffffu, __vmaxs2(cm, cGOBB) == cGOBB);
             }
         }
         if (!quiet) {
@@ -382,23 +404,24 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             if (write_bot && (unsigned)(c - 1) < (unsigned)w) bnd_out[c - 1] = (Hout >> 16) | (Fout & 0xFFFF0000u);
         }
 
-        // ---- running best with strict improvement
+        // ---- running best with strict improvement (ssw.c:283-306: first column that raises the maximum, then
+        // the smallest row holding it). The column is recorded at once; the row search is deferred until the
+        // half stops improving (along an alignment the maximum rises every step): the column that last raised
+        // it is then still intact in Ho, the other ping-pong array.
         // (not __vibmax_s16x2: its header asm lets the output alias input `a`, which turns both
         //  predicates into constants when best is updated in place)
         const uint32_t nb = __vmaxs2(best, cm);
-        if (nb != best) {
-            // first row of each half whose H equals the new maximum = number of rows whose running
-            // prefix maximum is still below it; both halves at once
-            uint32_t pm = cBB, cnt = 0u;
-#pragma unroll
-            for (int k = 0; k < R; k++) {
-                pm = __vmaxs2(pm, Hn[k]);
-                cnt += __vminu2(nb - pm, 0x00010001u);  // nb >= pm per half: plain subtract is exact
-            }
-            const uint32_t changed = nb ^ best;
-            if (changed & 0xFFFFu) { col_lo = c; row_lo = (int)(cnt & 0xFFFFu); }
-            if (changed >> 16) { col_hi = c - 1; row_hi = (int)(cnt >> 16); }
+        const uint32_t changed = nb ^ best;
+        const bool imp_lo = (changed & 0xFFFFu) != 0u, imp_hi = (changed >> 16) != 0u;
+        if ((pend_lo && !imp_lo) || (pend_hi && !imp_hi)) {
+            const uint32_t cnt = first_row_of(Ho, best, cBB);
+            if (pend_lo && !imp_lo) row_lo = (int)(cnt & 0xFFFFu);
+            if (pend_hi && !imp_hi) row_hi = (int)(cnt >> 16);
         }
+        if (imp_lo) col_lo = c;
+        if (imp_hi) col_hi = c - 1;
+        pend_lo = imp_lo;
+        pend_hi = imp_hi;
         best = nb;
         ++c;
     };
@@ -420,6 +443,12 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
                 t_end_warp = (__reduce_max_sync(0xffffffffu, t_end) + 1) & ~1;
             }
         }
+    }
+
+    if (pend_lo || pend_hi) {  // the last step wrote HA
+        const uint32_t cnt = first_row_of(HA, best, cBB);
+        if (pend_lo) row_lo = (int)(cnt & 0xFFFFu);
+        if (pend_hi) row_hi = (int)(cnt >> 16);
     }
 
     // ---- fold this strip's virtual lanes into the running key: max score, then min column, then min row

@@ -4,6 +4,7 @@
 //   2: same as 1 but the two adds written as plain C (compiler chooses the pipe)
 //   3: no score op at all (DPX floor of the recurrence)
 //   4: mode 1 without the column-max op (shows what the running maximum costs)
+//   5: query profile in registers: s = PRMT(QA[k], QB[k], step selector), no LOP3 (two registers per row)
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -21,12 +22,13 @@ __device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c) {
 template <int MODE>
 __global__ void __launch_bounds__(128) cellmix(uint32_t* out, int iters, uint32_t pa, uint32_t pb, uint32_t bb,
                                                uint32_t go2, uint32_t nge2, uint32_t amb2, uint32_t one, const uint32_t* rtab) {
-    uint32_t H[R], E[R], Q[R];
+    uint32_t H[R], E[R], Q[R], QB[MODE == 5 ? R : 1];
 #pragma unroll
     for (int k = 0; k < R; k++) {
         H[k] = bb; E[k] = 0;
         int q = (int)(rtab[1024 + ((threadIdx.x * R + k) & 1023)]);  // opaque to the compiler
         Q[k] = MODE == 0 ? q * 0x11 * 0x0101u : q * 0x0101u;
+        if (MODE == 5) { Q[k] = rtab[(threadIdx.x * 7 + k) & 1023] * 0x01010101u + q; QB[k] = rtab[(threadIdx.x * 5 + k * 3) & 1023] ^ (q << 8); }
     }
     uint32_t F = 0, cm = bb, diag = bb, best = bb;
     int col = 0;
@@ -39,6 +41,7 @@ __global__ void __launch_bounds__(128) cellmix(uint32_t* out, int iters, uint32_
             if (MODE == 0) s = prmt(pa, pb, Q[k] ^ r0);
             else if (MODE == 1 || MODE == 4) s = prmt(pa, pb, imad(Q[k], one, r0));
             else if (MODE == 2) s = prmt(pa, pb, Q[k] + r0);
+            else if (MODE == 5) s = prmt(Q[k], QB[k], r0);
             else s = Q[k];
             uint32_t m = __vimax3_s16x2(E[k], F, bb);
             uint32_t h = __viaddmax_s16x2(diag, s, m);
@@ -73,8 +76,8 @@ int main() {
     uint32_t *rx, *ra; cudaMalloc(&rx, 8192); cudaMalloc(&ra, 8192);
     cudaMemcpy(rx, h_x, 8192, cudaMemcpyHostToDevice); cudaMemcpy(ra, h_a, 8192, cudaMemcpyHostToDevice);
     int iters = 20000;
-    const char* names[5] = {"LOP3+PRMT", "IMAD+PRMT+IMAD bias", "add+PRMT+add (compiler)", "no score op (DPX floor)", "IMAD+PRMT, no colmax"};
-    for (int mode = 0; mode < 5; mode++) {
+    const char* names[6] = {"LOP3+PRMT", "IMAD+PRMT+IMAD bias", "add+PRMT+add (compiler)", "no score op (DPX floor)", "IMAD+PRMT, no colmax", "profile PRMT (no LOP3)"};
+    for (int mode = 0; mode < 6; mode++) {
         cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
         auto launch = [&](int it) {
             const uint32_t bb = 0x00060006u, go2 = 0x00060006u, nge2 = 0xffffffffu, amb2 = 0xfffcfffcu;
@@ -82,6 +85,7 @@ int main() {
             if (mode == 1) cellmix<1><<<sms * 16, 128>>>(out, it, 0x05000000u, 0u, bb, go2, nge2, amb2, 1, ra);
             if (mode == 2) cellmix<2><<<sms * 16, 128>>>(out, it, 0x05000000u, 0u, bb, go2, nge2, amb2, 1, ra);
             if (mode == 3) cellmix<3><<<sms * 16, 128>>>(out, it, 0x05000000u, 0u, bb, go2, nge2, amb2, 1, ra);
+            if (mode == 5) cellmix<5><<<sms * 16, 128>>>(out, it, 0x05000000u, 0u, bb, go2, nge2, amb2, 1, rx);
             if (mode == 4) cellmix<4><<<sms * 16, 128>>>(out, it, 0x05000000u, 0u, bb, go2, nge2, amb2, 1, ra);
         };
         launch(100); cudaDeviceSynchronize();
