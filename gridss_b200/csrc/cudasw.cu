@@ -90,8 +90,9 @@ struct cudasw {
     DevBuf<cudasw_result> res;
     DevBuf<uint32_t> cig;
     DevBuf<uint8_t> cub_tmp;
+    DevBuf<uint8_t> wflags;  // per pair: window contains N (xor-selector flavour)
     DevBuf<uint8_t> tb_pool;
-    int* d_hist = nullptr;  // 128 ints
+    int* d_hist = nullptr;  // 256 ints: pairs per (flavour, variant) slot
     uint32_t* d_pool = nullptr;  // {poolA, poolB}
     unsigned long long* d_counters = nullptr;  // [0] pool used, [1] cigar used, [2] retry count(int)
     int* h_hist = nullptr;                     // pinned
@@ -185,10 +186,10 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     if ((e = cudaEventCreateWithFlags(&h->fork_ev, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
     for (auto& j : h->join_ev)
         if ((e = cudaEventCreateWithFlags(&j, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
-    if ((e = cudaMalloc(&h->d_hist, 128 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
-    if ((e = cudaMallocHost(&h->h_hist, 128 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMallocHost(&h->h_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMallocHost(&h->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
 
@@ -204,17 +205,22 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     h->sc.ge = sc.gap_extend;
     h->sc.match = sc.match;
     {
-        uint32_t pool[32 * 8];
-        for (int l = 0; l < 32; l++) {
-            const uint32_t one[8] = {h->sc.poolA, h->sc.poolB, h->sc.BB, h->sc.GO2, h->sc.NGE2, h->sc.GOBB, 0u, 0u};
-            memcpy(pool + 8 * l, one, sizeof one);
+        // per lane: the packed constants, then the query profile words: byte x of profile[c] = score of query code c
+        // (A0 C1 G2 T3, N4, pads 5..7) against window base x (SswJniAligner.createMatrix, SswJniAligner.java:19-33)
+        uint32_t pool[32 * 16];
+        uint32_t one[16] = {h->sc.poolA, h->sc.poolB, h->sc.BB, h->sc.GO2, h->sc.NGE2, h->sc.GOBB, 0u, 0u};
+        for (int c = 0; c < 8; c++) {
+            uint32_t wd = 0;
+            for (int x = 0; x < 4; x++) wd |= b(c < 4 ? (c == x ? sc.match : sc.mismatch) : sc.ambiguous) << (8 * x);
+            one[8 + c] = wd;
         }
+        for (int l = 0; l < 32; l++) memcpy(pool + 16 * l, one, sizeof one);
         if ((e = cudaMalloc(&h->d_pool, sizeof pool)) != cudaSuccess) return fail(cudaGetErrorString(e));
         if ((e = cudaMemcpy(h->d_pool, pool, sizeof pool, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(cudaGetErrorString(e));
         h->sc.pool_dev = h->d_pool;
     }
     h->tc = TbConst{sc.match, sc.mismatch, sc.ambiguous, sc.gap_open, sc.gap_extend};
-    if (g_nvar > 100) { cudasw_destroy(h); g_create_error = "too many variants"; return CUDASW_EINVAL; }
+    if (2 * g_nvar + 1 > 127) { cudasw_destroy(h); g_create_error = "too many variants"; return CUDASW_EINVAL; }
     h->vt.n = g_nvar;
     h->vt.n_single = 0;
     for (int i = 0; i < g_nvar; i++) {
@@ -252,7 +258,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->seq_off.release(); h->ref_off.release(); h->keys.release(); h->keys_alt.release();
     h->vals.release(); h->vals_alt.release(); h->retry_a.release(); h->retry_b.release();
     h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
-    h->cub_tmp.release(); h->tb_pool.release();
+    h->cub_tmp.release(); h->tb_pool.release(); h->wflags.release();
     if (h->d_hist) cudaFree(h->d_hist);
     if (h->d_pool) cudaFree(h->d_pool);
     if (h->d_counters) cudaFree(h->d_counters);
@@ -275,22 +281,24 @@ int cudasw::launch_variants(bool reverse, const int* order, PairIO io, const int
                             uint64_t* launches) {
     cudaStream_t st = stream;
     int nonempty = 0;
-    for (int v = 0; v < g_nvar; v++) nonempty += h_hist[v] > 0;
+    for (int v = 0; v < 2 * g_nvar; v++) nonempty += h_hist[v] > 0;
     const bool spread = nonempty > 1;
     if (spread) CK(cudaEventRecord(fork_ev, st));
     bool used[kAux] = {};
     int64_t start = 0;
     int k = 0;
-    for (int v = 0; v < g_nvar; v++) {
-        const int c = h_hist[v];
+    for (int slot = 0; slot < 2 * g_nvar; slot++) {  // [0, nvar): query-profile flavour, [nvar, 2 nvar): xor-selector flavour
+        const int c = h_hist[slot];
         if (c > 0) {
+            const cusw::Variant& V = g_var[slot % g_nvar];
+            const bool xr = slot >= g_nvar;
             cudaStream_t s = st;
             if (spread) {
                 const int a = k++ % kAux;
                 s = aux[a];
                 if (!used[a]) { CK(cudaStreamWaitEvent(s, fork_ev, 0)); used[a] = true; }
             }
-            (reverse ? g_var[v].rev : g_var[v].fwd)(order + start, c, io, fwd_c, out_c, sc, spool, s);
+            (reverse ? (xr ? V.revx : V.rev) : (xr ? V.fwdx : V.fwd))(order + start, c, io, fwd_c, out_c, sc, spool, s);
             (*launches)++;
         }
         start += c;
@@ -311,18 +319,21 @@ int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, cons
     cudaStream_t st = stream;
     uint64_t launches = 0;
     const int64_t n = cnt;
+    int* any_n = reinterpret_cast<int*>(d_counters + 5);  // set by encode_kernel when a window holds an N
     CK(cudaEventRecord(ev[1], st));
     // ---- encode + forward binning
     {
         const int64_t tq = q_hi - q_lo, tw = w_hi - w_lo;
         int64_t thr = (tq + 15) / 16;
         int blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
-        if (tq > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u); launches++; }
+        if (tq > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u, nullptr); launches++; }
         thr = (tw + 15) / 16;
         blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
-        if (tw > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u); launches++; }
+        if (tw > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u, any_n); launches++; }
     }
     PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
+    window_flags_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, enc_ref.p, io.ref_off, any_n, wflags.p + first);
+    launches++;
     int4* fwd_c = fwd.p + first;
     cudasw_result* res_c = res.p + first;
     const bool have_multi = g_var[g_nvar - 1].multi;
@@ -330,13 +341,13 @@ int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, cons
                                   scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
     const int max_cols = (1 << 24) - 2;
     size_t cub_bytes = cub_tmp.cap;
-    CK(cudaMemsetAsync(d_hist, 0, 128 * sizeof(int), st));
+    CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
     fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
-                                                           keys.p, vals.p, d_hist, res_c);
+                                                           keys.p, vals.p, d_hist, res_c, any_n, wflags.p + first);
     launches++;
     CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
     launches += 3;
-    CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_hist, d_hist, 256 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(ev[2], st));
     CK(cudaStreamSynchronize(st));
 
@@ -367,12 +378,13 @@ int cudasw::finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, in
 
     // ---- reverse score pass
     CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
-    CK(cudaMemsetAsync(d_hist, 0, 128 * sizeof(int), st));
-    rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, vt, keys.p, vals.p, d_hist);
+    CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
+    rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, vt, keys.p, vals.p, d_hist,
+                                                           reinterpret_cast<int*>(d_counters + 5), wflags.p);
     launches++;
     CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
     launches += 3;
-    CK(cudaMemcpyAsync(h_hist, d_hist, 128 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_hist, d_hist, 256 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     { int rc = launch_variants(true, vals_alt.p, io, fwd_c, rev_c, spool, &launches); if (rc != CUDASW_OK) return rc; }
     CK(cudaGetLastError());
@@ -505,7 +517,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(enc_ref.ensure((size_t)total_w + 16));
     CK(keys.ensure(n)); CK(keys_alt.ensure(n)); CK(vals.ensure(n)); CK(vals_alt.ensure(n));
     CK(retry_a.ensure(n)); CK(retry_b.ensure(n));
-    CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n));
+    CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n)); CK(wflags.ensure(n));
     CK(cig.ensure((size_t)std::max<int64_t>(cigar_cap, 1)));
     {
         size_t cub_bytes = 0;

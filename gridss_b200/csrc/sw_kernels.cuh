@@ -36,7 +36,8 @@ __device__ __forceinline__ uint32_t base_code(uint32_t c) {
 // HBM-bound: 1 byte in, 1 byte out; 16-byte vector accesses.
 __global__ void __launch_bounds__(256) encode_kernel(const uint8_t* __restrict__ in,
                                                      uint8_t* __restrict__ out, int64_t n,
-                                                     uint32_t xor_mask) {
+                                                     uint32_t xor_mask, int* __restrict__ any_n) {
+    bool seen_n = false;
     int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x * 16;
     for (; i < n; i += stride) {
@@ -48,15 +49,39 @@ __global__ void __launch_bounds__(256) encode_kernel(const uint8_t* __restrict__
                 uint32_t r = 0;
 #pragma unroll
                 for (int b = 0; b < 4; b++)
-                    r |= ((base_code((wds[k] >> (8 * b)) & 0xFFu) * 0x11u) ^ xor_mask) << (8 * b);
+                {
+                    const uint32_t code = base_code((wds[k] >> (8 * b)) & 0xFFu);
+                    seen_n |= code == 4u;
+                    r |= ((code * 0x11u) ^ xor_mask) << (8 * b);
+                }
                 wds[k] = r;
             }
             *reinterpret_cast<uint4*>(out + i) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
         } else {
-            for (int64_t k = i; k < n && k < i + 16; k++)
-                out[k] = (uint8_t)((base_code(in[k]) * 0x11u) ^ xor_mask);
+            for (int64_t k = i; k < n && k < i + 16; k++) {
+                const uint32_t code = base_code(in[k]);
+                seen_n |= code == 4u;
+                out[k] = (uint8_t)((code * 0x11u) ^ xor_mask);
+            }
         }
     }
+    if (any_n && seen_n) *any_n = 1;  // some window of this batch holds an N: per-pair flags are needed
+}
+
+// Per-pair flag "the window contains N" (such pairs take the xor-selector flavour of the score kernel).
+// One warp per pair over the encoded window; does nothing unless encode_kernel saw an N at all.
+__global__ void __launch_bounds__(256) window_flags_kernel(int n, const uint8_t* __restrict__ enc_ref,
+                                                           const int64_t* __restrict__ ref_off,
+                                                           const int* __restrict__ any_n,
+                                                           uint8_t* __restrict__ flags) {
+    if (*any_n == 0) return;
+    const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (p >= n) return;
+    const int64_t b = ref_off[p], e = ref_off[p + 1];
+    bool seen = false;
+    for (int64_t i = b + (threadIdx.x & 31); i < e; i += 32) seen |= enc_ref[i] == ((4u * 0x11u) ^ 0x80u);
+    seen = __any_sync(0xffffffffu, seen);
+    if ((threadIdx.x & 31) == 0) flags[p] = seen ? 1 : 0;
 }
 
 #endif  // CUSW_MAIN_TU
@@ -73,7 +98,7 @@ struct ScoreConst {
     uint32_t NGE2;          // -gap_extend in both halves (two's complement per half)
     int32_t B;      // = gap_open
     int32_t ge, match;
-    const uint32_t* pool_dev;  // 32 x {poolA, poolB, BB, GO2, NGE2, GOBB, 0, 0} in device memory (same values, one copy per lane)
+    const uint32_t* pool_dev;  // 32 x {poolA, poolB, BB, GO2, NGE2, GOBB, 0, 0, profile[8]} in device memory (one copy per lane)
 };
 
 struct PairIO {
@@ -111,11 +136,12 @@ __host__ __device__ __forceinline__ int variant_of(const VariantTable& vt, int q
 }
 
 #ifdef CUSW_MAIN_TU
-// keys for the forward pass; hist[v] counts pairs per variant; slot vt.n counts invalid pairs
+// keys for the forward pass; hist[slot] counts pairs per (flavour, variant); the last slot counts invalid pairs
 __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
                                 const int64_t* __restrict__ ref_off, VariantTable vt, int max_rows,
                                 int max_cols, uint32_t* __restrict__ keys, int* __restrict__ vals,
-                                int* __restrict__ hist, cudasw_result* __restrict__ res) {
+                                int* __restrict__ hist, cudasw_result* __restrict__ res,
+                                const int* __restrict__ any_n, const uint8_t* __restrict__ wflags) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     int64_t q = seq_off[p + 1] - seq_off[p];
@@ -124,9 +150,10 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
     r.score = 0; r.ref_begin = -1; r.ref_end = -1; r.read_begin = 0; r.read_end = 0;
     r.cigar_off = 0; r.cigar_len = 0; r.status = CUDASW_OK;
     int v;
-    if (q <= 0 || w <= 0) { r.status = CUDASW_EINVAL; v = vt.n; }
-    else if (q > max_rows || w > max_cols) { r.status = CUDASW_ETOOLARGE; v = vt.n; }
-    else v = variant_of(vt, (int)q);
+    // slots [0, n): query-profile flavour, [n, 2n): xor-selector flavour, 2n: nothing to do
+    if (q <= 0 || w <= 0) { r.status = CUDASW_EINVAL; v = 2 * vt.n; }
+    else if (q > max_rows || w > max_cols) { r.status = CUDASW_ETOOLARGE; v = 2 * vt.n; }
+    else v = variant_of(vt, (int)q) + ((*any_n != 0 && wflags[p]) ? vt.n : 0);
     res[p] = r;
     uint32_t wq = (uint32_t)(w >> 4);
     if (wq > 0xFFFFFu) wq = 0xFFFFFu;  // 2^24 columns max / 16
@@ -139,16 +166,17 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
 __global__ void rev_keys_kernel(int n, const int4* __restrict__ fwd,
                                 cudasw_result* __restrict__ res, VariantTable vt,
                                 uint32_t* __restrict__ keys, int* __restrict__ vals,
-                                int* __restrict__ hist) {
+                                int* __restrict__ hist, const int* __restrict__ any_n,
+                                const uint8_t* __restrict__ wflags) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     int4 f = fwd[p];
     int v;
     uint32_t k2 = 0;
     if (res[p].status == CUDASW_OK && f.w != 0) res[p].status = CUDASW_ENOMEM;  // strip buffers exhausted
-    if (res[p].status != CUDASW_OK || f.x <= 0) v = vt.n;  // nothing to walk back
+    if (res[p].status != CUDASW_OK || f.x <= 0) v = 2 * vt.n;  // nothing to walk back
     else {
-        v = variant_of(vt, f.z + 1);
+        v = variant_of(vt, f.z + 1) + ((*any_n != 0 && wflags[p]) ? vt.n : 0);
         k2 = (uint32_t)min(f.y + 1, f.z + 1 + 64) >> 4;
         if (k2 > 0xFFFFFu) k2 = 0xFFFFFu;
     }
@@ -187,20 +215,32 @@ struct StripPool {
 };
 
 // Row (per half) of the first H equal to `target` = number of rows whose running prefix maximum is still below
-// it. Requires target >= every H[k] per half, so the plain 32-bit subtract is exact in both halves.
+// it. A half whose column is out of range may hold values above its target (they are never used): the prefix
+// maximum is clamped so that the packed subtract cannot borrow across halves.
 template <int R>
 __device__ __forceinline__ uint32_t first_row_of(const uint32_t (&H)[R], uint32_t target, uint32_t floor2) {
     uint32_t pm = floor2, cnt = 0u;
 #pragma unroll
     for (int k = 0; k < R; k++) {
-        pm = __vmaxs2(pm, H[k]);
+        pm = __vmins2(__vmaxs2(pm, H[k]), target);
         cnt += __vminu2(target - pm, 0x00010001u);
     }
     return cnt;
 }
 
-template <int G, int R, bool REV, bool MULTI>
-__global__ void __launch_bounds__(128)
+// PROF (query profile flavour, the default): every row keeps its four substitution scores against A, C, G, T for
+// both halves in two registers (QA: low virtual lane, QB: high one) and the window byte of the step is the PRMT
+// selector, so a cell pair needs ONE PRMT and no LOP3. Query N and pad rows are profile rows of `ambiguous`.
+// The window must be free of N (pairs whose window has one take the !PROF flavour, binned apart), and
+// out-of-range columns read as 'A': a half's state is reset when it reaches column 0 and its column maximum is
+// masked while it is outside [0, w), which is all a pad symbol was needed for.
+// Resident CTAs per SM the register allocation is tuned for: with the query profile a thread holds 5 registers
+// per row (HA, HB, E, QA, QB). Four CTAs (128 registers) measured 6.04 vs 5.63 TCUPS for three (R = 19, B200).
+template <int R, bool PROF>
+constexpr int score_min_blocks() { return (PROF ? 5 : 4) * R + 32 <= 128 ? 4 : (PROF ? 5 : 4) * R + 32 <= 168 ? 3 : 2; }
+
+template <int G, int R, bool REV, bool MULTI, bool PROF>
+__global__ void __launch_bounds__(128, score_min_blocks<R, PROF>())
 sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4* __restrict__ fwd,
                 int4* __restrict__ out, ScoreConst sc, StripPool sp) {
     static_assert(!MULTI || G == 32, "strip mining uses one warp per pair");
@@ -242,7 +282,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     // the PRMT pool lives in ordinary per-thread registers: read through a volatile load so that ptxas neither
     // keeps it in uniform registers nor re-materialises a copy in front of every PRMT of the row loops
     uint32_t cPA, cPB, cBB, cGO2, cNGE2, cGOBB;
-    const uint32_t* cptr = sc.pool_dev + 8 * (threadIdx.x & 31);  // one copy per lane: ptxas cannot prove uniformity
+    const uint32_t* cptr = sc.pool_dev + 16 * (threadIdx.x & 31);  // one copy per lane: ptxas cannot prove uniformity
     asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(cPA) : "l"(cptr));
     asm volatile("ld.volatile.global.u32 %0, [%1+4];" : "=r"(cPB) : "l"(cptr));
     asm volatile("ld.volatile.global.u32 %0, [%1+8];" : "=r"(cBB) : "l"(cptr));
@@ -274,8 +314,9 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     for (int strip = 0; strip < (MULTI ? nstrips : 1); ++strip) {
     const int row0 = strip * S;
 
-    // query rows -> PRMT selector halves (low byte: low virtual lane, high byte: high one)
-    uint32_t Q[R];
+    // query rows -> PRMT selector halves (low byte: low virtual lane, high byte: high one), or (PROF) the
+    // rows' profile words: byte x = substitution score of the row's base against window base x
+    uint32_t Q[R], QB[PROF ? R : 1];
     {
         const int r0 = row0 + (2 * lig) * R;
 #pragma unroll
@@ -283,7 +324,12 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             int a = r0 + k, b = r0 + R + k;
             uint32_t qa = a < q ? (uint32_t)qptr[(int64_t)a * STEP] : kQueryPad;
             uint32_t qb = b < q ? (uint32_t)qptr[(int64_t)b * STEP] : kQueryPad;
-            Q[k] = qa | (qb << 8);
+            if (PROF) {
+                Q[k] = cptr[8 + (qa & 7u)];
+                QB[k] = cptr[8 + (qb & 7u)];
+            } else {
+                Q[k] = qa | (qb << 8);
+            }
         }
     }
     // H ping-pongs between two register arrays (HA -> HB -> HA ...) so that `diag = old H[k]` needs no
@@ -297,14 +343,15 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     int col_lo = -1, col_hi = -1, row_lo = 0, row_hi = 0;
     bool pend_lo = false, pend_hi = false;  // column recorded, row search still owed
     uint32_t Hout = sc.BB, Fout = 0u, Hdiag_top = sc.BB, Emax = 0u;
-    uint32_t Rsel = kWindowPad | (kWindowPad << 8);
+    constexpr uint32_t kOut = PROF ? 0x80u : kWindowPad;  // PROF: 'A'; state reset / maximum mask take care of it
+    uint32_t Rsel = kOut | (kOut << 8);
 
     int t_end = active ? w + 2 * G - 1 : 0;
     int t_end_warp = (__reduce_max_sync(0xffffffffu, t_end) + 1) & ~1;
 
     // prefetch the window byte (and, when strip-mining, the boundary word) of step 0
     int c = -2 * lig;  // column of the low virtual lane at step t
-    uint32_t rb_next = ((unsigned)c < (unsigned)w) ? (uint32_t)rptr[(int64_t)c * STEP] : kWindowPad;
+    uint32_t rb_next = ((unsigned)c < (unsigned)w) ? (uint32_t)rptr[(int64_t)c * STEP] : kOut;
     uint32_t top_next = 0u;  // lane 0 only: (H | F << 16) of the row above this strip at column c
     const bool read_top = MULTI && strip > 0 && lig == 0;
     const bool write_bot = MULTI && strip + 1 < nstrips && lig == G - 1;
@@ -313,7 +360,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         if (read_top && (unsigned)c < (unsigned)w) top_next = bnd_in[c];
     }
 
-    auto step = [&](const uint32_t (&Ho)[R], uint32_t (&Hn)[R]) {
+    auto step = [&](uint32_t (&Ho)[R], uint32_t (&Hn)[R]) {
         // ---- inputs from the virtual lane above
         uint32_t rH = __shfl_up_sync(0xffffffffu, Hout, 1, G);
         uint32_t rF = __shfl_up_sync(0xffffffffu, Fout, 1, G);
@@ -329,7 +376,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         const uint32_t rb = rb_next;
         {
             int cn = c + 1;
-            rb_next = kWindowPad;
+            rb_next = kOut;
             if ((unsigned)cn < (unsigned)w) rb_next = (uint32_t)rptr[(int64_t)cn * STEP];
             if (MULTI) {
                 top_next = cBB & 0xFFFFu;
@@ -337,7 +384,22 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             }
         }
         Rsel = prmt(Rsel, rb, 0x3204u);  // byte1 <- old byte0, byte0 <- new
+        const uint32_t Rs = Rsel + 0x4400u;  // PROF: the high half indexes pool bytes 4..7 (QB)
 
+        if (PROF) {
+            // a half that enters column 0 now starts from the matrix border: whatever it computed over the
+            // out-of-range columns before (read as 'A') is discarded
+            if (c == 0 || c == 1) {
+                const uint32_t keep = c == 0 ? 0xFFFF0000u : 0x0000FFFFu;
+#pragma unroll
+                for (int k = 0; k < R; k++) {
+                    Ho[k] = (Ho[k] & keep) | (cBB & ~keep);
+                    E[k] &= keep;
+                }
+                Hdiag_top = (Hdiag_top & keep) | (cBB & ~keep);
+                Emax &= keep;
+            }
+        }
         const uint32_t diag0 = Hdiag_top;
         Hdiag_top = Hin;
         uint32_t cm = cBB;
@@ -360,11 +422,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
                 uint32_t diag = diag0;
 #pragma unroll
                 for (int k = 0; k < R; k++) {
-#ifdef CUSW_EXP_PROFILE
-                    const uint32_t s = prmt(Q[k], QB[k], Rsel);
-#else
-                    const uint32_t s = prmt(cPA, cPB, Q[k] ^ Rsel);
-#endif
+                    const uint32_t s = PROF ? prmt(Q[k], QB[PROF ? k : 0], Rs) : prmt(cPA, cPB, Q[k] ^ Rsel);
                     const uint32_t h = __viaddmax_s16x2(diag, s, cBB);
                     diag = Ho[k];
                     Hn[k] = h;
@@ -381,7 +439,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             F = Fin;
 #pragma unroll
             for (int k = 0; k < R; k++) {
-                const uint32_t s = prmt(cPA, cPB, Q[k] ^ Rsel);
+                const uint32_t s = PROF ? prmt(Q[k], QB[PROF ? k : 0], Rs) : prmt(cPA, cPB, Q[k] ^ Rsel);
                 const uint32_t m = __vimax3_s16x2(E[k], F, cBB);
                 const uint32_t h = __viaddmax_s16x2(diag, s, m);
                 diag = Ho[k];
@@ -404,6 +462,14 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             if (write_bot && (unsigned)(c - 1) < (unsigned)w) bnd_out[c - 1] = (Hout >> 16) | (Fout & 0xFFFF0000u);
         }
 
+        if (PROF) {
+            // columns outside [0, w) must never raise the maximum
+            const bool v_lo = (unsigned)c < (unsigned)w, v_hi = (unsigned)(c - 1) < (unsigned)w;
+            if (!(v_lo && v_hi)) {
+                const uint32_t keep = (v_lo ? 0x0000FFFFu : 0u) | (v_hi ? 0xFFFF0000u : 0u);
+                cm = (cm & keep) | (cBB & ~keep);
+            }
+        }
         // ---- running best with strict improvement (ssw.c:283-306: first column that raises the maximum, then
         // the smallest row holding it). The column is recorded at once; the row search is deferred until the
         // half stops improving (along an alignment the maximum rises every step): the column that last raised

@@ -14,7 +14,8 @@ typedef void (*score_launch_fn)(const int*, int, PairIO, const int4*, int4*, Sco
 struct Variant {
     int G, R, rows;  // rows = 2*G*R; for multi (strip-mined) variants rows per strip
     bool multi;
-    score_launch_fn fwd, rev;
+    score_launch_fn fwd, rev;    // query-profile flavour (window free of N)
+    score_launch_fn fwdx, revx;  // xor-selector flavour (any symbols)
 };
 
 // defined in score_variants.cu, one per -DSCORE_G
