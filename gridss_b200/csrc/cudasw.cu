@@ -90,6 +90,7 @@ struct cudasw {
     DevBuf<cudasw_result> res;
     DevBuf<uint32_t> cig;
     DevBuf<uint8_t> cub_tmp;
+    DevBuf<uint16_t> anchor;  // per pair: seed estimate of the alignment's first window column / 4 (scheduling hint)
     DevBuf<uint8_t> wflags;  // per pair: window contains N (xor-selector flavour)
     DevBuf<uint8_t> tb_pool;
     int* d_hist = nullptr;  // 256 ints: pairs per (flavour, variant) slot
@@ -166,6 +167,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
         return CUDASW_EINVAL;
     }
     std::call_once(g_var_once, [] { g_var = cusw::collect_variants(); g_nvar = (int)g_var.size(); });
+
     cudasw_t* h = new cudasw();
     h->device = device;
     h->scoring = sc;
@@ -258,7 +260,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->seq_off.release(); h->ref_off.release(); h->keys.release(); h->keys_alt.release();
     h->vals.release(); h->vals_alt.release(); h->retry_a.release(); h->retry_b.release();
     h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
-    h->cub_tmp.release(); h->tb_pool.release(); h->wflags.release();
+    h->cub_tmp.release(); h->tb_pool.release(); h->wflags.release(); h->anchor.release();
     if (h->d_hist) cudaFree(h->d_hist);
     if (h->d_pool) cudaFree(h->d_pool);
     if (h->d_counters) cudaFree(h->d_counters);
@@ -334,6 +336,9 @@ int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, cons
     PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
     window_flags_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, enc_ref.p, io.ref_off, any_n, wflags.p + first);
     launches++;
+    seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
+        (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first);
+    launches++;
     int4* fwd_c = fwd.p + first;
     cudasw_result* res_c = res.p + first;
     const bool have_multi = g_var[g_nvar - 1].multi;
@@ -343,9 +348,9 @@ int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, cons
     size_t cub_bytes = cub_tmp.cap;
     CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
     fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
-                                                           keys.p, vals.p, d_hist, res_c, any_n, wflags.p + first);
+                                                           keys.p, vals.p, d_hist, res_c, any_n, wflags.p + first, anchor.p + first);
     launches++;
-    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 32, st));
     launches += 3;
     CK(cudaMemcpyAsync(h_hist, d_hist, 256 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(ev[2], st));
@@ -517,7 +522,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(enc_ref.ensure((size_t)total_w + 16));
     CK(keys.ensure(n)); CK(keys_alt.ensure(n)); CK(vals.ensure(n)); CK(vals_alt.ensure(n));
     CK(retry_a.ensure(n)); CK(retry_b.ensure(n));
-    CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n)); CK(wflags.ensure(n));
+    CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n)); CK(wflags.ensure(n)); CK(anchor.ensure(n));
     CK(cig.ensure((size_t)std::max<int64_t>(cigar_cap, 1)));
     {
         size_t cub_bytes = 0;

@@ -136,12 +136,91 @@ __host__ __device__ __forceinline__ int variant_of(const VariantTable& vt, int q
 }
 
 #ifdef CUSW_MAIN_TU
+// ------------------------------------------------------------------------------------------
+// Scheduling hint (never affects a result): the window column where a pair's alignment probably starts,
+// from 8-mer seeds. The four pairs that share a warp of the score kernel leave their quiet steps only
+// while their own alignment crosses the wavefront; binning pairs with similar columns together makes
+// those busy stretches coincide. One warp per pair: every 8-mer of the query goes into a small tagged hash
+// table in shared memory, every 8th window 8-mer is looked up and votes for a diagonal bucket of 32 columns.
+// ------------------------------------------------------------------------------------------
+constexpr int kSeedK = 8, kSeedStride = 8, kSeedTable = 1024, kSeedBins = 512, kSeedWarps = 8;
+__device__ __forceinline__ bool seed_kmer(const uint8_t* __restrict__ p, uint32_t& km) {
+    km = 0;
+    bool ok = true;
+#pragma unroll
+    for (int x = 0; x < kSeedK; x++) {
+        const uint32_t c = p[x] & 7u;  // low nibble of an encoded byte = base code, >= 4: N / pad
+        ok &= c < 4u;
+        km = (km << 2) | (c & 3u);
+    }
+    return ok;
+}
+__global__ void __launch_bounds__(32 * kSeedWarps)
+seed_anchor_kernel(int n, const uint8_t* __restrict__ enc_seq, const uint8_t* __restrict__ enc_ref,
+                   const int64_t* __restrict__ seq_off, const int64_t* __restrict__ ref_off,
+                   uint16_t* __restrict__ anchor) {
+    __shared__ uint32_t table[kSeedWarps][kSeedTable];
+    __shared__ unsigned int bins[kSeedWarps][kSeedBins / 2];  // two 16-bit counters per word
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    uint32_t* tab = table[wib];
+    unsigned int* bin = bins[wib];
+    for (int i = lane; i < kSeedTable; i += 32) tab[i] = 0u;
+    uint32_t tag = 0;
+    for (int p = blockIdx.x * kSeedWarps + wib; p < n; p += gridDim.x * kSeedWarps) {
+        const int64_t qo = seq_off[p], ro = ref_off[p];
+        const int q = (int)(seq_off[p + 1] - qo), w = (int)(ref_off[p + 1] - ro);
+        int col = 0;
+        if (q >= kSeedK && w >= kSeedK && q <= 4096 && w + q <= 32 * kSeedBins) {  // uniform per warp
+            tag = tag == 0xFFFFFu ? 1u : tag + 1u;
+            for (int i = lane; i < kSeedBins / 2; i += 32) bin[i] = 0u;
+            const uint8_t* s = enc_seq + qo;
+            for (int qp = lane; qp + kSeedK <= q; qp += 32) {
+                uint32_t km;
+                if (seed_kmer(s + qp, km)) tab[(km ^ (km >> 6)) & (kSeedTable - 1)] = (tag << 12) | (uint32_t)qp;
+            }
+            __syncwarp();
+            const uint8_t* r = enc_ref + ro;
+            for (int wp = kSeedStride * lane; wp + kSeedK <= w; wp += 32 * kSeedStride) {
+                uint32_t km;
+                const bool ok = seed_kmer(r + wp, km);
+                const uint32_t ent = tab[(km ^ (km >> 6)) & (kSeedTable - 1)];
+                if (ok && (ent >> 12) == tag) {
+                    // a table slot is keyed by 10 hash bits only: confirm the 8-mer before voting
+                    uint32_t k2;
+                    const int qp = (int)(ent & 0xFFFu);
+                    if (seed_kmer(s + qp, k2) && k2 == km) {
+                        const int d = wp - qp + q;  // diagonal, shifted to be >= 0
+                        atomicAdd(bin + (d >> 6), (d >> 5) & 1 ? 0x10000u : 1u);
+                    }
+                }
+            }
+            __syncwarp();
+            int bestv = 0, bestb = 0;
+            for (int i = lane; i < kSeedBins / 2; i += 32) {
+                const unsigned int v2 = bin[i];
+                const int lo = (int)(v2 & 0xFFFFu), hi = (int)(v2 >> 16);
+                if (lo > bestv) { bestv = lo; bestb = 2 * i; }
+                if (hi > bestv) { bestv = hi; bestb = 2 * i + 1; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const int ov = __shfl_xor_sync(0xffffffffu, bestv, o), ob = __shfl_xor_sync(0xffffffffu, bestb, o);
+                if (ov > bestv || (ov == bestv && ob < bestb)) { bestv = ov; bestb = ob; }
+            }
+            col = bestv >= 2 ? max(bestb * 32 - q, 0) : 0;
+            __syncwarp();
+        }
+        if (lane == 0) anchor[p] = (uint16_t)min(col >> 2, 4095);
+    }
+}
+
 // keys for the forward pass; hist[slot] counts pairs per (flavour, variant); the last slot counts invalid pairs
 __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
                                 const int64_t* __restrict__ ref_off, VariantTable vt, int max_rows,
                                 int max_cols, uint32_t* __restrict__ keys, int* __restrict__ vals,
                                 int* __restrict__ hist, cudasw_result* __restrict__ res,
-                                const int* __restrict__ any_n, const uint8_t* __restrict__ wflags) {
+                                const int* __restrict__ any_n, const uint8_t* __restrict__ wflags,
+                                const uint16_t* __restrict__ anchor) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     int64_t q = seq_off[p + 1] - seq_off[p];
@@ -155,9 +234,10 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
     else if (q > max_rows || w > max_cols) { r.status = CUDASW_ETOOLARGE; v = 2 * vt.n; }
     else v = variant_of(vt, (int)q) + ((*any_n != 0 && wflags[p]) ? vt.n : 0);
     res[p] = r;
-    uint32_t wq = (uint32_t)(w >> 4);
-    if (wq > 0xFFFFFu) wq = 0xFFFFFu;  // 2^24 columns max / 16
-    keys[p] = ((uint32_t)v << 20) | wq;
+    // key = (slot : 7 | window length / 64 : 13 | seed anchor column / 4 : 12)
+    uint32_t wq = (uint32_t)(w >> 6);
+    if (wq > 0x1FFFu) wq = 0x1FFFu;
+    keys[p] = ((uint32_t)v << 25) | (wq << 12) | (uint32_t)anchor[p];
     vals[p] = p;
     atomicAdd(&hist[v], 1);
 }
