@@ -10,7 +10,7 @@ tail -3 $O/pytest_$TAG.log
 timeout 600 python bench.py > $O/bench_$TAG.json 2> $O/bench_$TAG.err; echo "bench exit $?"
 tail -c 600 $O/bench_$TAG.err
 timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$TAG.json 2>> $O/bench_$TAG.err; echo "ref exit $?"
-for p in int_peak pipe_probe cellmix_probe hfma_probe; do
+for p in int_peak; do
   [ -x tools/$p ] && timeout 120 tools/$p > $O/${p}_$TAG.txt 2>&1
 done
 if [ "$2" != "noncu" ]; then
