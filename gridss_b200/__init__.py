@@ -13,7 +13,10 @@ from .aligner import (  # noqa: F401
     BatchingAligner,
     CudaAligner,
     CudaSwError,
+    MultiGpuAligner,
     RESULT_DTYPE,
+    WINDOW_DTYPE,
+    WINDOW_REVCOMP,
     cigar_string,
     load_library,
 )
@@ -25,7 +28,10 @@ __all__ = [
     "BatchingAligner",
     "CudaAligner",
     "CudaSwError",
+    "MultiGpuAligner",
     "RESULT_DTYPE",
+    "WINDOW_DTYPE",
+    "WINDOW_REVCOMP",
     "cigar_string",
     "load_library",
 ]

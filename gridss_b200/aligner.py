@@ -40,6 +40,10 @@ RESULT_DTYPE = np.dtype(
         ("status", "<i4"),
     ]
 )
+# cudasw_window (include/cudasw.h): one window segment = bases [start, end) of a loaded contig, optionally
+# reverse-complemented (flags & WINDOW_REVCOMP)
+WINDOW_DTYPE = np.dtype([("contig", "<i4"), ("flags", "<i4"), ("start", "<i8"), ("end", "<i8")])
+WINDOW_REVCOMP = 1
 _OPS = "MIDNSHP=X"
 
 
@@ -82,6 +86,17 @@ ABI = [
     ("cudasw_destroy", None, [_vp]),
     ("cudasw_align_batch", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
     ("cudasw_align_batch_device", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_reference_load", ctypes.c_int, [_vp, _i32, _vp, _vp]),
+    ("cudasw_reference_fetch", ctypes.c_int, [_vp, _vp, _i32, _vp, _i64]),
+    ("cudasw_align_batch_windows", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_multi_create", ctypes.c_int, [ctypes.POINTER(_Scoring), _vp, ctypes.c_int, ctypes.POINTER(_vp)]),
+    ("cudasw_multi_destroy", None, [_vp]),
+    ("cudasw_multi_device_count", ctypes.c_int, [_vp]),
+    ("cudasw_multi_align_batch", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_multi_reference_load", ctypes.c_int, [_vp, _i32, _vp, _vp]),
+    ("cudasw_multi_align_batch_windows", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_multi_get_stats", ctypes.c_int, [_vp, ctypes.c_int, ctypes.POINTER(Stats), ctypes.POINTER(_i64), ctypes.POINTER(_i64)]),
+    ("cudasw_multi_last_error", ctypes.c_char_p, [_vp]),
     ("cudasw_device_alloc", ctypes.c_int, [_vp, _sz, ctypes.POINTER(_vp)]),
     ("cudasw_device_free", ctypes.c_int, [_vp, _vp]),
     ("cudasw_upload", ctypes.c_int, [_vp, _vp, _vp, _sz]),
@@ -287,6 +302,46 @@ class CudaAligner(Aligner):
             out.append(Alignment(int(r["ref_begin"]), cigar_string(cig[r["cigar_off"] : r["cigar_off"] + r["cigar_len"]]), int(r["score"])))
         return out
 
+    # -- device-resident reference (TwoBitBufferedReferenceSequenceFile.java:97-125)
+    def load_reference(self, contigs: Sequence[bytes]) -> None:
+        """Pack the contigs into HBM (2 bits per base + an N mask). Replaces any earlier reference."""
+        blob, off = pack(contigs)
+        rc = self._lib.cudasw_reference_load(self._h, len(contigs), blob.ctypes.data, off.ctypes.data)
+        if rc != 0:
+            raise (ValueError if rc == CUDASW_EINVAL else CudaSwError)(f"cudasw_reference_load failed ({rc}): {self._err()}")
+        self._contig_len = [len(c) for c in contigs]
+
+    def get_subsequence(self, contig: int, start: int, end: int, revcomp: bool = False) -> bytes:
+        """getSubsequenceAt(contig, start+1, end) of the packed reference: upper-case ACGT, anything else N."""
+        win = np.zeros(1, dtype=WINDOW_DTYPE)
+        win[0] = (contig, WINDOW_REVCOMP if revcomp else 0, start, end)
+        out = np.zeros(max(1, end - start), dtype=np.uint8)
+        rc = self._lib.cudasw_reference_fetch(self._h, win.ctypes.data, 1, out.ctypes.data, out.size)
+        if rc < 0:
+            raise (ValueError if rc == CUDASW_EINVAL else CudaSwError)(f"cudasw_reference_fetch failed ({rc}): {self._err()}")
+        return out[:rc].tobytes()
+
+    def align_blobs_windows(self, seq_blob, seq_off, win, win_off, res=None, cig=None):
+        """Queries from host blobs, windows named by WINDOW_DTYPE segments of the loaded reference
+        (pair i uses win[win_off[i]:win_off[i+1]] concatenated). Same outputs as align_blobs."""
+        n = len(seq_off) - 1
+        assert win.dtype == WINDOW_DTYPE and len(win_off) == n + 1
+        res = np.zeros(n, dtype=RESULT_DTYPE) if res is None else res
+        cap = max(64, 24 * n) if cig is None else len(cig)
+        while True:
+            if cig is None or len(cig) < cap:
+                cig = np.zeros(cap, dtype=np.uint32)
+            used = ctypes.c_int64(0)
+            rc = self._lib.cudasw_align_batch_windows(
+                self._h, n, seq_blob.ctypes.data, seq_off.ctypes.data, win.ctypes.data, win_off.ctypes.data,
+                res.ctypes.data, cig.ctypes.data, cap, ctypes.byref(used))
+            if rc == CUDASW_ENOMEM and used.value > cap:
+                cap = int(used.value) + 16
+                continue
+            if rc != 0:
+                raise CudaSwError(f"cudasw_align_batch_windows failed ({rc}): {self._err()}")
+            return res, cig[: used.value]
+
     def variant_for(self, query_len: int) -> tuple[int, int, int]:
         """(lanes per pair, rows per virtual lane, strips) of the score kernel a query length maps to."""
         g, r, s = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
@@ -340,6 +395,100 @@ class CudaAligner(Aligner):
         if r["status"] != 0:
             raise CudaSwError(f"pair failed with status {int(r['status'])}")
         return Alignment(int(r["ref_begin"]), cigar_string(cig[: need.value]), int(r["score"]))
+
+
+class MultiGpuAligner(Aligner):
+    """Several B200s behind one in-process handle (cudasw_multi_*): contiguous cost-balanced
+    slices, one host thread and engine per GPU, results at the original ordinals, no collective."""
+
+    def __init__(self, match=1, mismatch=-4, ambiguous=-4, gapOpen=6, gapExtend=1, devices: Sequence[int] | None = None):
+        lib = load_library()
+        self._lib = lib
+        sc = _Scoring(match, mismatch, ambiguous, gapOpen, gapExtend)
+        h = ctypes.c_void_p()
+        devs = np.asarray(list(devices), dtype=np.int32) if devices is not None else None
+        rc = lib.cudasw_multi_create(ctypes.byref(sc), devs.ctypes.data if devs is not None else None,
+                                     len(devs) if devs is not None else 0, ctypes.byref(h))
+        if rc != 0:
+            msg = (lib.cudasw_multi_last_error(None) or b"").decode()
+            if rc == CUDASW_EINVAL:
+                raise ValueError(msg)
+            raise CudaSwError(f"cudasw_multi_create failed ({rc}): {msg}")
+        self._h = h
+        self.n_devices = lib.cudasw_multi_device_count(h)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.cudasw_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _err(self) -> str:
+        return (self._lib.cudasw_multi_last_error(self._h) or b"").decode()
+
+    def _call(self, fn, name, n, args, res, cig):
+        res = np.zeros(n, dtype=RESULT_DTYPE) if res is None else res
+        cap = max(64, 24 * n) if cig is None else len(cig)
+        while True:
+            if cig is None or len(cig) < cap:
+                cig = np.zeros(cap, dtype=np.uint32)
+            used = ctypes.c_int64(0)
+            rc = fn(self._h, n, *args, res.ctypes.data, cig.ctypes.data, cap, ctypes.byref(used))
+            if rc == CUDASW_ENOMEM and used.value > cap:
+                cap = int(used.value) + 16
+                continue
+            if rc != 0:
+                raise CudaSwError(f"{name} failed ({rc}): {self._err()}")
+            return res, cig  # not compact: cigar_off is absolute into `cig`
+
+    def align_blobs(self, seq_blob, seq_off, ref_blob, ref_off, res=None, cig=None):
+        return self._call(self._lib.cudasw_multi_align_batch, "cudasw_multi_align_batch", len(seq_off) - 1,
+                          (seq_blob.ctypes.data, seq_off.ctypes.data, ref_blob.ctypes.data, ref_off.ctypes.data), res, cig)
+
+    def load_reference(self, contigs: Sequence[bytes]) -> None:
+        blob, off = pack(contigs)
+        rc = self._lib.cudasw_multi_reference_load(self._h, len(contigs), blob.ctypes.data, off.ctypes.data)
+        if rc != 0:
+            raise (ValueError if rc == CUDASW_EINVAL else CudaSwError)(f"cudasw_multi_reference_load failed ({rc}): {self._err()}")
+
+    def align_blobs_windows(self, seq_blob, seq_off, win, win_off, res=None, cig=None):
+        assert win.dtype == WINDOW_DTYPE
+        return self._call(self._lib.cudasw_multi_align_batch_windows, "cudasw_multi_align_batch_windows", len(seq_off) - 1,
+                          (seq_blob.ctypes.data, seq_off.ctypes.data, win.ctypes.data, win_off.ctypes.data), res, cig)
+
+    def align_batch(self, seqs: Sequence[bytes], refs: Sequence[bytes]) -> list[Alignment]:
+        if len(seqs) != len(refs):
+            raise ValueError("seqs and refs differ in length")
+        for s, r in zip(seqs, refs):
+            if not s:
+                raise ValueError("seq must be non-zero size")
+            if not r:
+                raise ValueError("ref must be non-zero size")
+        sb, so = pack(seqs)
+        rb, ro = pack(refs)
+        res, cig = self.align_blobs(sb, so, rb, ro)
+        out = []
+        for r in res:
+            if r["status"] != 0:
+                raise CudaSwError(f"pair failed with status {int(r['status'])}")
+            out.append(Alignment(int(r["ref_begin"]), cigar_string(cig[r["cigar_off"]: r["cigar_off"] + r["cigar_len"]]), int(r["score"])))
+        return out
+
+    def align_smith_waterman(self, seq: bytes, ref: bytes) -> Alignment:
+        return self.align_batch([seq], [ref])[0]
+
+    def slice_stats(self) -> list[dict]:
+        out = []
+        for d in range(self.n_devices):
+            st, f, c = Stats(), ctypes.c_int64(0), ctypes.c_int64(0)
+            self._lib.cudasw_multi_get_stats(self._h, d, ctypes.byref(st), ctypes.byref(f), ctypes.byref(c))
+            out.append({"first_pair": f.value, "pairs": c.value, **st.as_dict()})
+        return out
 
 
 class BatchingAligner(Aligner):

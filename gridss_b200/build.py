@@ -34,7 +34,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     extra = (["-Xptxas", "-v"] if verbose else []) + os.environ.get("CUDASW_NVCC_EXTRA", "").split()
     jobs = [(os.path.join(OBJ, "cudasw.o"), [os.path.join(CSRC, "cudasw.cu")]),
-            (os.path.join(OBJ, "variants.o"), [os.path.join(CSRC, "variants.cu")])]
+            (os.path.join(OBJ, "variants.o"), [os.path.join(CSRC, "variants.cu")]),
+            (os.path.join(OBJ, "multi.o"), [os.path.join(CSRC, "multi.cpp")])]
     for g in GROUPS:
         jobs.append((os.path.join(OBJ, f"score_g{g}.o"), [f"-DSCORE_G={g}", os.path.join(CSRC, "score_variants.cu")]))
 

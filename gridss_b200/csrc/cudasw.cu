@@ -93,6 +93,11 @@ struct cudasw {
     DevBuf<uint16_t> anchor;  // per pair: seed estimate of the alignment's first window column / 4 (scheduling hint)
     DevBuf<uint8_t> wflags;  // per pair: window contains N (xor-selector flavour)
     DevBuf<uint8_t> tb_pool;
+    // device-resident reference genome (cudasw_reference_load) and the window descriptors of the current batch
+    DevBuf<uint32_t> ref2bit, refN;
+    DevBuf<int64_t> d_contig_off, d_seg_off;
+    DevBuf<WindowSeg> d_segs;
+    std::vector<int64_t> contig_off;  // n_contigs + 1, linear base coordinates
     int* d_hist = nullptr;  // 256 ints: pairs per (flavour, variant) slot
     uint32_t* d_pool = nullptr;  // {poolA, poolB}
     unsigned long long* d_counters = nullptr;  // [0] pool used, [1] cigar used, [2] retry count(int)
@@ -114,13 +119,13 @@ struct cudasw {
     void set_error(const std::string& s) { error = s; }
     int process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so, const uint8_t* d_ref,
                       const int64_t* d_ro, int64_t q_lo, int64_t q_hi, int64_t w_lo, int64_t w_hi, int64_t cigar_cap,
-                      uint64_t* launches_out);
+                      bool gather, uint64_t* launches_out);
     int finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out);
     int run(int64_t n, const uint8_t* d_seq, const int64_t* d_seq_off, const uint8_t* d_ref,
             const int64_t* d_ref_off, int64_t total_q, int64_t total_w, cudasw_result* out,
             uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used, bool inputs_on_host,
             const uint8_t* h_seq, const int64_t* h_seq_off, const uint8_t* h_ref,
-            const int64_t* h_ref_off);
+            const int64_t* h_ref_off, const WindowSeg* h_segs = nullptr, const int64_t* h_seg_off = nullptr);
 };
 
 static uint32_t pack2(int v) { return ((uint32_t)v & 0xFFFFu) | (((uint32_t)v & 0xFFFFu) << 16); }
@@ -261,6 +266,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->vals.release(); h->vals_alt.release(); h->retry_a.release(); h->retry_b.release();
     h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
     h->cub_tmp.release(); h->tb_pool.release(); h->wflags.release(); h->anchor.release();
+    h->ref2bit.release(); h->refN.release(); h->d_contig_off.release(); h->d_seg_off.release(); h->d_segs.release();
     if (h->d_hist) cudaFree(h->d_hist);
     if (h->d_pool) cudaFree(h->d_pool);
     if (h->d_counters) cudaFree(h->d_counters);
@@ -317,7 +323,7 @@ int cudasw::launch_variants(bool reverse, const int* order, PairIO io, const int
 // Blob offsets are absolute, so a chunk is just a shifted view of the per-pair arrays.
 int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so,
                           const uint8_t* d_ref, const int64_t* d_ro, int64_t q_lo, int64_t q_hi,
-                          int64_t w_lo, int64_t w_hi, int64_t cigar_cap, uint64_t* launches_out) {
+                          int64_t w_lo, int64_t w_hi, int64_t cigar_cap, bool gather, uint64_t* launches_out) {
     cudaStream_t st = stream;
     uint64_t launches = 0;
     const int64_t n = cnt;
@@ -331,10 +337,17 @@ int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, cons
         if (tq > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u, nullptr); launches++; }
         thr = (tw + 15) / 16;
         blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
-        if (tw > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u, any_n); launches++; }
+        if (tw > 0 && !gather) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u, any_n); launches++; }
     }
     PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
-    window_flags_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, enc_ref.p, io.ref_off, any_n, wflags.p + first);
+    if (gather) {
+        // windows come out of the device-resident 2-bit reference already encoded, with their N flags
+        window_gather_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, d_segs.p, d_seg_off.p + first, io.ref_off,
+                                                                         d_contig_off.p, ref2bit.p, refN.p, enc_ref.p,
+                                                                         wflags.p + first, any_n, 0);
+    } else {
+        window_flags_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, enc_ref.p, io.ref_off, any_n, wflags.p + first);
+    }
     launches++;
     seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
         (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first);
@@ -458,8 +471,10 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
                 const uint8_t* d_ref_in, const int64_t* d_ref_off_in, int64_t total_q,
                 int64_t total_w, cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap,
                 int64_t* cigar_used, bool inputs_on_host, const uint8_t* h_seq,
-                const int64_t* h_seq_off, const uint8_t* h_ref, const int64_t* h_ref_off) {
+                const int64_t* h_seq_off, const uint8_t* h_ref, const int64_t* h_ref_off,
+                const WindowSeg* h_segs, const int64_t* h_seg_off) {
     std::lock_guard<std::mutex> lock(mu);
+    const bool gather = h_segs != nullptr;
     error.clear();
     stats = cudasw_stats{};
     if (cigar_used) *cigar_used = 0;
@@ -480,6 +495,9 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         // kernels have to wait for, and each later copy hides behind the (slower) kernels of the chunk before it
         int64_t target = inputs_on_host ? (int64_t)64 << 20 : (int64_t)1 << 60;  // resident inputs: nothing to overlap
         int64_t target_max = (int64_t)1 << 30;
+        // windows gathered on the device: only queries and descriptors cross PCIe (~1/12 of the bytes), so one small
+        // leading chunk is enough to hide the copy of the rest
+        if (gather) { target = (int64_t)128 << 20; target_max = (int64_t)1 << 60; }
         if (const char* e = getenv("CUDASW_CHUNK_MB")) target = target_max = std::max<int64_t>(1, atoll(e)) << 20;
         const int64_t max_pairs = 8 << 20;  // keeps the per-chunk sort/bin arrays small
         int64_t first = 0;
@@ -511,7 +529,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
             }
             chunks.push_back(c);
             first = last;
-            target = std::min(target * 2, std::max(target, target_max));
+            target = gather ? target_max : std::min(target * 2, std::max(target, target_max));
         }
     }
     int64_t max_cnt = 0;
@@ -554,27 +572,35 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     const int64_t* d_ro = d_ref_off_in;
     if (inputs_on_host) {
         CK(raw_seq.ensure((size_t)total_q + 16));
-        CK(raw_ref.ensure((size_t)total_w + 16));
+        if (!gather) CK(raw_ref.ensure((size_t)total_w + 16));
         CK(seq_off.ensure(n + 1));
         CK(ref_off.ensure(n + 1));
         CK(cudaEventRecord(ev[7], st));
         CK(cudaStreamWaitEvent(copy_stream, ev[7], 0));  // the previous batch's kernels no longer read raw_*
         CK(cudaMemcpyAsync(seq_off.p, h_seq_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
         CK(cudaMemcpyAsync(ref_off.p, h_ref_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
+        if (gather) {
+            const int64_t nsegs = h_seg_off[n];
+            CK(d_segs.ensure((size_t)std::max<int64_t>(nsegs, 1)));
+            CK(d_seg_off.ensure(n + 1));
+            CK(cudaMemcpyAsync(d_seg_off.p, h_seg_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
+            if (nsegs > 0) CK(cudaMemcpyAsync(d_segs.p, h_segs, (size_t)nsegs * sizeof(WindowSeg), cudaMemcpyHostToDevice, copy_stream));
+        }
         for (size_t i = 0; i < chunks.size(); i++) {
             const Chunk& c = chunks[i];
             if (c.q_hi > c.q_lo) CK(cudaMemcpyAsync(raw_seq.p + c.q_lo, h_seq + c.q_lo, (size_t)(c.q_hi - c.q_lo), cudaMemcpyHostToDevice, copy_stream));
-            if (c.w_hi > c.w_lo) CK(cudaMemcpyAsync(raw_ref.p + c.w_lo, h_ref + c.w_lo, (size_t)(c.w_hi - c.w_lo), cudaMemcpyHostToDevice, copy_stream));
+            if (c.w_hi > c.w_lo && !gather) CK(cudaMemcpyAsync(raw_ref.p + c.w_lo, h_ref + c.w_lo, (size_t)(c.w_hi - c.w_lo), cudaMemcpyHostToDevice, copy_stream));
             CK(cudaEventRecord(h2d_done[i], copy_stream));
         }
         d_seq = raw_seq.p; d_ref = raw_ref.p; d_so = seq_off.p; d_ro = ref_off.p;
-        stats.h2d_bytes = (uint64_t)total_q + (uint64_t)total_w + (uint64_t)(n + 1) * 16;
+        stats.h2d_bytes = (uint64_t)total_q + (uint64_t)(n + 1) * 16 +
+                          (gather ? (uint64_t)(n + 1) * 8 + (uint64_t)h_seg_off[n] * sizeof(WindowSeg) : (uint64_t)total_w);
     }
 
     for (size_t i = 0; i < chunks.size(); i++) {
         const Chunk& c = chunks[i];
         if (inputs_on_host) CK(cudaStreamWaitEvent(st, h2d_done[i], 0));
-        int rc = process_chunk(c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, cigar_cap, &launches);
+        int rc = process_chunk(c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, cigar_cap, gather, &launches);
         if (rc != CUDASW_OK) {
             cudaStreamSynchronize(copy_stream);  // do not leave copies in flight over the caller's buffers
             return rc;
@@ -661,6 +687,119 @@ extern "C" int cudasw_align_batch_device(cudasw_t* h, int64_t n, const uint8_t* 
     int64_t tq = n > 0 ? h_seq_off[n] : 0, tw = n > 0 ? h_ref_off[n] : 0;
     return h->run(n, d_seq_blob, d_seq_off, d_ref_blob, d_ref_off, tq, tw, out, cigar_blob, cigar_cap, cigar_used,
                   false, nullptr, h_seq_off, nullptr, h_ref_off);
+}
+
+// ---- device-resident reference + window descriptors
+static_assert(sizeof(cudasw_window) == sizeof(WindowSeg), "cudasw_window and the device descriptor share one layout");
+
+extern "C" int cudasw_reference_load(cudasw_t* h, int32_t n_contigs, const uint8_t* bases, const int64_t* contig_off) {
+    if (!h) return CUDASW_EINVAL;
+    std::lock_guard<std::mutex> lock(h->mu);
+    h->error.clear();
+    auto set_error = [&](const std::string& m) { h->error = m; };
+    if (n_contigs < 0 || (n_contigs > 0 && (!bases || !contig_off))) { h->set_error("null reference"); return CUDASW_EINVAL; }
+    if (n_contigs > 0 && contig_off[0] != 0) { h->set_error("contig offsets must start at 0"); return CUDASW_EINVAL; }
+    for (int32_t c = 0; c < n_contigs; c++)
+        if (contig_off[c + 1] < contig_off[c]) { h->set_error("contig offsets must be non-decreasing"); return CUDASW_EINVAL; }
+    CK(cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    CK(cudaStreamSynchronize(st));
+    h->ref2bit.release(); h->refN.release(); h->d_contig_off.release();
+    h->contig_off.clear();
+    if (n_contigs == 0) return CUDASW_OK;
+    const int64_t total = contig_off[n_contigs];
+    const size_t groups = (size_t)((total + 31) / 32);
+    CK(h->ref2bit.ensure(2 * groups + 4));
+    CK(h->refN.ensure(groups + 4));
+    CK(h->d_contig_off.ensure((size_t)n_contigs + 1));
+    CK(cudaMemcpyAsync(h->d_contig_off.p, contig_off, ((size_t)n_contigs + 1) * 8, cudaMemcpyHostToDevice, st));
+    // ASCII goes up in slices of 256 MB (a multiple of 32 bases) through a staging buffer that is released afterwards
+    const int64_t slice = (int64_t)256 << 20;
+    DevBuf<uint8_t> stage;
+    CK(stage.ensure((size_t)std::min(slice, total) + 32));
+    for (int64_t g0 = 0; g0 < total; g0 += slice) {
+        const int64_t len = std::min(slice, total - g0);
+        CK(cudaMemcpyAsync(stage.p, bases + g0, (size_t)len, cudaMemcpyHostToDevice, st));
+        const int64_t thr = (len + 31) / 32;
+        ref_pack_kernel<<<(int)std::min<int64_t>((thr + 255) / 256, 148 * 16), 256, 0, st>>>(stage.p, len, g0, h->ref2bit.p, h->refN.p);
+        CK(cudaStreamSynchronize(st));  // the staging buffer is reused by the next slice
+    }
+    CK(cudaGetLastError());
+    stage.release();
+    h->contig_off.assign(contig_off, contig_off + n_contigs + 1);
+    return CUDASW_OK;
+}
+
+// Validates the descriptors and sizes every window; an invalid descriptor makes its window empty, which the
+// pipeline reports as a per-pair CUDASW_EINVAL (like an empty `ref`, SswJniAligner.java:48-50).
+static void window_offsets(const cudasw_t* h, int64_t n, const cudasw_window* win, const int64_t* win_off,
+                           std::vector<int64_t>& ref_off) {
+    ref_off.assign((size_t)n + 1, 0);
+    const int64_t ncontig = (int64_t)h->contig_off.size() - 1;
+    for (int64_t p = 0; p < n; p++) {
+        int64_t len = 0;
+        bool ok = win_off[p + 1] >= win_off[p];
+        for (int64_t s = win_off[p]; ok && s < win_off[p + 1]; s++) {
+            const cudasw_window& w = win[s];
+            if (w.contig < 0 || w.contig >= ncontig || w.start < 0 || w.end < w.start ||
+                w.end > h->contig_off[w.contig + 1] - h->contig_off[w.contig]) ok = false;
+            else len += w.end - w.start;
+        }
+        ref_off[p + 1] = ref_off[p] + (ok ? len : 0);
+    }
+}
+
+extern "C" int cudasw_align_batch_windows(cudasw_t* h, int64_t n, const uint8_t* seq_blob, const int64_t* seq_off,
+                                          const cudasw_window* win, const int64_t* win_off, cudasw_result* out,
+                                          uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used) {
+    if (!h) return CUDASW_EINVAL;
+    if (n > 0 && (!seq_blob || !seq_off || !win || !win_off)) { h->error = "null input"; return CUDASW_EINVAL; }
+    if (n > 0 && (seq_off[0] != 0 || win_off[0] != 0)) { h->error = "offsets must start at 0"; return CUDASW_EINVAL; }
+    if (h->contig_off.empty()) { h->error = "no reference loaded (cudasw_reference_load)"; return CUDASW_EINVAL; }
+    std::vector<int64_t> ref_off;
+    window_offsets(h, std::max<int64_t>(n, 0), win, win_off, ref_off);
+    // a pair with a rejected descriptor has window length 0: the gather skips it and the pair reports EINVAL
+    int64_t tq = n > 0 ? seq_off[n] : 0, tw = n > 0 ? ref_off[n] : 0;
+    return h->run(n, nullptr, nullptr, nullptr, nullptr, tq, tw, out, cigar_blob, cigar_cap, cigar_used, true,
+                  seq_blob, seq_off, nullptr, ref_off.data(), reinterpret_cast<const WindowSeg*>(win), win_off);
+}
+
+extern "C" int cudasw_reference_fetch(cudasw_t* h, const cudasw_window* win, int32_t n_win, uint8_t* out, int64_t out_cap) {
+    if (!h || !out || (n_win > 0 && !win) || n_win < 0) return CUDASW_EINVAL;
+    std::lock_guard<std::mutex> lock(h->mu);
+    h->error.clear();
+    auto set_error = [&](const std::string& m) { h->error = m; };
+    if (h->contig_off.empty()) { h->set_error("no reference loaded (cudasw_reference_load)"); return CUDASW_EINVAL; }
+    const int64_t woff[2] = {0, n_win};
+    std::vector<int64_t> ref_off;
+    window_offsets(h, 1, win, woff, ref_off);
+    const int64_t len = ref_off[1];
+    if (len == 0 && n_win > 0) {
+        bool all_empty = true;
+        for (int32_t s = 0; s < n_win; s++) all_empty &= win[s].end == win[s].start;
+        if (!all_empty) { h->set_error("window outside the loaded reference"); return CUDASW_EINVAL; }
+    }
+    if (len > out_cap) { h->set_error("output buffer too small"); return CUDASW_ENOMEM; }
+    if (len == 0) return 0;
+    if (len > 0x7fffffffll) { h->set_error("window too long"); return CUDASW_ETOOLARGE; }
+    CK(cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    DevBuf<uint8_t> buf;
+    DevBuf<int64_t> offs;
+    DevBuf<WindowSeg> segs;
+    CK(buf.ensure((size_t)len + 16));
+    CK(offs.ensure(4));
+    CK(segs.ensure((size_t)n_win));
+    const int64_t hoffs[4] = {0, n_win, 0, len};
+    CK(cudaMemcpyAsync(offs.p, hoffs, sizeof hoffs, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(segs.p, win, (size_t)n_win * sizeof(WindowSeg), cudaMemcpyHostToDevice, st));
+    window_gather_kernel<<<1, 32, 0, st>>>(1, segs.p, offs.p, offs.p + 2, h->d_contig_off.p, h->ref2bit.p, h->refN.p, buf.p,
+                                           nullptr, nullptr, 1);
+    CK(cudaMemcpyAsync(out, buf.p, (size_t)len, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    buf.release(); offs.release(); segs.release();
+    return (int)len;
 }
 
 extern "C" int cudasw_device_alloc(cudasw_t* h, size_t bytes, void** dptr) {

@@ -84,6 +84,104 @@ __global__ void __launch_bounds__(256) window_flags_kernel(int n, const uint8_t*
     if ((threadIdx.x & 31) == 0) flags[p] = seen ? 1 : 0;
 }
 
+// ------------------------------------------------------------------------------------------
+// Device-resident reference genome. Mirrors PackedReferenceSequence
+// (picard/TwoBitBufferedReferenceSequenceFile.java:97-125): 2 bits per base plus one "ambiguous" bit per base
+// (every byte that clean() would turn into N, SswJniAligner.java:71-79). Contigs are concatenated in one linear
+// coordinate g = contig_off[c] + pos; base g lives in bits 2*(g&15) of word g>>4, its N flag in bit g&31 of
+// word g>>5. HBM-bound: 1 byte in, 3/8 byte out.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ref_pack_kernel(const uint8_t* __restrict__ in, int64_t n, int64_t g0,
+                                                       uint32_t* __restrict__ two_bit, uint32_t* __restrict__ nmask) {
+    // g0 is a multiple of 32; thread t packs bases [g0 + 32 t, g0 + 32 t + 32) of which `in` holds the first n
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; t * 32 < n; t += stride) {
+        const uint8_t* p = in + t * 32;
+        const int64_t left = n - t * 32;
+        uint32_t lo = 0, hi = 0, nm = 0;
+        uint32_t wds[8];
+        if (left >= 32 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+            const uint4 a = reinterpret_cast<const uint4*>(p)[0], b = reinterpret_cast<const uint4*>(p)[1];
+            wds[0] = a.x; wds[1] = a.y; wds[2] = a.z; wds[3] = a.w; wds[4] = b.x; wds[5] = b.y; wds[6] = b.z; wds[7] = b.w;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                uint32_t v = 0;
+                for (int b = 0; b < 4; b++) v |= (uint32_t)(4 * k + b < left ? p[4 * k + b] : 'A') << (8 * b);
+                wds[k] = v;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 32; k++) {
+            const uint32_t code = base_code((wds[k >> 2] >> (8 * (k & 3))) & 0xFFu);
+            const uint32_t two = code & 3u;  // an N stores 'A'; the mask bit overrides it
+            if (k < 16) lo |= two << (2 * k); else hi |= two << (2 * (k - 16));
+            nm |= (code >> 2) << k;
+        }
+        const int64_t g = (g0 >> 5) + t;
+        two_bit[2 * g] = lo;
+        two_bit[2 * g + 1] = hi;
+        nmask[g] = nm;
+    }
+}
+
+// One window segment: bases [start, end) of contig `contig` (0-based, end exclusive), reverse-complemented when
+// bit 0 of flags is set (BreakpointHomology.java:66-68 builds its windows from such pieces).
+struct WindowSeg {
+    int32_t contig, flags;
+    int64_t start, end;
+};
+
+// Expands window segments straight into the ENCODED window layout the score kernels read (no ASCII round trip):
+// one warp per pair, 4 bases per lane and iteration, 32-bit stores once the destination is aligned.
+// ascii != 0 writes upper-case "ACGTN" instead (getSubsequenceAt, for cudasw_reference_fetch).
+__global__ void __launch_bounds__(256)
+window_gather_kernel(int n, const WindowSeg* __restrict__ segs, const int64_t* __restrict__ seg_off,
+                     const int64_t* __restrict__ ref_off, const int64_t* __restrict__ contig_off,
+                     const uint32_t* __restrict__ two_bit, const uint32_t* __restrict__ nmask,
+                     uint8_t* __restrict__ out, uint8_t* __restrict__ flags, int* __restrict__ any_n, int ascii) {
+    const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (p >= n) return;
+    uint8_t* dst = out + ref_off[p];
+    const int64_t wlen = ref_off[p + 1] - ref_off[p];
+    int64_t done = 0;
+    bool seen_n = false;
+    auto fetch = [&](int64_t g, bool rc) -> uint32_t {
+        uint32_t code = (two_bit[g >> 4] >> (2 * (int)(g & 15))) & 3u;
+        if (rc) code = 3u - code;
+        if ((nmask[g >> 5] >> (int)(g & 31)) & 1u) { code = 4u; seen_n = true; }
+        if (ascii) return code == 0 ? 'A' : code == 1 ? 'C' : code == 2 ? 'G' : code == 3 ? 'T' : 'N';
+        return (code * 0x11u) ^ 0x80u;
+    };
+    for (int64_t s = seg_off[p]; s < seg_off[p + 1] && done < wlen; s++) {
+        const WindowSeg sg = segs[s];
+        const int64_t len = min(sg.end - sg.start, wlen - done);  // the host sized ref_off from the same segments
+        const bool rc = (sg.flags & 1) != 0;
+        const int64_t g0 = contig_off[sg.contig] + sg.start;
+        uint8_t* d = dst + done;
+        const int64_t head = min((int64_t)((4 - (reinterpret_cast<uintptr_t>(d) & 3)) & 3), len);
+        if (lane < head) d[lane] = (uint8_t)fetch(rc ? g0 + len - 1 - lane : g0 + lane, rc);
+        for (int64_t k = head + 4 * lane; k < len; k += 128) {
+            if (k + 4 <= len) {
+                uint32_t v = 0;
+#pragma unroll
+                for (int b = 0; b < 4; b++) v |= fetch(rc ? g0 + len - 1 - (k + b) : g0 + k + b, rc) << (8 * b);
+                *reinterpret_cast<uint32_t*>(d + k) = v;
+            } else {
+                for (int64_t b = k; b < len; b++) d[b] = (uint8_t)fetch(rc ? g0 + len - 1 - b : g0 + b, rc);
+            }
+        }
+        done += len;
+    }
+    seen_n = __any_sync(0xffffffffu, seen_n);
+    if (lane == 0) {
+        if (flags) flags[p] = seen_n ? 1 : 0;
+        if (any_n && seen_n) *any_n = 1;
+    }
+}
+
 #endif  // CUSW_MAIN_TU
 
 // ------------------------------------------------------------------------------------------

@@ -102,6 +102,33 @@ int cudasw_align_batch_device(cudasw_t* h, int64_t n_pairs,
                               cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap,
                               int64_t* cigar_used);
 
+/* ---- Device-resident reference genome + window descriptors.
+ * Replaces, for the aligner's callers, TwoBitBufferedReferenceSequenceFile.getSubsequenceAt
+ * (picard/TwoBitBufferedReferenceSequenceFile.java:97-125,210-216: 2 bits per base + an "ambiguous" BitSet) and the
+ * host-side reverse complements of BreakpointHomology.calculate (BreakpointHomology.java:62-72): the genome is packed
+ * once into HBM (3 bits per base) and a batch then names its windows instead of shipping their bytes.
+ * A window is the concatenation of one or more segments; a segment is bases [start, end) (0-based, end exclusive) of
+ * contig `contig`, reverse-complemented when (flags & CUDASW_WINDOW_REVCOMP). Every byte that clean()
+ * (SswJniAligner.java:71-79) would turn into N is stored as N; case is not kept (the aligner ignores it). */
+#define CUDASW_WINDOW_REVCOMP 1
+typedef struct cudasw_window {
+    int32_t contig;
+    int32_t flags;
+    int64_t start, end;
+} cudasw_window;
+
+/* `bases` holds the contigs back to back (raw ASCII, any case), contig c = bases[contig_off[c] .. contig_off[c+1]).
+ * Replaces any previously loaded reference; n_contigs == 0 unloads. */
+int cudasw_reference_load(cudasw_t* h, int32_t n_contigs, const uint8_t* bases, const int64_t* contig_off);
+/* getSubsequenceAt for one window of n_win segments: writes upper-case ACGT/N to `out`; returns the length or <0. */
+int cudasw_reference_fetch(cudasw_t* h, const cudasw_window* win, int32_t n_win, uint8_t* out, int64_t out_cap);
+/* cudasw_align_batch with windows named instead of shipped: pair i aligns seq_blob[seq_off[i]..seq_off[i+1]) inside
+ * the concatenation of win[win_off[i] .. win_off[i+1]). A descriptor outside the loaded reference, or an empty
+ * window, gives that pair status CUDASW_EINVAL. Results are identical to cudasw_align_batch on the fetched bytes. */
+int cudasw_align_batch_windows(cudasw_t* h, int64_t n_pairs, const uint8_t* seq_blob, const int64_t* seq_off,
+                               const cudasw_window* win, const int64_t* win_off, cudasw_result* out,
+                               uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used);
+
 /* Device-memory helpers so a torch-free host (the JNI shim, the ctypes mirror) can stage inputs. */
 int cudasw_device_alloc(cudasw_t* h, size_t bytes, void** dptr);
 int cudasw_device_free(cudasw_t* h, void* dptr);
@@ -123,6 +150,30 @@ int64_t cudasw_processed(cudasw_t* h);   /* flushed, not yet polled */
  * is done, 0 if it is still pending, <0 on error (unknown ticket -> CUDASW_EINVAL). */
 int cudasw_poll(cudasw_t* h, int64_t ticket, cudasw_result* res, uint32_t* cigar,
                 int32_t cigar_cap, int32_t* cigar_len);
+
+/* ---- Several GPUs behind one handle, for a single host process such as the JVM (the reference's
+ * own worker pool is in-process: AnnotateInexactHomology.java:17-21). A batch is cut into contiguous slices of
+ * balanced cost (sum of query_len * window_len), one per GPU, each driven by its own host thread and streams; results
+ * land at the pairs' original ordinals. No exchange step exists between pairs, hence no collective.
+ * devices == NULL or n_devices <= 0 selects every visible device. CIGAR words of GPU d are written to its own
+ * region of cigar_blob (the blob is not compact; cigar_off is absolute), *cigar_used = words used in total, or on
+ * CUDASW_ENOMEM a capacity with which a retry succeeds. Results are identical to cudasw_align_batch. */
+typedef struct cudasw_multi cudasw_multi_t;
+int cudasw_multi_create(const cudasw_scoring* scoring, const int* devices, int n_devices, cudasw_multi_t** out);
+void cudasw_multi_destroy(cudasw_multi_t* m);
+int cudasw_multi_device_count(cudasw_multi_t* m);
+int cudasw_multi_align_batch(cudasw_multi_t* m, int64_t n_pairs,
+                             const uint8_t* seq_blob, const int64_t* seq_off,
+                             const uint8_t* ref_blob, const int64_t* ref_off,
+                             cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used);
+/* The reference is replicated on every GPU of the handle (one-time, outside any timed path). */
+int cudasw_multi_reference_load(cudasw_multi_t* m, int32_t n_contigs, const uint8_t* bases, const int64_t* contig_off);
+int cudasw_multi_align_batch_windows(cudasw_multi_t* m, int64_t n_pairs, const uint8_t* seq_blob, const int64_t* seq_off,
+                                     const cudasw_window* win, const int64_t* win_off, cudasw_result* out,
+                                     uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used);
+/* Stats of GPU `idx` for the last batch and the slice [first_pair, first_pair + n_pairs) it was given. */
+int cudasw_multi_get_stats(cudasw_multi_t* m, int idx, cudasw_stats* out, int64_t* first_pair, int64_t* n_pairs);
+const char* cudasw_multi_last_error(cudasw_multi_t* m); /* m may be NULL: last create() error */
 
 int cudasw_get_stats(cudasw_t* h, cudasw_stats* out);
 /* Which score-pass kernel variant a query of `query_len` rows is dispatched to: lanes per pair (G),

@@ -253,3 +253,193 @@ def test_warp_traceback_wide_bands(aligner, oracle, monkeypatch):
                 refs.append(flank + a + b + flank)
     bad, undef = _compare(aligner, oracle, seqs, refs)
     assert bad == [] and undef == 0, bad[:3]
+
+
+# ---- device-resident reference + window descriptors
+_COMP = bytes.maketrans(b"ACGTN", b"TGCAN")
+
+
+def _toy_genome(rng):
+    """contigs with lower case, N runs and stray IUPAC codes (all of which clean() maps the way the packing does)"""
+    contigs = []
+    for L in (70001, 33, 12345, 1, 40000):
+        c = rng.choice(list(b"ACGT"), size=L).astype(np.uint8)
+        for _ in range(max(1, L // 4000)):
+            p = int(rng.integers(0, L))
+            c[p:p + int(rng.integers(1, 60))] = ord("N")
+        low = rng.random(L) < 0.1
+        c[low] |= 0x20
+        odd = rng.random(L) < 0.001
+        c[odd] = ord("R")
+        contigs.append(c.tobytes())
+    return contigs
+
+
+def _clean(b):
+    u = bytes(b).upper()
+    return bytes(x if x in b"ACGT" else ord("N") for x in u)
+
+
+def test_reference_fetch_matches_getSubsequenceAt():
+    import gridss_b200 as gb
+
+    rng = np.random.default_rng(11)
+    al = gb.CudaAligner()
+    contigs = _toy_genome(rng)
+    al.load_reference(contigs)
+    for _ in range(300):
+        c = int(rng.integers(0, len(contigs)))
+        L = len(contigs[c])
+        s = int(rng.integers(0, L))
+        e = int(rng.integers(s, min(L, s + 3000) + 1))
+        want = _clean(contigs[c][s:e])
+        assert al.get_subsequence(c, s, e) == want
+        assert al.get_subsequence(c, s, e, revcomp=True) == want.translate(_COMP)[::-1]
+    assert al.get_subsequence(1, 0, 33) == _clean(contigs[1])
+    with pytest.raises(ValueError):
+        al.get_subsequence(1, 0, 34)
+    with pytest.raises(ValueError):
+        al.get_subsequence(9, 0, 1)
+    al.close()
+
+
+def test_window_descriptors_match_shipped_bytes(oracle):
+    """cudasw_align_batch_windows == cudasw_align_batch on the same windows fetched on the host == oracle"""
+    import gridss_b200 as gb
+    from gridss_b200.aligner import pack
+
+    rng = np.random.default_rng(12)
+    al = gb.CudaAligner()
+    contigs = _toy_genome(rng)
+    al.load_reference(contigs)
+    n = 3000
+    seqs, refs, segs, win_off = [], [], [], [0]
+    for i in range(n):
+        nseg = 1 if i % 3 else 2  # BreakpointHomology-style two-piece windows every third pair
+        w = b""
+        for _ in range(nseg):
+            c = int(rng.choice([0, 2, 4]))
+            L = len(contigs[c])
+            wl = int(rng.integers(50, 2500))
+            s = int(rng.integers(0, L - wl))
+            rcf = int(rng.integers(0, 2))
+            piece = _clean(contigs[c][s:s + wl])
+            w += piece.translate(_COMP)[::-1] if rcf else piece
+            segs.append((c, rcf, s, s + wl))
+        win_off.append(len(segs))
+        ql = int(rng.integers(20, min(400, len(w))))
+        qs = int(rng.integers(0, len(w) - ql))
+        q = bytearray(w[qs:qs + ql])
+        for _ in range(ql // 25):
+            q[int(rng.integers(0, ql))] = int(rng.choice(list(b"ACGT")))
+        if i % 5 == 0:
+            p = int(rng.integers(1, ql - 1))
+            del q[p:p + int(rng.integers(1, 12))]
+        seqs.append(bytes(q))
+        refs.append(w)
+    sb, so = pack(seqs)
+    rb, ro = pack(refs)
+    win = np.array(segs, dtype=gb.WINDOW_DTYPE)
+    woff = np.array(win_off, dtype=np.int64)
+    res_w, cig_w = al.align_blobs_windows(sb, so, win, woff)
+    assert al.stats()["h2d_bytes"] < int(so[-1]) + 64 * n + 1024  # no window bytes crossed PCIe
+    res_b, cig_b = al.align_blobs(sb, so, rb, ro)
+    m = oracle.model_align_blobs(sb, so, rb, ro, threads=16)
+    for f in FIELDS:
+        assert np.array_equal(res_w[f], res_b[f]), f
+        assert np.array_equal(res_w[f], m.res[f]), f
+    for i in range(n):
+        assert _cig(res_w, cig_w, i) == _cig(res_b, cig_b, i)
+        assert _cig(res_w, cig_w, i) == tuple(int(x) for x in m.cig[m.res[i]["cigar_off"]: m.res[i]["cigar_off"] + m.res[i]["cigar_len"]])
+
+    # a bad descriptor fails its own pair only
+    win2 = win.copy()
+    win2[woff[7]]["end"] = len(contigs[win2[woff[7]]["contig"]]) + 5
+    win2[woff[8]]["contig"] = 99
+    res2, cig2 = al.align_blobs_windows(sb, so, win2, woff)
+    assert res2[7]["status"] == -1 and res2[8]["status"] == -1
+    ok = np.ones(n, dtype=bool)
+    ok[[7, 8]] = False
+    for f in FIELDS:
+        assert np.array_equal(res2[f][ok], res_b[f][ok]), f
+    al.close()
+
+
+def test_windows_without_reference_is_an_error(aligner):
+    import gridss_b200 as gb
+    from gridss_b200.aligner import pack
+
+    al = gb.CudaAligner()
+    sb, so = pack([b"ACGT"])
+    win = np.zeros(1, dtype=gb.WINDOW_DTYPE)
+    with pytest.raises(gb.CudaSwError):
+        al.align_blobs_windows(sb, so, win, np.array([0, 1], dtype=np.int64))
+    al.close()
+
+
+# ---- several engines behind one handle (cudasw_multi_*, SURVEY.md §8e); on a one-GPU box the slices share device 0
+def _visible_devices():
+    import gridss_b200 as gb
+
+    n = gb.load_library().cudasw_device_count()
+    return list(range(n)) if n > 1 else [0, 0, 0]
+
+
+def test_multi_handle_matches_single(aligner, synth):
+    import gridss_b200 as gb
+
+    ma = gb.MultiGpuAligner(devices=_visible_devices())
+    for cfg, n in ((4, 6000), (3, 900)):
+        sb, so, rb, ro = synth.generate(cfg, n)
+        res1, cig1 = aligner.align_blobs(sb, so, rb, ro)
+        resm, cigm = ma.align_blobs(sb, so, rb, ro)
+        for f in FIELDS:
+            assert np.array_equal(res1[f], resm[f]), f
+        assert all(_cig(res1, cig1, i) == _cig(resm, cigm, i) for i in range(n))
+        sl = ma.slice_stats()
+        assert sum(s["pairs"] for s in sl) == n and all(s["pairs"] > 0 for s in sl)
+        cost = [float((np.diff(so)[s["first_pair"]: s["first_pair"] + s["pairs"]] * np.diff(ro)[s["first_pair"]: s["first_pair"] + s["pairs"]]).sum()) for s in sl]
+        assert max(cost) < 1.25 * min(cost) + 3e7  # slices are cost-balanced
+    # a CIGAR blob that is too small is reported with a capacity that works
+    sb, so, rb, ro = synth.generate(4, 3000)
+    small = np.zeros(3000, dtype=np.uint32)
+    resm, cigm = ma.align_blobs(sb, so, rb, ro, cig=small)
+    res1, cig1 = aligner.align_blobs(sb, so, rb, ro)
+    assert all(_cig(res1, cig1, i) == _cig(resm, cigm, i) for i in range(3000))
+    # fewer pairs than engines, and the single-pair interface
+    a = ma.align_smith_waterman(b"AAACCCCCCCCCCCCCTTAATTAATTAATTTT", b"AAACCCCCCCCCCCCCGTTAATTAATTAATTTT")
+    assert (a.getStartPosition(), a.getCigar()) == (0, "16M1D16M")
+    ma.close()
+
+
+def test_multi_handle_windows(aligner):
+    import gridss_b200 as gb
+    from gridss_b200.aligner import pack
+
+    rng = np.random.default_rng(14)
+    contigs = _toy_genome(rng)
+    ma = gb.MultiGpuAligner(devices=_visible_devices())
+    ma.load_reference(contigs)
+    seqs, refs, segs = [], [], []
+    for i in range(2000):
+        c = int(rng.choice([0, 2, 4]))
+        wl = int(rng.integers(100, 3000))
+        s = int(rng.integers(0, len(contigs[c]) - wl))
+        rcf = int(rng.integers(0, 2))
+        w = _clean(contigs[c][s:s + wl])
+        w = w.translate(_COMP)[::-1] if rcf else w
+        ql = int(rng.integers(30, min(300, wl)))
+        qs = int(rng.integers(0, wl - ql))
+        seqs.append(w[qs:qs + ql])
+        refs.append(w)
+        segs.append((c, rcf, s, s + wl))
+    sb, so = pack(seqs)
+    rb, ro = pack(refs)
+    win = np.array(segs, dtype=gb.WINDOW_DTYPE)
+    woff = np.arange(len(segs) + 1, dtype=np.int64)
+    resm, cigm = ma.align_blobs_windows(sb, so, win, woff)
+    res1, cig1 = aligner.align_blobs(sb, so, rb, ro)
+    for f in FIELDS:
+        assert np.array_equal(res1[f], resm[f]), f
+    assert all(_cig(res1, cig1, i) == _cig(resm, cigm, i) for i in range(len(segs)))
+    ma.close()
