@@ -93,6 +93,8 @@ struct cudasw {
     DevBuf<uint16_t> anchor;  // per pair: seed estimate of the alignment's first window column / 4 (scheduling hint)
     DevBuf<uint8_t> wflags;  // per pair: window contains N (xor-selector flavour)
     DevBuf<uint8_t> tb_pool;
+    DevBuf<int> tb_esc;   // escalation lists between the traceback frame classes
+    DevBuf<int> tb_band;  // per pair: band the traceback reached so far (0 = not started)
     // device-resident reference genome (cudasw_reference_load) and the window descriptors of the current batch
     DevBuf<uint32_t> ref2bit, refN;
     DevBuf<int64_t> d_contig_off, d_seg_off;
@@ -265,7 +267,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->seq_off.release(); h->ref_off.release(); h->keys.release(); h->keys_alt.release();
     h->vals.release(); h->vals_alt.release(); h->retry_a.release(); h->retry_b.release();
     h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
-    h->cub_tmp.release(); h->tb_pool.release(); h->wflags.release(); h->anchor.release();
+    h->cub_tmp.release(); h->tb_pool.release(); h->tb_band.release(); h->tb_esc.release(); h->wflags.release(); h->anchor.release();
     h->ref2bit.release(); h->refN.release(); h->d_contig_off.release(); h->d_seg_off.release(); h->d_segs.release();
     if (h->d_hist) cudaFree(h->d_hist);
     if (h->d_pool) cudaFree(h->d_pool);
@@ -412,46 +414,142 @@ int cudasw::finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, in
     // Pairs are sorted by estimated banded cells: the widest go to the warp-cooperative kernel (one warp each, on
     // an auxiliary stream), the rest to the one-thread-per-pair kernel in descending cost order.
     {
-        long long wide_cells = 2048;  // measured on B200: profiles/tb_sweep_r01.txt
+        // default: the one-thread kernel keeps bands up to kTbThreadBand in registers, wider pairs take a warp each;
+        // CUDASW_TB_WIDE_CELLS additionally sends every pair above that many banded cells to the warp kernel (0 = all)
+        long long wide_cells = -1;
         if (const char* e = getenv("CUDASW_TB_WIDE_CELLS")) wide_cells = atoll(e);
+        CK(cudaMemsetAsync(tb_band.p, 0, (size_t)n * sizeof(int), st));
         TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
         int* retry_count = reinterpret_cast<int*>(d_counters + 2);
         int* wide_count = reinterpret_cast<int*>(d_counters + 3);
         const int* list = nullptr;  // first round: every pair
         int c = (int)n;
         int* retry_out = retry_a.p;
+        bool stuck = false;
         for (int round = 0; round < 64 && c > 0; round++) {
             CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));      // pool
             CK(cudaMemsetAsync(d_counters + 2, 0, 2 * sizeof(unsigned long long), st));  // retry + wide counters
-            tb_keys_kernel<<<(c + 255) / 256, 256, 0, st>>>(list, c, fwd_c, rev_c, res_c, wide_cells, keys.p, vals.p, wide_count);
+            CK(cudaMemsetAsync(d_hist, 0, 8 * sizeof(int), st));                         // pairs per frame class
+            CK(cudaMemsetAsync(d_counters + 7, 0, sizeof(unsigned long long), st));      // scratch estimate
+            // few pairs cannot fill the machine with one thread each: long ones then take a warp each
+            // (and run all their band passes in one kernel: a kernel boundary between passes costs the sum of the slowest
+            // pairs of each stage instead of the slowest pair overall)
+            const long long wc = wide_cells >= 0 ? wide_cells : (c < 8192 ? 2048 : -1);
+            tb_keys_kernel<<<(c + 255) / 256, 256, 0, st>>>(list, c, fwd_c, rev_c, res_c, wc, c < 8192 ? 1 : 0, tb_band.p, keys.p, vals.p, wide_count,
+                                                            d_hist, d_counters + 7);
             launches++;
-            CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, c, 0, 22, st));
+            CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, c, 0, 23, st));
             launches += 3;
             CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            CK(cudaMemcpyAsync(h_hist, d_hist, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
             const int nwide = *reinterpret_cast<int*>(h_counters + 3);
+            {
+                // the scratch pool follows the demand of the batch (first band passes + a margin for doublings)
+                const unsigned long long est = 3ull * h_counters[7] + ((unsigned long long)256 << 20);
+                if (est > tb_pool_bytes && !getenv("CUDASW_TB_POOL_MB")) {
+                    size_t free_b = 0, total_b = 0;
+                    CK(cudaMemGetInfo(&free_b, &total_b));
+                    const size_t want = (size_t)std::min<unsigned long long>(est, (unsigned long long)((free_b + tb_pool_bytes) / 2));
+                    if (want > tb_pool_bytes) {
+                        tb_pool.release();
+                        tb_pool_bytes = 0;
+                        CK(tb_pool.ensure(want));
+                        tb_pool_bytes = want;
+                        pool = TbPool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+                    }
+                }
+            }
+            const int nbig = reinterpret_cast<int*>(h_counters + 3)[1];
+            // escalation lists: kTbClasses + 2 arrays of c ints (list k = input of thread class k, list kTbClasses = input
+            // of the small warp kernel, list kTbClasses + 1 = input of the big one); their counters live in d_hist[8 ..]
+            CK(tb_esc.ensure((size_t)(kTbClasses + 2) * (size_t)c));
+            CK(cudaMemsetAsync(d_hist + 8, 0, 8 * sizeof(int), st));
+            int* esc_small = tb_esc.p + (size_t)kTbClasses * c;
+            int* esc_big = tb_esc.p + (size_t)(kTbClasses + 1) * c;
+            int* esc_small_count = d_hist + 8 + kTbClasses;
+            int* esc_big_count = d_hist + 8 + kTbClasses + 1;
             if (nwide > 0) {
                 CK(cudaEventRecord(fork_ev, st));
-                CK(cudaStreamWaitEvent(aux[0], fork_ev, 0));
-                sw_traceback_warp_kernel<<<(nwide + 3) / 4, 128, 0, aux[0]>>>(vals_alt.p, nwide, io, fwd_c, rev_c, tc, pool,
-                                                                              res_c, cig.p, (unsigned long long)cigar_cap,
-                                                                              d_counters + 1, retry_out, retry_count);
-                launches++;
-                CK(cudaEventRecord(join_ev[0], aux[0]));
+                if (nbig > 0) {
+                    CK(cudaStreamWaitEvent(aux[0], fork_ev, 0));
+                    sw_traceback_warp_kernel<64><<<(nbig + 3) / 4, 128, 0, aux[0]>>>(vals_alt.p, nbig, nullptr, nullptr, nullptr, io, fwd_c, rev_c, tc,
+                                                                                     pool, res_c, cig.p, (unsigned long long)cigar_cap,
+                                                                                     d_counters + 1, retry_out, retry_count, tb_band.p);
+                    launches++;
+                    CK(cudaEventRecord(join_ev[0], aux[0]));
+                }
+                if (nwide > nbig) {
+                    CK(cudaStreamWaitEvent(aux[1], fork_ev, 0));
+                    sw_traceback_warp_kernel<16><<<(nwide - nbig + 3) / 4, 128, 0, aux[1]>>>(vals_alt.p + nbig, nwide - nbig, nullptr, esc_big,
+                                                                                             esc_big_count, io, fwd_c, rev_c, tc, pool, res_c, cig.p,
+                                                                                             (unsigned long long)cigar_cap, d_counters + 1, retry_out,
+                                                                                             retry_count, tb_band.p);
+                    launches++;
+                    CK(cudaEventRecord(join_ev[1], aux[1]));
+                }
             }
-            if (c > nwide) {
-                sw_traceback_kernel<<<(c - nwide + 127) / 128, 128, 0, st>>>(vals_alt.p + nwide, c - nwide, io, fwd_c, rev_c, tc,
-                                                                            pool, res_c, cig.p, (unsigned long long)cigar_cap,
-                                                                            d_counters + 1, retry_out, retry_count);
+            {
+                // One launch per frame class, narrowest first: class k appends the pairs that outgrow its frame to the
+                // escalation list that class k+1 reads behind its own (sorted) list, and the widest class hands over to
+                // a second warp-kernel launch, all stream-ordered. Class slot 5 = pairs with nothing to trace.
+                int start = nwide;
+                int cstart[kTbClasses + 1];
+                for (int k = 0; k <= kTbClasses; k++) { cstart[k] = start; start += h_hist[k]; }
+                for (int k = 0; k < kTbClasses; k++) {
+                    const int own = h_hist[k];
+                    const int* esc_in = k == 0 ? nullptr : tb_esc.p + (size_t)k * c;
+                    const int* esc_in_count = k == 0 ? nullptr : d_hist + 8 + k;
+                    int* esc_out = tb_esc.p + (size_t)(k + 1) * c;
+                    int* esc_out_count = d_hist + 8 + k + 1;
+                    // the escalated pairs are not known to the host: the grid covers the own list plus a few CTAs per SM
+                    // and strides over whatever else there is
+                    const int grid = (own + 127) / 128 + (k == 0 ? 0 : 148 * 2);
+                    if (grid == 0) continue;
+#define CUSW_TB_LAUNCH(B)                                                                                              \
+    sw_traceback_kernel<B><<<grid, 128, 0, st>>>(vals_alt.p + cstart[k], own, esc_in, esc_in_count, esc_out, esc_out_count, io, \
+                                                 fwd_c, rev_c, tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,     \
+                                                 d_counters + 1, retry_out, retry_count, tb_band.p)
+                    switch (k) {
+                        case 0: CUSW_TB_LAUNCH(1); break;
+                        case 1: CUSW_TB_LAUNCH(2); break;
+                        case 2: CUSW_TB_LAUNCH(4); break;
+                        case 3: CUSW_TB_LAUNCH(8); break;
+                        default: CUSW_TB_LAUNCH(16); break;
+                    }
+                    launches++;
+                }
+                if (h_hist[kTbClasses] > 0) {  // score 0 / failed pairs: "1M(q-1)S" or nothing; any class will do
+                    const int k = kTbClasses, own = h_hist[kTbClasses];
+                    const int grid = (own + 127) / 128;
+                    const int *esc_in = nullptr, *esc_in_count = nullptr;
+                    int* esc_out = tb_esc.p;
+                    int* esc_out_count = d_hist + 8;
+                    CUSW_TB_LAUNCH(1);
+                    launches++;
+                }
+#undef CUSW_TB_LAUNCH
+                // pairs that outgrew the widest frame, then those that outgrew the small warp kernel (from either launch)
+                sw_traceback_warp_kernel<16><<<148 * 4, 128, 0, st>>>(esc_small, 0, esc_small_count, esc_big, esc_big_count, io, fwd_c,
+                                                                      rev_c, tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,
+                                                                      d_counters + 1, retry_out, retry_count, tb_band.p);
+                launches++;
+                if (nwide > nbig) CK(cudaStreamWaitEvent(st, join_ev[1], 0));
+                sw_traceback_warp_kernel<64><<<148 * 3, 128, 0, st>>>(esc_big, 0, esc_big_count, nullptr, nullptr, io, fwd_c,
+                                                                      rev_c, tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,
+                                                                      d_counters + 1, retry_out, retry_count, tb_band.p);
                 launches++;
             }
-            if (nwide > 0) CK(cudaStreamWaitEvent(st, join_ev[0], 0));
+            if (nbig > 0) CK(cudaStreamWaitEvent(st, join_ev[0], 0));
             CK(cudaEventRecord(ev[5], st));
             CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
             int nretry = *reinterpret_cast<int*>(h_counters + 2);
             if (nretry == 0) { c = 0; break; }
-            if (nretry == c && round > 0) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
+            // a whole round may legitimately come back once (every pair handed from the thread kernel to the warp
+            // kernel); twice in a row means no pair fits the scratch pool
+            if (nretry == c && stuck) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
+            stuck = nretry == c;
             list = retry_out;
             retry_out = (retry_out == retry_a.p) ? retry_b.p : retry_a.p;
             c = nretry;
@@ -540,7 +638,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(enc_ref.ensure((size_t)total_w + 16));
     CK(keys.ensure(n)); CK(keys_alt.ensure(n)); CK(vals.ensure(n)); CK(vals_alt.ensure(n));
     CK(retry_a.ensure(n)); CK(retry_b.ensure(n));
-    CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n)); CK(wflags.ensure(n)); CK(anchor.ensure(n));
+    CK(fwd.ensure(n)); CK(rev.ensure(n)); CK(res.ensure(n)); CK(wflags.ensure(n)); CK(anchor.ensure(n)); CK(tb_band.ensure(n));
     CK(cig.ensure((size_t)std::max<int64_t>(cigar_cap, 1)));
     {
         size_t cub_bytes = 0;

@@ -768,8 +768,10 @@ __device__ __forceinline__ int tb_sub(const TbConst& tc, uint32_t qb, uint32_t r
 
 // Walks the direction matrix. When `outp` != nullptr writes ops (reversed order resolved by index).
 // Returns number of M/I/D ops, or a negative status.
+// center < 0: the reference's flat layout (row i starts at its first in-band column). center >= 0: band-frame layout
+// of sw_traceback_kernel, cell (i, j) at dir[width_d * i + (j - i + center)].
 __device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, int readLen,
-                       int refLen, uint32_t* outp, int total_ops) {
+                       int refLen, uint32_t* outp, int total_ops, int center = -1) {
     int i = readLen - 1, j = refLen - 1;
     int e = 0, l = 0, state = 2;
     int op = 0, prev_op = 0;  // 0 = M, 1 = I, 2 = D
@@ -778,7 +780,7 @@ __device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, i
         const int jj = j - xi;
         const int lo = max(i - band, 0) - xi, hi = min(i + band, refLen - 1) - xi;
         if (jj < lo || jj > hi) return CUDASW_EUNDEF;
-        const uint32_t b = dir[(int64_t)width_d * i + jj];
+        const uint32_t b = dir[(int64_t)width_d * i + (center >= 0 ? j - i + center : jj)];
         int dv = state == 2 ? (int)(b & 7u) : state == 0 ? (2 + (int)((b >> 3) & 1u)) : (4 + (int)((b >> 4) & 1u));
         switch (dv) {
             case 1: --i; --j; state = 2; op = 0; break;
@@ -809,27 +811,53 @@ __device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, i
     return l;
 }
 
-// Sort keys for the traceback: estimated banded cells readLen * (2*band0 + 1), descending, so that the threads
-// of a warp get pairs of similar cost and the long ones start first; counts the pairs handed to the warp kernel.
+// Sort keys for the traceback: estimated banded cells readLen * (2*band + 1), descending, so that the threads of a
+// warp get pairs of similar cost and the long ones start first. A pair whose (starting) band exceeds kTbThreadBand
+// goes to the warp-cooperative kernel; `tb_band` remembers the band a pair reached in an earlier round.
 constexpr uint32_t kTbKeyMax = (1u << 22) - 1u;
+constexpr int kTbThreadBand = 16;  // widest band sw_traceback_kernel keeps in registers (33 diagonals)
+constexpr int kTbClasses = 5;      // register frames of half-width 1, 2, 4, 8, 16
+constexpr int kTbWarpSmallD = 16;  // sw_traceback_warp_kernel<16>: bands of up to 32*16 diagonals; <64>: everything else
+__host__ __device__ __forceinline__ int tb_class_of(int band) { return band <= 1 ? 0 : band <= 2 ? 1 : band <= 4 ? 2 : band <= 8 ? 3 : 4; }
+__host__ __device__ __forceinline__ int tb_frame_bytes(int cls) { return ((2 << cls) + 1 + 3) & ~3; }  // direction bytes per row
+// Keys: warp-kernel pairs first (by descending cost), then the one-thread pairs grouped by frame class and, inside a
+// class, by descending read length: the 32 pairs of a warp then run the same instantiation for about as many rows.
+// cls_count[c] = pairs of class c; est_bytes = scratch the first band pass of every pair will ask for.
 __global__ void tb_keys_kernel(const int* __restrict__ list, int n, const int4* __restrict__ fwd,
                                const int4* __restrict__ rev, const cudasw_result* __restrict__ res,
-                               long long wide_cells, uint32_t* __restrict__ keys, int* __restrict__ vals,
-                               int* __restrict__ wide_count) {
+                               long long wide_cells, int all_big, const int* __restrict__ tb_band, uint32_t* __restrict__ keys,
+                               int* __restrict__ vals, int* __restrict__ wide_count, int* __restrict__ cls_count,
+                               unsigned long long* __restrict__ est_bytes) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= n) return;
     const int pair = list ? list[tid] : tid;
-    long long cost = 0;
+    uint32_t key = ((uint32_t)kTbClasses << 19) | 0x7FFFu | (1u << 22);  // nothing to trace: sorts last (class slot 5)
+    int cls = kTbClasses;
     if (res[pair].status == CUDASW_OK && fwd[pair].x > 0) {
         const int4 rv = rev[pair];
         const int refLen = rv.y + 1, readLen = rv.z + 1;
-        cost = (long long)readLen * (2 * (abs(refLen - readLen) + 1) + 1);
-        if (cost > wide_cells) atomicAdd(wide_count, 1);
-        else if (cost > (long long)kTbKeyMax - 1) cost = kTbKeyMax - 1;  // below every warp-kernel pair
+        const int band = max(abs(refLen - readLen) + 1, tb_band[pair]);
+        long long cost = (long long)readLen * (2 * band + 1);
+        // wide_cells < 0: the default rule; >= 0: additionally every pair above that many cells (0 = all of them)
+        const bool wide = band > kTbThreadBand || (wide_cells >= 0 && cost > wide_cells);
+        if (wide) {
+            // warp-kernel pairs: those that start beyond 16 diagonals per lane first (their kernel holds more state
+            // per thread), each group by descending cost; wide_count = {all, big}
+            const bool big = all_big || 2 * band + 1 > 32 * kTbWarpSmallD;
+            atomicAdd(wide_count, 1);
+            if (big) atomicAdd(wide_count + 1, 1);
+            if (cost > (long long)(kTbKeyMax >> 1) - 1) cost = (kTbKeyMax >> 1) - 1;
+            key = (big ? 0u : (1u << 21)) | ((kTbKeyMax >> 1) - (uint32_t)cost);
+            cls = -1;
+            atomicAdd(est_bytes, (unsigned long long)readLen * (unsigned long long)(2 * band + 1) + 16ull);
+        } else {
+            cls = tb_class_of(band);
+            key = (1u << 22) | ((uint32_t)cls << 19) | (0x7FFFu - (uint32_t)min(readLen, 0x7FFF));
+            atomicAdd(est_bytes, (unsigned long long)readLen * (unsigned long long)tb_frame_bytes(cls) + 16ull);
+        }
     }
-    // warp-kernel pairs sort first (key 0 side), then by descending cost
-    uint32_t k = cost > wide_cells ? 0u : kTbKeyMax - (uint32_t)cost;
-    keys[tid] = k;
+    if (cls >= 0) atomicAdd(&cls_count[cls], 1);
+    keys[tid] = key;
     vals[tid] = pair;
 }
 
@@ -838,7 +866,7 @@ __device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begi
                                         int read_end, int nbody, const uint8_t* dirp, int width_d, int band,
                                         int readLen, int refLen, cudasw_result r, cudasw_result* __restrict__ res,
                                         uint32_t* __restrict__ cig, unsigned long long cig_cap,
-                                        unsigned long long* __restrict__ cig_used) {
+                                        unsigned long long* __restrict__ cig_used, int center = -1) {
     const int lead = read_begin != 0;
     const int tail = (q - read_end - 1) != 0;
     const int nops = nbody + lead + tail;
@@ -854,7 +882,7 @@ __device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begi
         uint32_t* o = cig + coff;
         if (lead) *o++ = ((uint32_t)read_begin << 4) | CUDASW_CIGAR_S;
         if (score <= 0) *o = (1u << 4) | CUDASW_CIGAR_M;
-        else tb_walk(dirp, width_d, band, readLen, refLen, o, nbody);
+        else tb_walk(dirp, width_d, band, readLen, refLen, o, nbody, center);
         if (tail) o[nbody] = ((uint32_t)(q - read_end - 1) << 4) | CUDASW_CIGAR_S;
     } else {
         r.status = CUDASW_ENOMEM;
@@ -862,101 +890,143 @@ __device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begi
     res[pair] = r;
 }
 
+}  // namespace cusw
+#include "tb_warp.cuh"
+namespace cusw {
+
+// Banded DP of one pair by one thread with the whole band in registers. The frame is WMAX = 2*BMAX + 1 diagonals
+// centred on the main diagonal (x = j - i + BMAX); a narrower band simply leaves the outer slots idle. Same cell
+// arithmetic and border rules as tb_dp_warp (tb_warp.cuh header): out-of-band neighbours read as 0, row 0 uses
+// -gapOpen / -gapExtend, plus the reference's `edge` quirk. The window bytes of the frame slide along in registers
+// (one new byte per row) and the direction bytes of a row leave as packed 32-bit words.
+template <int BMAX>
+__device__ int tb_dp_thread(const TbConst& tc, const uint8_t* __restrict__ ref, const uint8_t* __restrict__ read,
+                            int refLen, int readLen, int band, uint8_t* __restrict__ dir) {
+    constexpr int WMAX = 2 * BMAX + 1;
+    constexpr int WP = (WMAX + 3) & ~3;
+    int H[WMAX], E[WMAX];
+    uint32_t rw[WMAX];
+#pragma unroll
+    for (int x = 0; x < WMAX; x++) {
+        H[x] = 0; E[x] = 0;
+        const int j = x - BMAX;
+        rw[x] = (unsigned)j < (unsigned)refLen ? (uint32_t)ref[j] : 0u;
+    }
+    int mx = 0;
+    for (int i = 0; i < readLen; i++) {
+        const int beg = max(i - band, 0);
+        const int end = min(i + band, refLen - 1);
+        const int endp = min(i - 1 + band, refLen - 1);  // last column of the previous row
+        const bool quirk = i >= 1 && i <= band + 1 && end == refLen - 1 && endp == end && end <= 2 * band + 1;
+        const uint32_t qb = read[i];
+        const int j0 = i - BMAX;
+        int hleft = 0, fgap = 0;
+        int cur_h = H[0];
+        uint32_t* drow = reinterpret_cast<uint32_t*>(dir + (long long)WP * i);
+        uint32_t dw = 0;
+#pragma unroll
+        for (int x = 0; x < WMAX; x++) {
+            const int j = j0 + x;
+            const int nxt_h = x + 1 < WMAX ? H[x + 1 < WMAX ? x + 1 : 0] : 0;
+            const int nxt_e = x + 1 < WMAX ? E[x + 1 < WMAX ? x + 1 : 0] : 0;
+            if (j >= beg && j <= end) {
+                int up_h = 0, up_e = 0;
+                if (j <= endp && !(quirk && j == end)) { up_h = nxt_h; up_e = nxt_e; }
+                const int hdiag = (i >= 1 && j >= 1) ? cur_h : 0;
+                int h, e;
+                uint8_t dv;
+                tb_cell(tc, i, up_h, up_e, hdiag, tb_sub(tc, qb, rw[x]), hleft, fgap, mx, h, e, dv);
+                H[x] = h;
+                E[x] = e;
+                dw |= (uint32_t)dv << (8 * (x & 3));
+            }
+            cur_h = nxt_h;
+            if ((x & 3) == 3 || x == WMAX - 1) { drow[x >> 2] = dw; dw = 0; }
+        }
+        // slide the window bytes: the frame of row i+1 starts one column further right
+#pragma unroll
+        for (int x = 0; x + 1 < WMAX; x++) rw[x] = rw[x + 1];
+        const int jn = i + 1 + BMAX;
+        rw[WMAX - 1] = jn < refLen ? (uint32_t)ref[jn] : 0u;
+    }
+    return mx;
+}
+
+// Phase 3 for pairs whose band fits a register frame: one thread per pair, one instantiation (and launch) per frame
+// class so that a warp never mixes frame widths. Runs the band-doubling loop of banded_sw (ssw.c:630-631) while the
+// band fits THIS frame. A pair that needs a wider band is appended to `esc_out`, the input of the next wider class
+// (launched behind this one on the same stream; the widest class hands over to the warp-cooperative kernel), so the
+// whole escalation chain needs no host round trip. A pair that finds the scratch pool exhausted goes to the retry
+// list of the host loop. tb_band remembers the band reached.
+template <int BMAX>
 __global__ void __launch_bounds__(128)
-sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* __restrict__ fwd,
-                    const int4* __restrict__ rev, TbConst tc, TbPool pool,
+sw_traceback_kernel(const int* __restrict__ list, int n_own, const int* __restrict__ esc_in,
+                    const int* __restrict__ esc_in_count, int* __restrict__ esc_out, int* __restrict__ esc_out_count,
+                    PairIO io, const int4* __restrict__ fwd, const int4* __restrict__ rev, TbConst tc, TbPool pool,
                     cudasw_result* __restrict__ res, uint32_t* __restrict__ cig,
                     unsigned long long cig_cap, unsigned long long* __restrict__ cig_used,
-                    int* __restrict__ retry_list, int* __restrict__ retry_count) {
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= n) return;
-    const int pair = list ? list[tid] : tid;
-    cudasw_result r = res[pair];
-    if (r.status != CUDASW_OK) return;
-    const int q = (int)(io.seq_off[pair + 1] - io.seq_off[pair]);
-    const int4 f = fwd[pair];
-    const int score = f.x;
+                    int* __restrict__ retry_list, int* __restrict__ retry_count, int* __restrict__ tb_band) {
+    const int n_all = n_own + (esc_in_count ? *esc_in_count : 0);
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_all; idx += gridDim.x * blockDim.x) {
+        const int pair = idx < n_own ? list[idx] : esc_in[idx - n_own];
+        cudasw_result r = res[pair];
+        if (r.status != CUDASW_OK) continue;
+        const int q = (int)(io.seq_off[pair + 1] - io.seq_off[pair]);
+        const int4 f = fwd[pair];
+        const int score = f.x;
 
-    int nbody = 0;
-    int ref_begin = -1, read_begin = 0, ref_end = f.y, read_end = f.z;
-    const uint8_t* dirp = nullptr;
-    int width_d = 0, band = 0, readLen = 0, refLen = 0;
+        int nbody = 0;
+        int ref_begin = -1, read_begin = 0, ref_end = f.y, read_end = f.z;
+        const uint8_t* dirp = nullptr;
+        constexpr int width_d = (2 * BMAX + 1 + 3) & ~3;
+        int band = 0, readLen = 0, refLen = 0;
 
-    if (score <= 0) {
-        // no positive cell -> start -1, "1M" + (q-1)S
-        ref_end = -1; read_end = 0;
-        nbody = 1;
-    } else {
-        const int4 rv = rev[pair];
-        if (rv.w != 0) { res[pair].status = CUDASW_ENOMEM; return; }     // strip buffers exhausted
-        if (rv.x != score) { res[pair].status = CUDASW_ECUDA; return; }  // internal inconsistency
-        ref_begin = ref_end - rv.y;
-        read_begin = read_end - rv.z;
-        refLen = ref_end - ref_begin + 1;
-        readLen = read_end - read_begin + 1;
-        const uint8_t* ref = io.enc_ref + io.ref_off[pair] + ref_begin;
-        const uint8_t* read = io.enc_seq + io.seq_off[pair] + read_begin;
-        band = abs(refLen - readLen) + 1;
-        int mx = 0;
-        for (;;) {
-            width_d = 2 * band + 1;
-            const int width = 2 * band + 3;
-            const long long ndir = (long long)width_d * readLen;
-            if (ndir * 3 >= (1ll << 31)) { res[pair].status = CUDASW_ETOOLARGE; return; }
-            const unsigned long long need = (((unsigned long long)width * 8ull + 15ull) & ~15ull) +
-                                            (((unsigned long long)ndir + 15ull) & ~15ull);
-            if (need > pool.cap) { res[pair].status = CUDASW_ETOOLARGE; return; }
-            const unsigned long long off = atomicAdd(pool.used, need);
-            if (off + need > pool.cap) {
-                retry_list[atomicAdd(retry_count, 1)] = pair;
-                return;
-            }
-            int2* he = reinterpret_cast<int2*>(pool.base + off);
-            uint8_t* dir = pool.base + off + (((unsigned long long)width * 8ull + 15ull) & ~15ull);
-            dirp = dir;
-            for (int k = 0; k < width; k++) he[k] = make_int2(0, 0);
-            for (int i = 0; i < readLen; i++) {
-                const int beg = max(i - band, 0);
-                const int end = min(i + band, refLen - 1);
-                const int edge = min(end + 1, width - 1);
-                const int xi = beg;
-                const int xp = max(i - 1 - band, 0);
-                he[0] = make_int2(0, 0);
-                he[edge] = make_int2(0, 0);
-                int fgap = 0, hleft = 0;
-                int hdiag = he[beg - xp].x;
-                const uint32_t qb = read[i];
-                uint8_t* drow = dir + (long long)width_d * i - xi;
-                for (int j = beg; j <= end; j++) {
-                    const int2 up = he[j - xp + 1];
-                    int t1 = i == 0 ? -tc.go : up.x - tc.go;
-                    int t2 = i == 0 ? -tc.ge : up.y - tc.ge;
-                    const int E = max(t1, t2);
-                    const uint32_t dE = t1 > t2 ? 1u : 0u;
-                    t1 = hleft - tc.go;
-                    t2 = fgap - tc.ge;
-                    fgap = max(t1, t2);
-                    const uint32_t dF = t1 > t2 ? 1u : 0u;
-                    const int e1 = max(E, 0), f1 = max(fgap, 0);
-                    const int g = max(e1, f1);
-                    const int d = hdiag + tb_sub(tc, qb, ref[j]);
-                    const int h = max(g, d);
-                    mx = max(mx, h);
-                    const uint32_t dH = (g <= d) ? 1u : (e1 > f1 ? 2u + dE : 4u + dF);
-                    drow[j] = (uint8_t)(dH | (dE << 3) | (dF << 4));
-                    hdiag = up.x;
-                    he[j - xi + 1] = make_int2(h, E);
-                    hleft = h;
+        if (score <= 0) {
+            // no positive cell -> start -1, "1M" + (q-1)S
+            ref_end = -1; read_end = 0;
+            nbody = 1;
+        } else {
+            const int4 rv = rev[pair];
+            if (rv.w != 0) { res[pair].status = CUDASW_ENOMEM; continue; }     // strip buffers exhausted
+            if (rv.x != score) { res[pair].status = CUDASW_ECUDA; continue; }  // internal inconsistency
+            ref_begin = ref_end - rv.y;
+            read_begin = read_end - rv.z;
+            refLen = ref_end - ref_begin + 1;
+            readLen = read_end - read_begin + 1;
+            const uint8_t* ref = io.enc_ref + io.ref_off[pair] + ref_begin;
+            const uint8_t* read = io.enc_seq + io.seq_off[pair] + read_begin;
+            band = max(abs(refLen - readLen) + 1, tb_band[pair]);
+            int mx = 0;
+            bool done = false;
+            for (;;) {
+                if (band > BMAX) {  // a wider frame class, or the warp-cooperative kernel, takes over at this band
+                    tb_band[pair] = band;
+                    esc_out[atomicAdd(esc_out_count, 1)] = pair;
+                    break;
                 }
+                // the reference gives up (exit(1)) when its own direction matrix would not fit an int (ssw.c:580-585)
+                if ((long long)(2 * band + 1) * readLen * 3 >= (1ll << 31)) { res[pair].status = CUDASW_ETOOLARGE; break; }
+                const unsigned long long need = (((unsigned long long)width_d * (unsigned long long)readLen) + 15ull) & ~15ull;
+                if (need > pool.cap) { res[pair].status = CUDASW_ETOOLARGE; break; }
+                const unsigned long long off = dirp ? (unsigned long long)(dirp - pool.base) : atomicAdd(pool.used, need);
+                if (off + need > pool.cap) {
+                    tb_band[pair] = band;
+                    retry_list[atomicAdd(retry_count, 1)] = pair;
+                    break;
+                }
+                uint8_t* dir = pool.base + off;  // a wider band inside the same frame overwrites the failed pass
+                dirp = dir;
+                mx = max(mx, tb_dp_thread<BMAX>(tc, ref, read, refLen, readLen, band, dir));  // the reference never resets its maximum
+                if (mx >= score) { done = true; break; }
+                band *= 2;
             }
-            if (mx >= score) break;
-            band *= 2;
+            if (!done) continue;
+            nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0, BMAX);
+            if (nbody < 0) { res[pair].status = nbody; continue; }
         }
-        nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0);
-        if (nbody < 0) { res[pair].status = nbody; return; }
+        tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen, r,
+                res, cig, cig_cap, cig_used, BMAX);
     }
-    tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen, r,
-            res, cig, cig_cap, cig_used);
 }
 
 #endif  // CUSW_MAIN_TU
@@ -964,23 +1034,27 @@ sw_traceback_kernel(const int* __restrict__ list, int n, PairIO io, const int4* 
 }  // namespace cusw
 
 #ifdef CUSW_MAIN_TU
-#include "tb_warp.cuh"
 namespace cusw {
 
 // One warp per pair of `list` (the pairs sw_traceback_kernel handed over): banded DP by tb_dp_warp, then lane 0
 // walks the direction matrix and emits the CIGAR exactly like the one-thread kernel.
+// DMAX = 16: passes of up to 16 diagonals per lane (bands up to 255) with a small register footprint; a pair that
+// outgrows it is appended to esc_out, the input of the DMAX = 64 instantiation launched behind it (which also has
+// the memory-backed path for even wider bands).
+template <int DMAX>
 __global__ void __launch_bounds__(128)
-sw_traceback_warp_kernel(const int* __restrict__ list, int n, PairIO io, const int4* __restrict__ fwd,
+sw_traceback_warp_kernel(const int* __restrict__ list, int n, const int* __restrict__ n_dev, int* __restrict__ esc_out,
+                         int* __restrict__ esc_out_count, PairIO io, const int4* __restrict__ fwd,
                          const int4* __restrict__ rev, TbConst tc, TbPool pool, cudasw_result* __restrict__ res,
                          uint32_t* __restrict__ cig, unsigned long long cig_cap,
                          unsigned long long* __restrict__ cig_used, int* __restrict__ retry_list,
-                         int* __restrict__ retry_count) {
-    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+                         int* __restrict__ retry_count, int* __restrict__ tb_band) {
     const int lane = threadIdx.x & 31;
-    if (wid >= n) return;
+    if (n_dev) n = *n_dev;  // the list was filled on the device (pairs escalated by sw_traceback_kernel<16>)
+    for (int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; wid < n; wid += (gridDim.x * blockDim.x) >> 5) {
     const int pair = list[wid];
     const cudasw_result r = res[pair];
-    if (r.status != CUDASW_OK) return;
+    if (r.status != CUDASW_OK) continue;
     const int q = (int)(io.seq_off[pair + 1] - io.seq_off[pair]);
     const int4 f = fwd[pair];
     const int4 rv = rev[pair];
@@ -990,15 +1064,21 @@ sw_traceback_warp_kernel(const int* __restrict__ list, int n, PairIO io, const i
     const int refLen = ref_end - ref_begin + 1, readLen = read_end - read_begin + 1;
     const uint8_t* ref = io.enc_ref + io.ref_off[pair] + ref_begin;
     const uint8_t* read = io.enc_seq + io.seq_off[pair] + read_begin;
-    int band = abs(refLen - readLen) + 1;
+    int band = max(abs(refLen - readLen) + 1, tb_band[pair]);  // tb_band: where an earlier round / kernel stopped
     int mx = 0, width_d = 0;
     const uint8_t* dirp = nullptr;
+    bool ok = true;
     for (;;) {
         width_d = 2 * band + 1;
         const long long ndir = (long long)width_d * readLen;
         int status = CUDASW_OK;
         const int nd = (width_d + 31) / 32;
-        const unsigned long long row_bytes = nd > 16 ? (((unsigned long long)width_d * 8ull + 15ull) & ~15ull) : 0ull;
+        if (DMAX < 64 && nd > DMAX) {  // the wide-state instantiation takes over at this band
+            if (lane == 0) { tb_band[pair] = band; esc_out[atomicAdd(esc_out_count, 1)] = pair; }
+            ok = false;
+            break;
+        }
+        const unsigned long long row_bytes = nd > 64 ? (((unsigned long long)width_d * 8ull + 15ull) & ~15ull) : 0ull;
         const unsigned long long need = row_bytes + (((unsigned long long)ndir + 15ull) & ~15ull);
         unsigned long long off = 0;
         if (ndir * 3 >= (1ll << 31) || need > pool.cap) status = CUDASW_ETOOLARGE;
@@ -1009,10 +1089,11 @@ sw_traceback_warp_kernel(const int* __restrict__ list, int n, PairIO io, const i
         }
         if (status != CUDASW_OK) {
             if (lane == 0) {
-                if (status == 1) retry_list[atomicAdd(retry_count, 1)] = pair;
+                if (status == 1) { tb_band[pair] = band; retry_list[atomicAdd(retry_count, 1)] = pair; }
                 else res[pair].status = status;
             }
-            return;
+            ok = false;
+            break;
         }
         int2* row = reinterpret_cast<int2*>(pool.base + off);
         uint8_t* dir = pool.base + off + row_bytes;
@@ -1023,18 +1104,22 @@ sw_traceback_warp_kernel(const int* __restrict__ list, int n, PairIO io, const i
         else if (nd <= 4) m = tb_dp_warp<4>(tc, ref, read, refLen, readLen, band, dir, row, nd);
         else if (nd <= 8) m = tb_dp_warp<8>(tc, ref, read, refLen, readLen, band, dir, row, nd);
         else if (nd <= 16) m = tb_dp_warp<16>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        else if (DMAX >= 64 && nd <= 32) m = tb_dp_warp<DMAX >= 64 ? 32 : 1>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        else if (DMAX >= 64 && nd <= 64) m = tb_dp_warp<DMAX >= 64 ? 64 : 1>(tc, ref, read, refLen, readLen, band, dir, row, nd);
         else m = tb_dp_warp<0>(tc, ref, read, refLen, readLen, band, dir, row, nd);
         mx = max(mx, m);  // the reference never resets its running maximum between band widths
         if (mx >= score) break;
         band *= 2;
     }
     __syncwarp();  // every lane's direction bytes are visible to lane 0
-    if (lane == 0) {
+    if (ok && lane == 0) {
         const int nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0);
-        if (nbody < 0) { res[pair].status = nbody; return; }
-        tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen,
-                r, res, cig, cig_cap, cig_used);
+        if (nbody < 0) res[pair].status = nbody;
+        else tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen,
+                     r, res, cig, cig_cap, cig_used);
     }
+    __syncwarp();
+    }  // pairs of this warp
 }
 
 }  // namespace cusw
