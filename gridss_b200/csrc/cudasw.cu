@@ -72,9 +72,20 @@ struct cudasw {
     cudaStream_t copy_stream = nullptr;  // H2D of the next chunk while the current one computes
     std::vector<cudaEvent_t> h2d_done;
     static constexpr int kAux = 4;  // variant kernels of one pass run side by side (mixed-length batches)
-    cudaStream_t aux[kAux]{};
-    cudaEvent_t fork_ev = nullptr, join_ev[kAux]{};
-    int launch_variants(bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool, uint64_t* launches);
+    // A phase's launches: its main stream plus auxiliary streams forked/joined by events. Two sets, because the
+    // forward pass of chunk i (compute) runs concurrently with the reverse pass and traceback of chunk i-1 (post).
+    struct StreamSet {
+        cudaStream_t main = nullptr;
+        cudaStream_t aux[kAux]{};
+        cudaEvent_t fork_ev = nullptr, join_ev[kAux]{};
+    };
+    StreamSet fwd_set, post_set;  // fwd_set.main == stream
+    cudaStream_t pack_stream = nullptr;  // encode / bin of chunk i+1 while chunk i is in its forward pass
+    struct ChunkEvents { cudaEvent_t pack0, pack1, fwd0, fwd1; };
+    std::vector<ChunkEvents> chunk_ev;
+    unsigned long long* d_strip = nullptr;  // bump counters of the strip-mining boundary buffers: [0] forward, [1] reverse
+    DevBuf<uint8_t> strip_fwd, strip_rev;
+    int launch_variants(StreamSet& ss, bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool, uint64_t* launches);
     std::vector<int16_t> var_by_q;  // host copy of variant_of() for the stats
     cudaEvent_t ev[8]{};
     std::mutex mu;
@@ -119,10 +130,13 @@ struct cudasw {
     std::unordered_map<int64_t, Done> done;
 
     void set_error(const std::string& s) { error = s; }
-    int process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so, const uint8_t* d_ref,
-                      const int64_t* d_ro, int64_t q_lo, int64_t q_hi, int64_t w_lo, int64_t w_hi, int64_t cigar_cap,
-                      bool gather, uint64_t* launches_out);
-    int finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out);
+    int pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so, const uint8_t* d_ref,
+                   const int64_t* d_ro, int64_t q_lo, int64_t q_hi, int64_t w_lo, int64_t w_hi, bool gather,
+                   uint64_t* launches_out);
+    int forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* d_so, const int64_t* d_ro, uint64_t* launches_out);
+    int post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out);
+    int size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off);
+    float last_post_ms = 0.f;
     int run(int64_t n, const uint8_t* d_seq, const int64_t* d_seq_off, const uint8_t* d_ref,
             const int64_t* d_ref_off, int64_t total_q, int64_t total_w, cudasw_result* out,
             uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used, bool inputs_on_host,
@@ -190,11 +204,25 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
         return fail(cudaGetErrorString(e));
     for (auto& ev : h->ev)
         if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(cudaGetErrorString(e));
-    for (auto& a : h->aux)
-        if ((e = cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking)) != cudaSuccess) return fail(cudaGetErrorString(e));
-    if ((e = cudaEventCreateWithFlags(&h->fork_ev, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
-    for (auto& j : h->join_ev)
-        if ((e = cudaEventCreateWithFlags(&j, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
+    {
+        // pack and post work is latency-bound and small next to the forward pass it overlaps: give it priority so its
+        // CTAs take the SM slots that the forward kernel frees
+        int lo_pri = 0, hi_pri = 0;
+        cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri);
+        h->fwd_set.main = h->stream;
+        if ((e = cudaStreamCreateWithPriority(&h->post_set.main, cudaStreamNonBlocking, hi_pri)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        if ((e = cudaStreamCreateWithPriority(&h->pack_stream, cudaStreamNonBlocking, hi_pri)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        for (auto* ss : {&h->fwd_set, &h->post_set}) {
+            for (auto& a : ss->aux) {
+                e = ss == &h->post_set ? cudaStreamCreateWithPriority(&a, cudaStreamNonBlocking, hi_pri) : cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking);
+                if (e != cudaSuccess) return fail(cudaGetErrorString(e));
+            }
+            if ((e = cudaEventCreateWithFlags(&ss->fork_ev, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
+            for (auto& j : ss->join_ev)
+                if ((e = cudaEventCreateWithFlags(&j, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        }
+    }
+    if ((e = cudaMalloc(&h->d_strip, 2 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
@@ -277,9 +305,16 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     for (auto& ev : h->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : h->h2d_done) cudaEventDestroy(ev);
-    for (auto& a : h->aux) if (a) { cudaStreamSynchronize(a); cudaStreamDestroy(a); }
-    if (h->fork_ev) cudaEventDestroy(h->fork_ev);
-    for (auto& j : h->join_ev) if (j) cudaEventDestroy(j);
+    for (auto* ss : {&h->fwd_set, &h->post_set}) {
+        for (auto& a : ss->aux) if (a) { cudaStreamSynchronize(a); cudaStreamDestroy(a); }
+        if (ss->fork_ev) cudaEventDestroy(ss->fork_ev);
+        for (auto& j : ss->join_ev) if (j) cudaEventDestroy(j);
+    }
+    if (h->post_set.main) { cudaStreamSynchronize(h->post_set.main); cudaStreamDestroy(h->post_set.main); }
+    if (h->pack_stream) { cudaStreamSynchronize(h->pack_stream); cudaStreamDestroy(h->pack_stream); }
+    for (auto& c : h->chunk_ev) { cudaEventDestroy(c.pack0); cudaEventDestroy(c.pack1); cudaEventDestroy(c.fwd0); cudaEventDestroy(c.fwd1); }
+    if (h->d_strip) cudaFree(h->d_strip);
+    h->strip_fwd.release(); h->strip_rev.release();
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -287,13 +322,13 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
 
 // Launches the score kernel of every variant that has pairs in h_hist (sorted order in `order`). With several
 // variants the launches are spread over auxiliary streams so that small launches overlap (fork/join by events).
-int cudasw::launch_variants(bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool,
-                            uint64_t* launches) {
-    cudaStream_t st = stream;
+int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c,
+                            StripPool spool, uint64_t* launches) {
+    cudaStream_t st = ss.main;
     int nonempty = 0;
     for (int v = 0; v < 2 * g_nvar; v++) nonempty += h_hist[v] > 0;
     const bool spread = nonempty > 1;
-    if (spread) CK(cudaEventRecord(fork_ev, st));
+    if (spread) CK(cudaEventRecord(ss.fork_ev, st));
     bool used[kAux] = {};
     int64_t start = 0;
     int k = 0;
@@ -305,8 +340,8 @@ int cudasw::launch_variants(bool reverse, const int* order, PairIO io, const int
             cudaStream_t s = st;
             if (spread) {
                 const int a = k++ % kAux;
-                s = aux[a];
-                if (!used[a]) { CK(cudaStreamWaitEvent(s, fork_ev, 0)); used[a] = true; }
+                s = ss.aux[a];
+                if (!used[a]) { CK(cudaStreamWaitEvent(s, ss.fork_ev, 0)); used[a] = true; }
             }
             (reverse ? (xr ? V.revx : V.rev) : (xr ? V.fwdx : V.fwd))(order + start, c, io, fwd_c, out_c, sc, spool, s);
             (*launches)++;
@@ -315,23 +350,28 @@ int cudasw::launch_variants(bool reverse, const int* order, PairIO io, const int
     }
     for (int a = 0; a < kAux; a++)
         if (used[a]) {
-            CK(cudaEventRecord(join_ev[a], aux[a]));
-            CK(cudaStreamWaitEvent(st, join_ev[a], 0));
+            CK(cudaEventRecord(ss.join_ev[a], ss.aux[a]));
+            CK(cudaStreamWaitEvent(st, ss.join_ev[a], 0));
         }
     return CUDASW_OK;
 }
 
-// One chunk of pairs [first, first+cnt): encode -> bin -> forward -> bin -> reverse -> traceback.
-// Blob offsets are absolute, so a chunk is just a shifted view of the per-pair arrays.
-int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so,
-                          const uint8_t* d_ref, const int64_t* d_ro, int64_t q_lo, int64_t q_hi,
-                          int64_t w_lo, int64_t w_hi, int64_t cigar_cap, bool gather, uint64_t* launches_out) {
-    cudaStream_t st = stream;
+// Chunk pipeline. Blob offsets are absolute, so a chunk is a shifted view of the per-pair arrays; every per-pair
+// scratch array (keys, order, results) is used at offset `first`, which keeps concurrently running chunks apart.
+//   pack_chunk    (pack stream)    encode -> window flags / gather -> seed anchors -> bin; ends with a host sync
+//   forward_chunk (compute stream) forward score pass of every variant that has pairs
+//   post_chunk    (post stream)    bin -> reverse pass -> traceback + CIGARs; host-synchronised
+// The host issues pack(i), forward(i), post(i-1): the ALU-bound forward kernels of chunk i then share the SMs with
+// the memory-bound pack of chunk i+1 and the latency-bound reverse/traceback kernels of chunk i-1. pack and post
+// never overlap each other (both are host-synchronised), so they share d_hist, h_hist and the sort workspace.
+int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so,
+                       const uint8_t* d_ref, const int64_t* d_ro, int64_t q_lo, int64_t q_hi,
+                       int64_t w_lo, int64_t w_hi, bool gather, uint64_t* launches_out) {
+    cudaStream_t st = pack_stream;
     uint64_t launches = 0;
     const int64_t n = cnt;
     int* any_n = reinterpret_cast<int*>(d_counters + 5);  // set by encode_kernel when a window holds an N
-    CK(cudaEventRecord(ev[1], st));
-    // ---- encode + forward binning
+    CK(cudaEventRecord(chunk_ev[ci].pack0, st));
     {
         const int64_t tq = q_hi - q_lo, tw = w_hi - w_lo;
         int64_t thr = (tq + 15) / 16;
@@ -354,8 +394,6 @@ int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, cons
     seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
         (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first);
     launches++;
-    int4* fwd_c = fwd.p + first;
-    cudasw_result* res_c = res.p + first;
     const bool have_multi = g_var[g_nvar - 1].multi;
     const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
                                   scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
@@ -363,50 +401,68 @@ int cudasw::process_chunk(int64_t first, int64_t cnt, const uint8_t* d_seq, cons
     size_t cub_bytes = cub_tmp.cap;
     CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
     fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
-                                                           keys.p, vals.p, d_hist, res_c, any_n, wflags.p + first, anchor.p + first);
+                                                           keys.p + first, vals.p + first, d_hist, res.p + first, any_n,
+                                                           wflags.p + first, anchor.p + first);
     launches++;
-    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 32, st));
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p + first, keys_alt.p + first, vals.p + first,
+                                       vals_alt.p + first, (int)n, 0, 32, st));
     launches += 3;
     CK(cudaMemcpyAsync(h_hist, d_hist, 256 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CK(cudaEventRecord(ev[2], st));
+    CK(cudaEventRecord(chunk_ev[ci].pack1, st));
     CK(cudaStreamSynchronize(st));
-
-    // ---- forward score pass (strip-mined variants borrow the traceback pool for their boundary rows)
-    CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
-    StripPool spool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
-    { int rc = launch_variants(false, vals_alt.p, io, nullptr, fwd_c, spool, &launches); if (rc != CUDASW_OK) return rc; }
     CK(cudaGetLastError());
-
-    // the stream is idle up to the forward launches (synchronised above); fold the pack time in now
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, ev[1], ev[2]); stats.ms_pack += ms;
     *launches_out += launches;
     return CUDASW_OK;
 }
 
-// Reverse pass + traceback over the whole batch (all of it is encoded and forward-scored by now).
-int cudasw::finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out) {
+// Forward score pass of one packed chunk (h_hist holds its pairs per variant). Waits for the pack by event.
+int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* d_so, const int64_t* d_ro, uint64_t* launches_out) {
+    (void)cnt;
     cudaStream_t st = stream;
     uint64_t launches = 0;
-    PairIO io{enc_seq.p, enc_ref.p, d_so, d_ro};
-    int4* fwd_c = fwd.p;
-    int4* rev_c = rev.p;
-    cudasw_result* res_c = res.p;
+    PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
+    CK(cudaStreamWaitEvent(st, chunk_ev[ci].pack1, 0));
+    CK(cudaEventRecord(chunk_ev[ci].fwd0, st));
+    CK(cudaMemsetAsync(d_strip, 0, sizeof(unsigned long long), st));
+    StripPool spool{strip_fwd.p, (unsigned long long)strip_fwd.cap, d_strip};
+    { int rc = launch_variants(fwd_set, false, vals_alt.p + first, io, nullptr, fwd.p + first, spool, &launches); if (rc != CUDASW_OK) return rc; }
+    CK(cudaEventRecord(chunk_ev[ci].fwd1, st));
+    CK(cudaGetLastError());
+    *launches_out += launches;
+    return CUDASW_OK;
+}
+
+// Reverse pass + traceback of one chunk whose forward pass has been queued (waits for it by event).
+int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out) {
+    cudaStream_t st = post_set.main;
+    CK(cudaStreamWaitEvent(st, chunk_ev[ci].fwd1, 0));
+    cudaStream_t* aux = post_set.aux;
+    cudaEvent_t fork_ev = post_set.fork_ev;
+    cudaEvent_t* join_ev = post_set.join_ev;
+    uint64_t launches = 0;
+    PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
+    int4* fwd_c = fwd.p + first;
+    int4* rev_c = rev.p + first;
+    cudasw_result* res_c = res.p + first;
+    DevBuf<uint32_t> keys = this->keys, keys_alt = this->keys_alt;  // shifted views (never released here)
+    DevBuf<int> vals = this->vals, vals_alt = this->vals_alt, retry_a = this->retry_a, retry_b = this->retry_b, tb_band = this->tb_band;
+    keys.p += first; keys_alt.p += first; vals.p += first; vals_alt.p += first; retry_a.p += first; retry_b.p += first; tb_band.p += first;
+    const uint8_t* wflags_c = wflags.p + first;
     size_t cub_bytes = cub_tmp.cap;
-    StripPool spool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+    StripPool spool{strip_rev.p, (unsigned long long)strip_rev.cap, d_strip + 1};
     CK(cudaEventRecord(ev[3], st));
 
     // ---- reverse score pass
-    CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(d_strip + 1, 0, sizeof(unsigned long long), st));
     CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
     rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, vt, keys.p, vals.p, d_hist,
-                                                           reinterpret_cast<int*>(d_counters + 5), wflags.p);
+                                                           reinterpret_cast<int*>(d_counters + 5), wflags_c);
     launches++;
     CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
     launches += 3;
     CK(cudaMemcpyAsync(h_hist, d_hist, 256 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    { int rc = launch_variants(true, vals_alt.p, io, fwd_c, rev_c, spool, &launches); if (rc != CUDASW_OK) return rc; }
+    { int rc = launch_variants(post_set, true, vals_alt.p, io, fwd_c, rev_c, spool, &launches); if (rc != CUDASW_OK) return rc; }
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[4], st));
 
@@ -559,9 +615,32 @@ int cudasw::finish_batch(int64_t n, const int64_t* d_so, const int64_t* d_ro, in
     CK(cudaGetLastError());
     // the stream is idle here (synchronised above): fold this chunk's phase times into the batch stats
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, ev[3], ev[4]); stats.ms_reverse += ms;
-    cudaEventElapsedTime(&ms, ev[4], ev[5]); stats.ms_traceback += ms;
+    cudaEventElapsedTime(&ms, ev[3], ev[4]); stats.ms_reverse += ms; last_post_ms = ms;
+    cudaEventElapsedTime(&ms, ev[4], ev[5]); stats.ms_traceback += ms; last_post_ms += ms;
     *launches_out += launches;
+    return CUDASW_OK;
+}
+
+// Boundary rows of the strip-mined score variants (queries above the tallest single-strip variant): two rows of one
+// 32-bit word per window column and pair. Sized exactly for the chunk, so the kernels' bump allocation cannot fail.
+int cudasw::size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off) {
+    bool any = false;
+    for (int v = 0; v < g_nvar; v++)
+        if (g_var[v].multi && (h_hist[v] > 0 || h_hist[g_nvar + v] > 0)) any = true;
+    if (!any) return CUDASW_OK;
+    const int64_t single_rows = vt.n_single > 0 ? vt.rows[vt.n_single - 1] : 0;
+    unsigned long long need = 0;
+    for (int64_t i = first; i < first + cnt; i++) {
+        const int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
+        if (q > single_rows && w > 0) need += ((((unsigned long long)w * 4ull + 15ull) & ~15ull) * 2ull);
+    }
+    if (need > strip_fwd.cap || need > strip_rev.cap) {
+        // the buffers may still be in use by the chunk before: let it finish before they are replaced
+        CK(cudaStreamSynchronize(stream));
+        CK(cudaStreamSynchronize(post_set.main));
+        CK(strip_fwd.ensure((size_t)need + 256));
+        CK(strip_rev.ensure((size_t)need + 256));
+    }
     return CUDASW_OK;
 }
 
@@ -589,14 +668,23 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     struct Chunk { int64_t first, cnt, q_lo, q_hi, w_lo, w_hi; };
     std::vector<Chunk> chunks;
     {
-        // chunk sizes grow geometrically (64 MB, 128 MB, ... capped at 1 GB): the first copy is the only one the
-        // kernels have to wait for, and each later copy hides behind the (slower) kernels of the chunk before it
-        int64_t target = inputs_on_host ? (int64_t)64 << 20 : (int64_t)1 << 60;  // resident inputs: nothing to overlap
-        int64_t target_max = (int64_t)1 << 30;
-        // windows gathered on the device: only queries and descriptors cross PCIe (~1/12 of the bytes), so one small
-        // leading chunk is enough to hide the copy of the rest
-        if (gather) { target = (int64_t)128 << 20; target_max = (int64_t)1 << 60; }
-        if (const char* e = getenv("CUDASW_CHUNK_MB")) target = target_max = std::max<int64_t>(1, atoll(e)) << 20;
+        // Host inputs: chunk sizes grow geometrically (64 MB, 128 MB, ... capped at 1 GB): the first copy is the only one
+        // the kernels have to wait for, and each later copy hides behind the (slower) kernels of the chunk before it.
+        // Resident inputs: one chunk. (Splitting them so that the pack of chunk i+1 runs beside the forward pass of chunk i
+        // was measured neutral on B200: the forward kernel fills the register file, so whatever runs beside it takes SM
+        // slots from it. The split is kept only for the CUDASW_POST_PER_CHUNK experiment.)
+        const int64_t total_bytes = total_q + total_w;
+        const bool ppc = getenv("CUDASW_POST_PER_CHUNK") != nullptr;
+        const bool pipelined = ppc && !getenv("CUDASW_NO_OVERLAP") && total_bytes >= ((int64_t)256 << 20);
+        int64_t target = inputs_on_host ? (int64_t)64 << 20 : (pipelined ? std::max<int64_t>(total_bytes / 16, 1) : (int64_t)1 << 60);
+        int64_t target_max = inputs_on_host ? (int64_t)1 << 30 : (pipelined && ppc ? std::max<int64_t>(5 * total_bytes / 16, 1) : (int64_t)1 << 60);
+        const int64_t tail_bytes = pipelined && ppc ? total_bytes / 16 : 0;
+        // windows gathered on the device: only queries and descriptors cross PCIe (~1/12 of the bytes), so the copy of
+        // everything behind the small leading chunk hides behind that chunk
+        if (gather && inputs_on_host && !pipelined) { target = (int64_t)128 << 20; target_max = (int64_t)1 << 60; }
+        if (gather && pipelined) { target = std::max<int64_t>(total_bytes / 16, 1); target_max = ppc ? std::max<int64_t>(5 * total_bytes / 16, 1) : (int64_t)1 << 60; }
+        bool fixed_target = false;
+        if (const char* e = getenv("CUDASW_CHUNK_MB")) { target = target_max = std::max<int64_t>(1, atoll(e)) << 20; fixed_target = true; }
         const int64_t max_pairs = 8 << 20;  // keeps the per-chunk sort/bin arrays small
         int64_t first = 0;
         while (first < n) {
@@ -605,6 +693,14 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
                 // largest `last` with bytes(first..last) <= target (offsets are monotone: binary search)
                 int64_t lo = first + 1, hi = std::min(n, first + max_pairs);
                 const int64_t base = h_seq_off[first] + h_ref_off[first];
+                int64_t want_bytes = target;
+                if (!fixed_target && tail_bytes > 0) {
+                    // keep a small trailing chunk: whatever is left after this one is either >= 1.5 tails or exactly one
+                    const int64_t left = total_bytes - base;
+                    if (left <= tail_bytes + tail_bytes / 2) want_bytes = left;                 // this is the trailing chunk
+                    else if (left - want_bytes < tail_bytes + tail_bytes / 2) want_bytes = left - tail_bytes;
+                }
+                const int64_t target = want_bytes;
                 while (lo < hi) {
                     int64_t mid = lo + (hi - lo + 1) / 2;
                     if (h_seq_off[mid] + h_ref_off[mid] - base <= target) lo = mid; else hi = mid - 1;
@@ -627,7 +723,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
             }
             chunks.push_back(c);
             first = last;
-            target = gather ? target_max : std::min(target * 2, std::max(target, target_max));
+            target = fixed_target ? target : (inputs_on_host && !gather ? std::min(target * 2, std::max(target, target_max)) : target_max);
         }
     }
     int64_t max_cnt = 0;
@@ -660,9 +756,16 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         h2d_done.push_back(e);
     }
+    while (chunk_ev.size() < chunks.size()) {
+        ChunkEvents ce{};
+        CK(cudaEventCreate(&ce.pack0)); CK(cudaEventCreate(&ce.pack1)); CK(cudaEventCreate(&ce.fwd0)); CK(cudaEventCreate(&ce.fwd1));
+        chunk_ev.push_back(ce);
+    }
 
     CK(cudaEventRecord(ev[0], st));
     CK(cudaMemsetAsync(d_counters, 0, 8 * sizeof(unsigned long long), st));
+    CK(cudaEventRecord(ev[1], st));
+    CK(cudaStreamWaitEvent(pack_stream, ev[1], 0));  // the counters (any-N flag) are reset before the first encode
     // ---- H2D: everything is queued on the copy stream now, one event per chunk
     const uint8_t* d_seq = d_seq_in;
     const uint8_t* d_ref = d_ref_in;
@@ -695,18 +798,31 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
                           (gather ? (uint64_t)(n + 1) * 8 + (uint64_t)h_seg_off[n] * sizeof(WindowSeg) : (uint64_t)total_w);
     }
 
+    // ---- the chunk pipeline: pack(i) | forward(i) | post(i-1), see pack_chunk
+    auto drain = [&]() {  // nothing may stay in flight over the caller's buffers or this handle's scratch
+        cudaStreamSynchronize(copy_stream); cudaStreamSynchronize(pack_stream); cudaStreamSynchronize(st);
+        cudaStreamSynchronize(post_set.main);
+    };
+    const bool serial = getenv("CUDASW_NO_OVERLAP") != nullptr;
+    const bool post_per_chunk = getenv("CUDASW_POST_PER_CHUNK") != nullptr;
     for (size_t i = 0; i < chunks.size(); i++) {
         const Chunk& c = chunks[i];
-        if (inputs_on_host) CK(cudaStreamWaitEvent(st, h2d_done[i], 0));
-        int rc = process_chunk(c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, cigar_cap, gather, &launches);
-        if (rc != CUDASW_OK) {
-            cudaStreamSynchronize(copy_stream);  // do not leave copies in flight over the caller's buffers
-            return rc;
-        }
+        if (inputs_on_host) CK(cudaStreamWaitEvent(pack_stream, h2d_done[i], 0));
+        int rc = pack_chunk(i, c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, gather, &launches);
+        if (rc == CUDASW_OK) rc = size_strip_buffers(c.first, c.cnt, h_seq_off, h_ref_off);
+        if (rc == CUDASW_OK) rc = forward_chunk(i, c.first, c.cnt, d_so, d_ro, &launches);
+        if (rc == CUDASW_OK && serial) rc = cudaStreamSynchronize(st) == cudaSuccess ? CUDASW_OK : CUDASW_ECUDA;
+        if (rc == CUDASW_OK && post_per_chunk && i > 0) rc = post_chunk(i - 1, chunks[i - 1].first, chunks[i - 1].cnt, d_so, d_ro, cigar_cap, &launches);
+        if (rc != CUDASW_OK) { drain(); return rc; }
     }
     {
-        int rc = finish_batch(n, d_so, d_ro, cigar_cap, &launches);
-        if (rc != CUDASW_OK) return rc;
+        // Reverse pass + traceback: once over the whole batch. Running them per chunk beside the next chunk's forward
+        // pass was measured slower on B200 (C2: 253 vs 237 ms per 1 M pairs): their latency-bound CTAs displace
+        // forward CTAs that fill the register file. CUDASW_POST_PER_CHUNK=1 keeps that experiment available.
+        const Chunk& c = chunks.back();
+        int rc = post_per_chunk ? post_chunk(chunks.size() - 1, c.first, c.cnt, d_so, d_ro, cigar_cap, &launches)
+                                : post_chunk(chunks.size() - 1, 0, n, d_so, d_ro, cigar_cap, &launches);
+        if (rc != CUDASW_OK) { drain(); return rc; }
     }
     CK(cudaEventRecord(ev[5], st));
 #ifdef CUSW_STEP_STATS
@@ -727,10 +843,17 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     stats.kernel_launches = launches;
     cudaEventElapsedTime(&stats.ms_d2h, ev[5], ev[6]);
     cudaEventElapsedTime(&stats.ms_total, ev[0], ev[6]);
-    // H2D time not hidden behind kernels = total minus everything else
-    cudaEventElapsedTime(&stats.ms_forward, ev[0], ev[3]);
-    stats.ms_forward -= stats.ms_pack;  // chunk loop = pack + forward kernels (+ any H2D wait, reported as ms_h2d when known)
-    stats.ms_h2d = std::max(0.f, stats.ms_total - stats.ms_pack - stats.ms_forward - stats.ms_reverse - stats.ms_traceback - stats.ms_d2h);
+    // per-phase device time summed over the chunks. The phases of neighbouring chunks overlap (pack and post run beside a
+    // forward pass), so they add up to more than ms_total; ms_h2d = the part of ms_total that is none of: first pack,
+    // forward passes, last post, D2H (i.e. copy waits and pipeline bubbles)
+    float pack_first = 0.f;
+    for (size_t i = 0; i < chunks.size(); i++) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, chunk_ev[i].pack0, chunk_ev[i].pack1); stats.ms_pack += ms;
+        if (i == 0) pack_first = ms;
+        cudaEventElapsedTime(&ms, chunk_ev[i].fwd0, chunk_ev[i].fwd1); stats.ms_forward += ms;
+    }
+    stats.ms_h2d = std::max(0.f, stats.ms_total - pack_first - stats.ms_forward - last_post_ms - stats.ms_d2h);
     if (h_seq_off && h_ref_off) {
         const bool have_multi = g_var[g_nvar - 1].multi;
         const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
