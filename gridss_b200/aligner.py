@@ -70,6 +70,8 @@ class Stats(ctypes.Structure):
         ("h2d_bytes", ctypes.c_uint64),
         ("d2h_bytes", ctypes.c_uint64),
         ("forward_cells_padded", ctypes.c_uint64),
+        ("ms_encode", ctypes.c_float),
+        ("encode_bytes", ctypes.c_uint64),
     ]
 
     def as_dict(self):
@@ -310,6 +312,12 @@ class CudaAligner(Aligner):
         if rc != 0:
             raise (ValueError if rc == CUDASW_EINVAL else CudaSwError)(f"cudasw_reference_load failed ({rc}): {self._err()}")
         self._contig_len = [len(c) for c in contigs]
+
+    def load_reference_blob(self, blob: np.ndarray, contig_off: np.ndarray) -> None:
+        """Same from one uint8 blob + int64 contig offsets (no copy on the host)."""
+        rc = self._lib.cudasw_reference_load(self._h, len(contig_off) - 1, blob.ctypes.data, contig_off.ctypes.data)
+        if rc != 0:
+            raise (ValueError if rc == CUDASW_EINVAL else CudaSwError)(f"cudasw_reference_load failed ({rc}): {self._err()}")
 
     def get_subsequence(self, contig: int, start: int, end: int, revcomp: bool = False) -> bytes:
         """getSubsequenceAt(contig, start+1, end) of the packed reference: upper-case ACGT, anything else N."""

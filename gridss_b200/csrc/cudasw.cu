@@ -81,7 +81,7 @@ struct cudasw {
     };
     StreamSet fwd_set, post_set;  // fwd_set.main == stream
     cudaStream_t pack_stream = nullptr;  // encode / bin of chunk i+1 while chunk i is in its forward pass
-    struct ChunkEvents { cudaEvent_t pack0, pack1, fwd0, fwd1; };
+    struct ChunkEvents { cudaEvent_t pack0, enc1, pack1, fwd0, fwd1; };
     std::vector<ChunkEvents> chunk_ev;
     unsigned long long* d_strip = nullptr;  // bump counters of the strip-mining boundary buffers: [0] forward, [1] reverse
     DevBuf<uint8_t> strip_fwd, strip_rev;
@@ -312,7 +312,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     }
     if (h->post_set.main) { cudaStreamSynchronize(h->post_set.main); cudaStreamDestroy(h->post_set.main); }
     if (h->pack_stream) { cudaStreamSynchronize(h->pack_stream); cudaStreamDestroy(h->pack_stream); }
-    for (auto& c : h->chunk_ev) { cudaEventDestroy(c.pack0); cudaEventDestroy(c.pack1); cudaEventDestroy(c.fwd0); cudaEventDestroy(c.fwd1); }
+    for (auto& c : h->chunk_ev) { cudaEventDestroy(c.pack0); cudaEventDestroy(c.enc1); cudaEventDestroy(c.pack1); cudaEventDestroy(c.fwd0); cudaEventDestroy(c.fwd1); }
     if (h->d_strip) cudaFree(h->d_strip);
     h->strip_fwd.release(); h->strip_rev.release();
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
@@ -388,8 +388,12 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
                                                                          d_contig_off.p, ref2bit.p, refN.p, enc_ref.p,
                                                                          wflags.p + first, any_n, 0);
     } else {
+        CK(cudaEventRecord(chunk_ev[ci].enc1, st));
         window_flags_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, enc_ref.p, io.ref_off, any_n, wflags.p + first);
     }
+    if (gather) CK(cudaEventRecord(chunk_ev[ci].enc1, st));
+    // 1 byte read + 1 written per base; a gathered window reads 3 bits and writes 1 byte per base
+    stats.encode_bytes += 2ull * (uint64_t)(q_hi - q_lo) + (gather ? (uint64_t)(w_hi - w_lo) * 11ull / 8ull : 2ull * (uint64_t)(w_hi - w_lo));
     launches++;
     seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
         (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first);
@@ -758,7 +762,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     }
     while (chunk_ev.size() < chunks.size()) {
         ChunkEvents ce{};
-        CK(cudaEventCreate(&ce.pack0)); CK(cudaEventCreate(&ce.pack1)); CK(cudaEventCreate(&ce.fwd0)); CK(cudaEventCreate(&ce.fwd1));
+        CK(cudaEventCreate(&ce.pack0)); CK(cudaEventCreate(&ce.enc1)); CK(cudaEventCreate(&ce.pack1)); CK(cudaEventCreate(&ce.fwd0)); CK(cudaEventCreate(&ce.fwd1));
         chunk_ev.push_back(ce);
     }
 
@@ -849,6 +853,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     float pack_first = 0.f;
     for (size_t i = 0; i < chunks.size(); i++) {
         float ms = 0.f;
+        cudaEventElapsedTime(&ms, chunk_ev[i].pack0, chunk_ev[i].enc1); stats.ms_encode += ms;
         cudaEventElapsedTime(&ms, chunk_ev[i].pack0, chunk_ev[i].pack1); stats.ms_pack += ms;
         if (i == 0) pack_first = ms;
         cudaEventElapsedTime(&ms, chunk_ev[i].fwd0, chunk_ev[i].fwd1); stats.ms_forward += ms;

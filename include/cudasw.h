@@ -70,6 +70,8 @@ typedef struct cudasw_stats {
     float ms_h2d, ms_pack, ms_forward, ms_reverse, ms_traceback, ms_d2h;
     uint64_t h2d_bytes, d2h_bytes;
     uint64_t forward_cells_padded; /* cells actually computed by the forward kernels */
+    float ms_encode;               /* part of ms_pack: the HBM-bound encode (or window gather) kernels alone */
+    uint64_t encode_bytes;         /* bytes those kernels read + wrote */
 } cudasw_stats;
 
 /* Create an engine on CUDA device `device`. Replaces the AlignerFactory static initialiser's

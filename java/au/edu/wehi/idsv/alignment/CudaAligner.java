@@ -45,11 +45,62 @@ public class CudaAligner implements Aligner, AutoCloseable {
 		}
 		return out;
 	}
+	/**
+	 * Packs the reference into GPU memory once (2 bits per base + ambiguity bit); replaces the per-window
+	 * ReferenceLookup.getSubsequenceAt + reverseComplement work of SAMRecordUtil.realign and BreakpointHomology.calculate.
+	 * contigOff has one entry per contig plus the total length.
+	 */
+	public void loadReference(byte[] bases, long[] contigOff) {
+		int rc = loadReference(handle, bases, contigOff);
+		if (rc != 0) throw new IllegalStateException("cudasw_reference_load failed (" + rc + "): " + lastError(handle));
+	}
+	/** A window made of reference segments [start, end) (0-based) of contig referenceIndex, optionally reverse-complemented. */
+	public static final class Window {
+		public final int[] contig; public final boolean[] revcomp; public final long[] start, end;
+		public Window(int[] contig, boolean[] revcomp, long[] start, long[] end) { this.contig = contig; this.revcomp = revcomp; this.start = start; this.end = end; }
+		public static Window of(int contig, long start, long end, boolean revcomp) {
+			return new Window(new int[] { contig }, new boolean[] { revcomp }, new long[] { start }, new long[] { end });
+		}
+	}
+	/** alignBatch with the windows named instead of shipped: one JNI round trip, ~24 bytes per window segment. */
+	public Alignment[] alignBatch(byte[][] seqs, Window[] windows) {
+		int n = seqs.length, nseg = 0;
+		long[] seqOff = new long[n + 1], winOff = new long[n + 1];
+		for (int i = 0; i < n; i++) {
+			seqOff[i + 1] = seqOff[i] + seqs[i].length;
+			nseg += windows[i].contig.length;
+			winOff[i + 1] = nseg;
+		}
+		byte[] seqBlob = new byte[(int) seqOff[n]];
+		int[] segContig = new int[nseg], segFlags = new int[nseg];
+		long[] segStart = new long[nseg], segEnd = new long[nseg];
+		for (int i = 0, k = 0; i < n; i++) {
+			System.arraycopy(seqs[i], 0, seqBlob, (int) seqOff[i], seqs[i].length);
+			for (int j = 0; j < windows[i].contig.length; j++, k++) {
+				segContig[k] = windows[i].contig[j]; segFlags[k] = windows[i].revcomp[j] ? 1 : 0;
+				segStart[k] = windows[i].start[j]; segEnd[k] = windows[i].end[j];
+			}
+		}
+		int[] start = new int[n], status = new int[n];
+		String[] cigar = new String[n];
+		int rc = alignBatchWindows(handle, n, seqBlob, seqOff, segContig, segFlags, segStart, segEnd, winOff, start, cigar, status);
+		if (rc != 0) throw new IllegalStateException("cudasw_align_batch_windows failed (" + rc + "): " + lastError(handle));
+		Alignment[] out = new Alignment[n];
+		for (int i = 0; i < n; i++) {
+			if (status[i] == -1) throw new IllegalArgumentException("seq and ref must be non-zero size and inside the reference");
+			if (status[i] != 0) throw new IllegalStateException("cudasw pair status " + status[i]);
+			out[i] = new Alignment(start[i], cigar[i]);
+		}
+		return out;
+	}
 	@Override
 	public void close() { if (handle != 0) { destroy(handle); handle = 0; } }
 	private static native long create(int match, int mismatch, int ambiguous, int gapOpen, int gapExtend, int device);
 	private static native void destroy(long handle);
 	private static native String lastError(long handle);
+	private static native int loadReference(long handle, byte[] bases, long[] contigOff);
+	private static native int alignBatchWindows(long handle, int n, byte[] seqBlob, long[] seqOff, int[] segContig, int[] segFlags,
+			long[] segStart, long[] segEnd, long[] winOff, int[] startOut, String[] cigarOut, int[] statusOut);
 	private static native int alignBatch(long handle, int n, byte[] seqBlob, long[] seqOff, byte[] refBlob, long[] refOff,
 			int[] startOut, String[] cigarOut, int[] statusOut);
 }

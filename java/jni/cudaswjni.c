@@ -56,3 +56,70 @@ JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_alignBatch(JN
     free(res);
     return rc;
 }
+
+/* Shared tail of both batch entry points: results -> int[] start, String[] cigar, int[] status. */
+static void cudaswjni_deliver(JNIEnv* env, jint n, const cudasw_result* res, const uint32_t* cig, jintArray startOut,
+                              jobjectArray cigarOut, jintArray statusOut) {
+    jint* st = (*env)->GetIntArrayElements(env, startOut, NULL);
+    jint* status = (*env)->GetIntArrayElements(env, statusOut, NULL);
+    char buf[1 << 16];
+    for (jint i = 0; i < n; i++) {
+        st[i] = res[i].ref_begin;
+        status[i] = res[i].status;
+        if (res[i].status == 0 && cudasw_cigar_string(cig + res[i].cigar_off, res[i].cigar_len, buf, sizeof buf) >= 0)
+            (*env)->SetObjectArrayElement(env, cigarOut, i, (*env)->NewStringUTF(env, buf));
+    }
+    (*env)->ReleaseIntArrayElements(env, startOut, st, 0);
+    (*env)->ReleaseIntArrayElements(env, statusOut, status, 0);
+}
+
+/* Device-resident reference (replaces TwoBitBufferedReferenceSequenceFile's per-JVM cache for the aligner's callers,
+ * picard/TwoBitBufferedReferenceSequenceFile.java:97-125): called once per contig set. */
+JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_loadReference(JNIEnv* env, jclass c, jlong h,
+        jbyteArray bases, jlongArray contigOff) {
+    jsize nc = (*env)->GetArrayLength(env, contigOff) - 1;
+    jbyte* b = (*env)->GetPrimitiveArrayCritical(env, bases, NULL);
+    jlong* o = (*env)->GetPrimitiveArrayCritical(env, contigOff, NULL);
+    int rc = cudasw_reference_load((cudasw_t*)(intptr_t)h, (int32_t)nc, (const uint8_t*)b, (const int64_t*)o);
+    (*env)->ReleasePrimitiveArrayCritical(env, contigOff, o, JNI_ABORT);
+    (*env)->ReleasePrimitiveArrayCritical(env, bases, b, JNI_ABORT);
+    return rc;
+}
+
+/* Windows named as segments: parallel arrays (contig, flags, start, end) of nSeg entries + winOff[n+1]. */
+JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_alignBatchWindows(JNIEnv* env, jclass c, jlong h, jint n,
+        jbyteArray seqBlob, jlongArray seqOff, jintArray segContig, jintArray segFlags, jlongArray segStart,
+        jlongArray segEnd, jlongArray winOff, jintArray startOut, jobjectArray cigarOut, jintArray statusOut) {
+    jsize nseg = (*env)->GetArrayLength(env, segContig);
+    cudasw_window* win = (cudasw_window*)malloc(sizeof(cudasw_window) * (size_t)(nseg > 0 ? nseg : 1));
+    {
+        jint* sc = (*env)->GetIntArrayElements(env, segContig, NULL);
+        jint* sf = (*env)->GetIntArrayElements(env, segFlags, NULL);
+        jlong* ss = (*env)->GetLongArrayElements(env, segStart, NULL);
+        jlong* se = (*env)->GetLongArrayElements(env, segEnd, NULL);
+        for (jsize k = 0; k < nseg; k++) {
+            win[k].contig = sc[k]; win[k].flags = sf[k]; win[k].start = ss[k]; win[k].end = se[k];
+        }
+        (*env)->ReleaseIntArrayElements(env, segContig, sc, JNI_ABORT);
+        (*env)->ReleaseIntArrayElements(env, segFlags, sf, JNI_ABORT);
+        (*env)->ReleaseLongArrayElements(env, segStart, ss, JNI_ABORT);
+        (*env)->ReleaseLongArrayElements(env, segEnd, se, JNI_ABORT);
+    }
+    cudasw_result* res = (cudasw_result*)malloc(sizeof(cudasw_result) * (size_t)(n > 0 ? n : 1));
+    jsize qbytes = (*env)->GetArrayLength(env, seqBlob);
+    int64_t cap = (int64_t)qbytes + 4 * (int64_t)n + 16, used = 0;
+    uint32_t* cig = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)cap);
+    jbyte* s = (*env)->GetPrimitiveArrayCritical(env, seqBlob, NULL);
+    jlong* so = (*env)->GetPrimitiveArrayCritical(env, seqOff, NULL);
+    jlong* wo = (*env)->GetPrimitiveArrayCritical(env, winOff, NULL);
+    int rc = cudasw_align_batch_windows((cudasw_t*)(intptr_t)h, n, (const uint8_t*)s, (const int64_t*)so, win,
+                                        (const int64_t*)wo, res, cig, cap, &used);
+    (*env)->ReleasePrimitiveArrayCritical(env, winOff, wo, JNI_ABORT);
+    (*env)->ReleasePrimitiveArrayCritical(env, seqOff, so, JNI_ABORT);
+    (*env)->ReleasePrimitiveArrayCritical(env, seqBlob, s, JNI_ABORT);
+    if (rc == CUDASW_OK) cudaswjni_deliver(env, n, res, cig, startOut, cigarOut, statusOut);
+    free(cig);
+    free(res);
+    free(win);
+    return rc;
+}

@@ -1,0 +1,113 @@
+#!/usr/bin/env python
+"""Differential fuzz of the CUDA path against the reference's own shipped libsswjni.so (SURVEY.md §8c "Volume parity
+plan"). Test infrastructure: run by hand on a GPU box, not collected by pytest.
+
+  python tests/fuzz_gpu.py --seconds 180          # about that much reference-binary time on all host cores
+
+Streams fresh slices of the counter-based C1-C4 workloads (new seeds every round) and the adversarial families
+through cudasw_align_batch and through the checker, compares (score, ref_begin, ref_end, read_begin, read_end,
+CIGAR words, status) per pair and prints one JSON summary line; any mismatch is listed and the exit code is 1.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+FIELDS = ["score", "ref_begin", "ref_end", "read_begin", "read_end", "cigar_len", "status"]
+
+
+def compare(res, cig, m):
+    bad = 0
+    first = None
+    same = np.ones(len(res), dtype=bool)
+    for f in FIELDS:
+        same &= res[f] == m.res[f]
+    # CIGAR words: compare through the per-pair digests of the product's own checksum helper, then exactly where cheap
+    from gridss_b200.shard import pair_digests
+
+    same &= pair_digests(res, cig, 0) == pair_digests(m.res, m.cig, 0)
+    undef = (res["status"] == -5) | (m.res["status"] == -5)
+    same |= undef
+    bad = int((~same).sum())
+    if bad:
+        first = int(np.flatnonzero(~same)[0])
+    return bad, int(undef.sum()), first
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--seconds", type=float, default=180.0)
+    ap.add_argument("--checker", default="reference", choices=["reference", "model"])
+    args = ap.parse_args()
+    import gridss_b200 as g
+    from gridss_b200.aligner import pack
+    from oracle import oracle as O
+    from tools import synth as S
+
+    O.build()
+    S.build()
+    cores = os.cpu_count() or 1
+    use_ref = args.checker == "reference" and O.have_reference()
+    check = O.ref_align_blobs if use_ref else O.model_align_blobs
+    al = g.CudaAligner()
+    plan = [(1, 200000), (2, 60000), (4, 100000), (3, 30000)]
+    kinds = ["random", "mutated", "two_letter", "homopolymer", "dinuc", "tandem", "subst_block", "with_n", "zero", "tiny", "q_gt_w", "indel_heavy"]
+    tot = {"pairs": 0, "cells": 0.0, "mismatches": 0, "undefined_in_reference": 0, "by_source": {}}
+    examples = []
+    t_end = time.time() + args.seconds
+    rnd = 0
+    while time.time() < t_end:
+        rnd += 1
+        for cfg, n in plan:
+            if time.time() >= t_end:
+                break
+            seed = 100000 * cfg + rnd
+            sb, so, rb, ro = S.generate(cfg, n, seed=seed)
+            res, cig = al.align_blobs(sb, so, rb, ro)
+            m = check(sb, so, rb, ro, threads=cores)
+            bad, undef, first = compare(res, cig, m)
+            key = f"C{cfg}"
+            d = tot["by_source"].setdefault(key, {"pairs": 0, "mismatches": 0})
+            d["pairs"] += n
+            d["mismatches"] += bad
+            tot["pairs"] += n
+            tot["cells"] += float((np.diff(so).astype(np.float64) * np.diff(ro)).sum())
+            tot["mismatches"] += bad
+            tot["undefined_in_reference"] += undef
+            if bad and len(examples) < 5:
+                examples.append({"source": key, "seed": seed, "pair": first})
+        for kind in kinds:
+            if time.time() >= t_end:
+                break
+            seqs, refs = S.adversarial(kind, 1500, seed=1000 + rnd, qmax=300 + 100 * (rnd % 5), wmax=600 + 300 * (rnd % 4))
+            sb, so = pack(seqs)
+            rb, ro = pack(refs)
+            res, cig = al.align_blobs(sb, so, rb, ro)
+            m = check(sb, so, rb, ro, threads=cores)
+            bad, undef, first = compare(res, cig, m)
+            d = tot["by_source"].setdefault("adversarial:" + kind, {"pairs": 0, "mismatches": 0})
+            d["pairs"] += len(seqs)
+            d["mismatches"] += bad
+            tot["pairs"] += len(seqs)
+            tot["cells"] += float((np.diff(so).astype(np.float64) * np.diff(ro)).sum())
+            tot["mismatches"] += bad
+            tot["undefined_in_reference"] += undef
+            if bad and len(examples) < 5:
+                examples.append({"source": kind, "seed": 1000 + rnd, "pair": first})
+    tot["checker"] = ("libsswjni.so as shipped by the reference" if use_ref else "oracle/ssw_model.c") + f", {cores} host threads"
+    tot["rounds"] = rnd
+    tot["examples"] = examples
+    print(json.dumps(tot), flush=True)
+    al.close()
+    return 1 if tot["mismatches"] else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

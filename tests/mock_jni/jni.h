@@ -1,0 +1,31 @@
+/* Minimal stand-in for <jni.h>: just the types and JNIEnv members java/jni/cudaswjni.c uses, so that the JNI glue can
+ * be type-checked against include/cudasw.h on a machine without a JDK (tests/test_abi.py). Not a JNI implementation. */
+#ifndef MOCK_JNI_H
+#define MOCK_JNI_H
+#include <stdint.h>
+typedef int32_t jint;
+typedef int64_t jlong;
+typedef int8_t jbyte;
+typedef uint8_t jboolean;
+typedef jint jsize;
+typedef void* jobject;
+typedef jobject jclass, jstring, jarray, jbyteArray, jintArray, jlongArray, jobjectArray;
+#define JNIEXPORT __attribute__((visibility("default")))
+#define JNICALL
+#define JNI_ABORT 2
+struct JNINativeInterface_;
+typedef const struct JNINativeInterface_* JNIEnv;
+struct JNINativeInterface_ {
+    jclass (*FindClass)(JNIEnv*, const char*);
+    jint (*ThrowNew)(JNIEnv*, jclass, const char*);
+    jstring (*NewStringUTF)(JNIEnv*, const char*);
+    jsize (*GetArrayLength)(JNIEnv*, jarray);
+    void* (*GetPrimitiveArrayCritical)(JNIEnv*, jarray, jboolean*);
+    void (*ReleasePrimitiveArrayCritical)(JNIEnv*, jarray, void*, jint);
+    jint* (*GetIntArrayElements)(JNIEnv*, jintArray, jboolean*);
+    void (*ReleaseIntArrayElements)(JNIEnv*, jintArray, jint*, jint);
+    jlong* (*GetLongArrayElements)(JNIEnv*, jlongArray, jboolean*);
+    void (*ReleaseLongArrayElements)(JNIEnv*, jlongArray, jlong*, jint);
+    void (*SetObjectArrayElement)(JNIEnv*, jobjectArray, jsize, jobject);
+};
+#endif

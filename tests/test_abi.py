@@ -80,3 +80,18 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 txt = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "oracle" not in txt.replace("SURVEY", ""), f"{f} mentions the oracle"
+
+
+def test_jni_glue_type_checks_against_the_header():
+    """java/jni/cudaswjni.c (the reference-side binding of INTEGRATION.md) compiles against include/cudasw.h; a
+    minimal stand-in for <jni.h> is used because the build image has no JDK."""
+    import subprocess
+
+    src = os.path.join(ROOT, "java", "jni", "cudaswjni.c")
+    subprocess.check_call(["gcc", "-fsyntax-only", "-Wall", "-Werror", "-Wno-unused-parameter",
+                           "-I" + os.path.join(ROOT, "tests", "mock_jni"), "-I" + os.path.join(ROOT, "include"), src])
+    # every native method CudaAligner.java declares has its JNI symbol in the glue
+    java = open(os.path.join(ROOT, "java", "au", "edu", "wehi", "idsv", "alignment", "CudaAligner.java")).read()
+    glue = open(src).read()
+    for name in re.findall(r"private static native \w+(?:\[\])? (\w+)\(", java):
+        assert f"Java_au_edu_wehi_idsv_alignment_CudaAligner_{name}(" in glue, name
