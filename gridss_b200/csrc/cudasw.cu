@@ -374,10 +374,10 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     CK(cudaEventRecord(chunk_ev[ci].pack0, st));
     {
         const int64_t tq = q_hi - q_lo, tw = w_hi - w_lo;
-        int64_t thr = (tq + 15) / 16;
+        int64_t thr = (tq + 31) / 32;
         int blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
         if (tq > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u, nullptr); launches++; }
-        thr = (tw + 15) / 16;
+        thr = (tw + 31) / 32;
         blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
         if (tw > 0 && !gather) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u, any_n); launches++; }
     }

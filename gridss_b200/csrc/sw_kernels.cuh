@@ -34,31 +34,49 @@ __device__ __forceinline__ uint32_t base_code(uint32_t c) {
 #ifdef CUSW_MAIN_TU
 // Elementwise encode of a whole blob (layout unchanged, so per-pair offsets still apply).
 // HBM-bound: 1 byte in, 1 byte out; 16-byte vector accesses.
+__device__ __forceinline__ uint32_t encode_word(uint32_t w, uint32_t xor_word, bool& seen_n) {
+    // four bases per word, byte-parallel: upper-case, compare against A/C/G/T, everything else is N (4)
+    const uint32_t u = w & 0xDFDFDFDFu;
+    const uint32_t mC = __vcmpeq4(u, 0x43434343u), mG = __vcmpeq4(u, 0x47474747u), mT = __vcmpeq4(u, 0x54545454u);
+    const uint32_t mN = ~(__vcmpeq4(u, 0x41414141u) | mC | mG | mT);
+    const uint32_t cw = (mC & 0x01010101u) | (mG & 0x02020202u) | (mT & 0x03030303u) | (mN & 0x04040404u);
+    seen_n |= mN != 0u;
+    return (cw | (cw << 4)) ^ xor_word;
+}
+
 __global__ void __launch_bounds__(256) encode_kernel(const uint8_t* __restrict__ in,
                                                      uint8_t* __restrict__ out, int64_t n,
                                                      uint32_t xor_mask, int* __restrict__ any_n) {
     bool seen_n = false;
-    int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 16;
+    const uint32_t xw = xor_mask * 0x01010101u;
+    // a chunk starts at an arbitrary byte of the blob; input and output share the layout, hence the misalignment:
+    // the first `head` bytes go one by one, the body in 16-byte vectors
+    const bool same = ((reinterpret_cast<uintptr_t>(in) ^ reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+    int64_t head = same ? (int64_t)((16 - (reinterpret_cast<uintptr_t>(in) & 15)) & 15) : n;
+    if (head > n) head = n;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (int64_t k = tid; k < head; k += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t code = base_code(in[k]);
+        seen_n |= code == 4u;
+        out[k] = (uint8_t)((code * 0x11u) ^ xor_mask);
+    }
+    in += head; out += head; n -= head;
+    // 32 bytes per thread and iteration (two 16-byte loads in flight before the first use)
+    int64_t i = tid * 32;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 32;
     for (; i < n; i += stride) {
-        if (i + 16 <= n && ((reinterpret_cast<uintptr_t>(in + i) | reinterpret_cast<uintptr_t>(out + i)) & 15) == 0) {
-            uint4 v = *reinterpret_cast<const uint4*>(in + i);
-            uint32_t wds[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                uint32_t r = 0;
-#pragma unroll
-                for (int b = 0; b < 4; b++)
-                {
-                    const uint32_t code = base_code((wds[k] >> (8 * b)) & 0xFFu);
-                    seen_n |= code == 4u;
-                    r |= ((code * 0x11u) ^ xor_mask) << (8 * b);
-                }
-                wds[k] = r;
-            }
-            *reinterpret_cast<uint4*>(out + i) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+        if (i + 32 <= n) {
+            const uint4 v0 = __ldcs(reinterpret_cast<const uint4*>(in + i));
+            const uint4 v1 = __ldcs(reinterpret_cast<const uint4*>(in + i + 16));
+            uint4 o0, o1;
+            o0.x = encode_word(v0.x, xw, seen_n); o0.y = encode_word(v0.y, xw, seen_n);
+            o0.z = encode_word(v0.z, xw, seen_n); o0.w = encode_word(v0.w, xw, seen_n);
+            o1.x = encode_word(v1.x, xw, seen_n); o1.y = encode_word(v1.y, xw, seen_n);
+            o1.z = encode_word(v1.z, xw, seen_n); o1.w = encode_word(v1.w, xw, seen_n);
+            *reinterpret_cast<uint4*>(out + i) = o0;
+            *reinterpret_cast<uint4*>(out + i + 16) = o1;
         } else {
-            for (int64_t k = i; k < n && k < i + 16; k++) {
+            for (int64_t k = i; k < n && k < i + 32; k++) {
                 const uint32_t code = base_code(in[k]);
                 seen_n |= code == 4u;
                 out[k] = (uint8_t)((code * 0x11u) ^ xor_mask);
