@@ -109,6 +109,9 @@ ABI = [
     ("cudasw_outstanding", _i64, [_vp]),
     ("cudasw_processed", _i64, [_vp]),
     ("cudasw_poll", ctypes.c_int, [_vp, _i64, _vp, _vp, _i32, ctypes.POINTER(_i32)]),
+    ("cudasw_wait", ctypes.c_int, [_vp, _i64, _i64, _vp, _vp, _i32, ctypes.POINTER(_i32)]),
+    ("cudasw_dispatcher_start", ctypes.c_int, [_vp, _i64, _i64]),
+    ("cudasw_dispatcher_stop", ctypes.c_int, [_vp]),
     ("cudasw_get_stats", ctypes.c_int, [_vp, ctypes.POINTER(Stats)]),
     ("cudasw_variant_for", ctypes.c_int, [_vp, _i32, ctypes.POINTER(_i32), ctypes.POINTER(_i32), ctypes.POINTER(_i32)]),
     ("cudasw_last_error", ctypes.c_char_p, [_vp]),
@@ -383,6 +386,38 @@ class CudaAligner(Aligner):
 
     def processed(self) -> int:
         return int(self._lib.cudasw_processed(self._h))
+
+    def start_dispatcher(self, max_pairs: int = 65536, max_delay_ms: float = 2.0) -> None:
+        """One native thread turns the submit stream into GPU batches (size- or age-triggered flush)."""
+        rc = self._lib.cudasw_dispatcher_start(self._h, int(max_pairs), int(max_delay_ms * 1000))
+        if rc != 0:
+            raise CudaSwError(f"cudasw_dispatcher_start failed ({rc})")
+
+    def stop_dispatcher(self) -> None:
+        rc = self._lib.cudasw_dispatcher_stop(self._h)
+        if rc != 0:
+            raise CudaSwError(f"cudasw_dispatcher_stop failed ({rc}): {self._err()}")
+
+    def wait(self, ticket: int, timeout_ms: int = -1) -> Alignment | None:
+        """Blocking getAlignment for one ticket (None on timeout). Releases the GIL while waiting."""
+        res = np.zeros(1, dtype=RESULT_DTYPE)
+        cap = 256
+        while True:
+            cig = np.zeros(cap, dtype=np.uint32)
+            need = ctypes.c_int32(0)
+            rc = self._lib.cudasw_wait(self._h, ticket, timeout_ms, res.ctypes.data, cig.ctypes.data, cap, ctypes.byref(need))
+            if rc == CUDASW_ENOMEM and need.value > cap:
+                cap = need.value
+                continue
+            break
+        if rc == 0:
+            return None
+        if rc < 0:
+            raise KeyError(f"unknown ticket {ticket}")
+        r = res[0]
+        if r["status"] != 0:
+            raise CudaSwError(f"pair failed with status {int(r['status'])}")
+        return Alignment(int(r["ref_begin"]), cigar_string(cig[: need.value]), int(r["score"]))
 
     def poll(self, ticket: int) -> Alignment | None:
         res = np.zeros(1, dtype=RESULT_DTYPE)

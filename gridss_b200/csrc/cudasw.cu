@@ -12,7 +12,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
+#include <unordered_set>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -128,6 +132,13 @@ struct cudasw {
         std::vector<uint32_t> cigar;
     };
     std::unordered_map<int64_t, Done> done;
+    std::unordered_set<int64_t> live;  // submitted and not yet delivered (pending, on the GPU, or done)
+    std::mutex qmu;                    // guards the queue state above; `mu` guards the engine itself
+    std::condition_variable cv_work, cv_done;
+    std::thread disp;
+    bool disp_run = false;
+    int64_t disp_max_pairs = 0, disp_delay_us = 0;
+    std::chrono::steady_clock::time_point first_pending;
 
     void set_error(const std::string& s) { error = s; }
     int pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so, const uint8_t* d_ref,
@@ -288,6 +299,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
 
 extern "C" void cudasw_destroy(cudasw_t* h) {
     if (!h) return;
+    cudasw_dispatcher_stop(h);
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
@@ -672,7 +684,8 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     struct Chunk { int64_t first, cnt, q_lo, q_hi, w_lo, w_hi; };
     std::vector<Chunk> chunks;
     {
-        // Host inputs: chunk sizes grow geometrically (64 MB, 128 MB, ... capped at 1 GB): the first copy is the only one
+        // Host inputs: chunk sizes grow geometrically (64 MB, 160 MB, 400 MB, ... capped at 4 GB; a pinned copy runs about
+        // 2.5x faster than the kernels consume the bytes): the first copy is the only one
         // the kernels have to wait for, and each later copy hides behind the (slower) kernels of the chunk before it.
         // Resident inputs: one chunk. (Splitting them so that the pack of chunk i+1 runs beside the forward pass of chunk i
         // was measured neutral on B200: the forward kernel fills the register file, so whatever runs beside it takes SM
@@ -681,7 +694,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         const bool ppc = getenv("CUDASW_POST_PER_CHUNK") != nullptr;
         const bool pipelined = ppc && !getenv("CUDASW_NO_OVERLAP") && total_bytes >= ((int64_t)256 << 20);
         int64_t target = inputs_on_host ? (int64_t)64 << 20 : (pipelined ? std::max<int64_t>(total_bytes / 16, 1) : (int64_t)1 << 60);
-        int64_t target_max = inputs_on_host ? (int64_t)1 << 30 : (pipelined && ppc ? std::max<int64_t>(5 * total_bytes / 16, 1) : (int64_t)1 << 60);
+        int64_t target_max = inputs_on_host ? (int64_t)4 << 30 : (pipelined && ppc ? std::max<int64_t>(5 * total_bytes / 16, 1) : (int64_t)1 << 60);
         const int64_t tail_bytes = pipelined && ppc ? total_bytes / 16 : 0;
         // windows gathered on the device: only queries and descriptors cross PCIe (~1/12 of the bytes), so the copy of
         // everything behind the small leading chunk hides behind that chunk
@@ -727,7 +740,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
             }
             chunks.push_back(c);
             first = last;
-            target = fixed_target ? target : (inputs_on_host && !gather ? std::min(target * 2, std::max(target, target_max)) : target_max);
+            target = fixed_target ? target : (inputs_on_host && !gather ? std::min(target * 5 / 2, std::max(target, target_max)) : target_max);
         }
     }
     int64_t max_cnt = 0;
@@ -1069,17 +1082,38 @@ extern "C" int cudasw_variant_for(cudasw_t* h, int32_t q, int32_t* lanes, int32_
     return CUDASW_OK;
 }
 
-// ---- async trio (StreamingAligner.java:10-44 contract)
+// ---- async interface (StreamingAligner.java:10-44 contract) + dispatcher thread (SURVEY.md §8b "Threading")
+// The queue has its own mutex (qmu): submit / poll / wait never block behind a running GPU batch (mu).
+static int deliver_locked(cudasw_t* h, std::unordered_map<int64_t, cudasw::Done>::iterator it, cudasw_result* res,
+                          uint32_t* cigar, int32_t cigar_cap, int32_t* cigar_len) {
+    int32_t need = (int32_t)it->second.cigar.size();
+    if (cigar_len) *cigar_len = need;
+    if (need > cigar_cap || (need && !cigar)) return CUDASW_ENOMEM;
+    *res = it->second.r;
+    if (need) memcpy(cigar, it->second.cigar.data(), (size_t)need * 4);
+    h->live.erase(it->first);
+    h->done.erase(it);
+    return 1;
+}
+
 extern "C" int cudasw_submit(cudasw_t* h, const uint8_t* seq, int64_t seq_len, const uint8_t* ref,
                              int64_t ref_len, int64_t* ticket) {
     if (!h || !ticket || seq_len < 0 || ref_len < 0 || (seq_len && !seq) || (ref_len && !ref)) return CUDASW_EINVAL;
-    std::lock_guard<std::mutex> lock(h->mu);
-    h->pend_seq.insert(h->pend_seq.end(), seq, seq + seq_len);
-    h->pend_ref.insert(h->pend_ref.end(), ref, ref + ref_len);
-    h->pend_seq_off.push_back((int64_t)h->pend_seq.size());
-    h->pend_ref_off.push_back((int64_t)h->pend_ref.size());
-    *ticket = h->next_ticket++;
-    h->pend_tickets.push_back(*ticket);
+    bool wake;
+    {
+        std::lock_guard<std::mutex> lock(h->qmu);
+        if (h->pend_tickets.empty()) h->first_pending = std::chrono::steady_clock::now();
+        h->pend_seq.insert(h->pend_seq.end(), seq, seq + seq_len);
+        h->pend_ref.insert(h->pend_ref.end(), ref, ref + ref_len);
+        h->pend_seq_off.push_back((int64_t)h->pend_seq.size());
+        h->pend_ref_off.push_back((int64_t)h->pend_ref.size());
+        *ticket = h->next_ticket++;
+        h->pend_tickets.push_back(*ticket);
+        h->live.insert(*ticket);
+        // the dispatcher sleeps with a deadline once something is pending: wake it for the first pair and for a full batch
+        wake = h->disp_run && (h->pend_tickets.size() == 1 || (int64_t)h->pend_tickets.size() >= h->disp_max_pairs);
+    }
+    if (wake) h->cv_work.notify_one();
     return CUDASW_OK;
 }
 
@@ -1088,7 +1122,7 @@ extern "C" int cudasw_flush(cudasw_t* h) {
     std::vector<uint8_t> seq, ref;
     std::vector<int64_t> so, ro, tickets;
     {
-        std::lock_guard<std::mutex> lock(h->mu);
+        std::lock_guard<std::mutex> lock(h->qmu);
         if (h->pend_tickets.empty()) return CUDASW_OK;
         seq.swap(h->pend_seq); ref.swap(h->pend_ref);
         so.swap(h->pend_seq_off); ro.swap(h->pend_ref_off);
@@ -1103,47 +1137,93 @@ extern "C" int cudasw_flush(cudasw_t* h) {
     if (seq.empty()) seq.push_back(0);
     if (ref.empty()) ref.push_back(0);
     int rc = cudasw_align_batch(h, n, seq.data(), so.data(), ref.data(), ro.data(), res.data(), cig.data(), cap, &used);
-    std::lock_guard<std::mutex> lock(h->mu);
-    for (int64_t i = 0; i < n; i++) {
-        cudasw::Done d;
-        d.r = res[i];
-        if (rc != CUDASW_OK && d.r.status == CUDASW_OK) d.r.status = rc;
-        if (rc == CUDASW_OK && d.r.status == CUDASW_OK)
-            d.cigar.assign(cig.begin() + d.r.cigar_off, cig.begin() + d.r.cigar_off + d.r.cigar_len);
-        d.r.cigar_off = 0;
-        h->done.emplace(tickets[i], std::move(d));
+    {
+        std::lock_guard<std::mutex> lock(h->qmu);
+        for (int64_t i = 0; i < n; i++) {
+            cudasw::Done d;
+            d.r = res[i];
+            if (rc != CUDASW_OK && d.r.status == CUDASW_OK) d.r.status = rc;
+            if (rc == CUDASW_OK && d.r.status == CUDASW_OK)
+                d.cigar.assign(cig.begin() + d.r.cigar_off, cig.begin() + d.r.cigar_off + d.r.cigar_len);
+            d.r.cigar_off = 0;
+            h->done.emplace(tickets[i], std::move(d));
+        }
     }
+    h->cv_done.notify_all();
     return rc;
 }
 
 extern "C" int64_t cudasw_outstanding(cudasw_t* h) {
     if (!h) return 0;
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::mutex> lock(h->qmu);
     return (int64_t)h->pend_tickets.size();
 }
 extern "C" int64_t cudasw_processed(cudasw_t* h) {
     if (!h) return 0;
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::mutex> lock(h->qmu);
     return (int64_t)h->done.size();
 }
 
 extern "C" int cudasw_poll(cudasw_t* h, int64_t ticket, cudasw_result* res, uint32_t* cigar,
                            int32_t cigar_cap, int32_t* cigar_len) {
     if (!h || !res) return CUDASW_EINVAL;
-    std::lock_guard<std::mutex> lock(h->mu);
+    std::lock_guard<std::mutex> lock(h->qmu);
     auto it = h->done.find(ticket);
-    if (it == h->done.end()) {
-        for (int64_t t : h->pend_tickets)
-            if (t == ticket) return 0;
-        return CUDASW_EINVAL;
+    if (it == h->done.end()) return h->live.count(ticket) ? 0 : CUDASW_EINVAL;  // pending or on the GPU / unknown
+    return deliver_locked(h, it, res, cigar, cigar_cap, cigar_len);
+}
+
+extern "C" int cudasw_wait(cudasw_t* h, int64_t ticket, int64_t timeout_ms, cudasw_result* res, uint32_t* cigar,
+                           int32_t cigar_cap, int32_t* cigar_len) {
+    if (!h || !res) return CUDASW_EINVAL;
+    std::unique_lock<std::mutex> lock(h->qmu);
+    if (!h->live.count(ticket)) return CUDASW_EINVAL;
+    auto ready = [&] { return h->done.find(ticket) != h->done.end(); };
+    if (timeout_ms < 0) h->cv_done.wait(lock, ready);
+    else if (!h->cv_done.wait_for(lock, std::chrono::milliseconds(timeout_ms), ready)) return 0;
+    return deliver_locked(h, h->done.find(ticket), res, cigar, cigar_cap, cigar_len);
+}
+
+// Dispatcher: one thread per engine that turns the submit stream into GPU batches, flushing when `max_pairs` are
+// pending or the oldest pending pair has waited `max_delay_us` (BwaStreamingAligner.java:79-127: size-triggered flush
+// by a single driver thread). Worker threads then only submit and wait.
+static void dispatcher_main(cudasw_t* h) {
+    std::unique_lock<std::mutex> lock(h->qmu);
+    while (h->disp_run) {
+        if (h->pend_tickets.empty()) { h->cv_work.wait(lock); continue; }
+        const auto deadline = h->first_pending + std::chrono::microseconds(h->disp_delay_us);
+        if ((int64_t)h->pend_tickets.size() < h->disp_max_pairs && std::chrono::steady_clock::now() < deadline) {
+            h->cv_work.wait_until(lock, deadline);
+            continue;
+        }
+        lock.unlock();
+        cudasw_flush(h);  // errors reach the callers as per-pair status
+        lock.lock();
     }
-    int32_t need = (int32_t)it->second.cigar.size();
-    if (cigar_len) *cigar_len = need;
-    if (need > cigar_cap || (need && !cigar)) return CUDASW_ENOMEM;
-    *res = it->second.r;
-    if (need) memcpy(cigar, it->second.cigar.data(), (size_t)need * 4);
-    h->done.erase(it);
-    return 1;
+}
+
+extern "C" int cudasw_dispatcher_start(cudasw_t* h, int64_t max_pairs, int64_t max_delay_us) {
+    if (!h || max_pairs <= 0 || max_delay_us < 0) return CUDASW_EINVAL;
+    std::lock_guard<std::mutex> lock(h->qmu);
+    if (h->disp_run) return CUDASW_EINVAL;
+    h->disp_max_pairs = max_pairs;
+    h->disp_delay_us = max_delay_us;
+    h->disp_run = true;
+    h->first_pending = std::chrono::steady_clock::now();
+    h->disp = std::thread(dispatcher_main, h);
+    return CUDASW_OK;
+}
+
+extern "C" int cudasw_dispatcher_stop(cudasw_t* h) {
+    if (!h) return CUDASW_EINVAL;
+    {
+        std::lock_guard<std::mutex> lock(h->qmu);
+        if (!h->disp_run) return CUDASW_OK;
+        h->disp_run = false;
+    }
+    h->cv_work.notify_all();
+    if (h->disp.joinable()) h->disp.join();
+    return cudasw_flush(h);  // nothing stays pending behind a stopped dispatcher
 }
 
 extern "C" int cudasw_cigar_string(const uint32_t* ops, int32_t n_ops, char* buf, int32_t cap) {

@@ -788,11 +788,18 @@ __device__ __forceinline__ int tb_sub(const TbConst& tc, uint32_t qb, uint32_t r
 // Returns number of M/I/D ops, or a negative status.
 // center < 0: the reference's flat layout (row i starts at its first in-band column). center >= 0: band-frame layout
 // of sw_traceback_kernel, cell (i, j) at dir[width_d * i + (j - i + center)].
+// Ops come out last-to-first. With `outp` they are written to their final place (needs the total, i.e. a second walk);
+// with `buf` the first kTbOpsBuf of them are kept in walk order, so that the usual short CIGAR needs one walk only.
+constexpr int kTbOpsBuf = 12;
 __device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, int readLen,
-                       int refLen, uint32_t* outp, int total_ops, int center = -1) {
+                       int refLen, uint32_t* outp, int total_ops, int center = -1, uint32_t* buf = nullptr) {
     int i = readLen - 1, j = refLen - 1;
     int e = 0, l = 0, state = 2;
     int op = 0, prev_op = 0;  // 0 = M, 1 = I, 2 = D
+    auto put = [&](int idx, uint32_t v) {
+        if (outp) outp[total_ops - idx] = v;
+        if (buf && idx <= kTbOpsBuf) buf[idx - 1] = v;
+    };
     while (i > 0) {
         const int xi = max(i - band, 0);
         const int jj = j - xi;
@@ -811,20 +818,18 @@ __device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, i
         if (op == prev_op) ++e;
         else {
             ++l;
-            if (outp) outp[total_ops - l] = ((uint32_t)e << 4) | (uint32_t)prev_op;
+            put(l, ((uint32_t)e << 4) | (uint32_t)prev_op);
             prev_op = op;
             e = 1;
         }
     }
     if (op == 0) {
         ++l;
-        if (outp) outp[total_ops - l] = ((uint32_t)(e + 1) << 4) | 0u;
+        put(l, ((uint32_t)(e + 1) << 4) | 0u);
     } else {
         l += 2;
-        if (outp) {
-            outp[total_ops - (l - 1)] = ((uint32_t)e << 4) | (uint32_t)op;
-            outp[total_ops - l] = (1u << 4) | 0u;
-        }
+        put(l - 1, ((uint32_t)e << 4) | (uint32_t)op);
+        put(l, (1u << 4) | 0u);
     }
     return l;
 }
@@ -884,7 +889,8 @@ __device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begi
                                         int read_end, int nbody, const uint8_t* dirp, int width_d, int band,
                                         int readLen, int refLen, cudasw_result r, cudasw_result* __restrict__ res,
                                         uint32_t* __restrict__ cig, unsigned long long cig_cap,
-                                        unsigned long long* __restrict__ cig_used, int center = -1) {
+                                        unsigned long long* __restrict__ cig_used, int center = -1,
+                                        const uint32_t* buf = nullptr) {
     const int lead = read_begin != 0;
     const int tail = (q - read_end - 1) != 0;
     const int nops = nbody + lead + tail;
@@ -900,7 +906,9 @@ __device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begi
         uint32_t* o = cig + coff;
         if (lead) *o++ = ((uint32_t)read_begin << 4) | CUDASW_CIGAR_S;
         if (score <= 0) *o = (1u << 4) | CUDASW_CIGAR_M;
-        else tb_walk(dirp, width_d, band, readLen, refLen, o, nbody, center);
+        else if (buf && nbody <= kTbOpsBuf) {
+            for (int k = 0; k < nbody; k++) o[k] = buf[nbody - 1 - k];  // kept by the counting walk, last op first
+        } else tb_walk(dirp, width_d, band, readLen, refLen, o, nbody, center);
         if (tail) o[nbody] = ((uint32_t)(q - read_end - 1) << 4) | CUDASW_CIGAR_S;
     } else {
         r.status = CUDASW_ENOMEM;
@@ -931,12 +939,18 @@ __device__ int tb_dp_thread(const TbConst& tc, const uint8_t* __restrict__ ref, 
         rw[x] = (unsigned)j < (unsigned)refLen ? (uint32_t)ref[j] : 0u;
     }
     int mx = 0;
+    // the two bytes a row needs (its query base, the window byte entering the frame after it) are loaded one row ahead
+    uint32_t qb_next = read[0];
+    uint32_t rw_next = BMAX + 1 < refLen ? (uint32_t)ref[BMAX + 1] : 0u;
     for (int i = 0; i < readLen; i++) {
         const int beg = max(i - band, 0);
         const int end = min(i + band, refLen - 1);
         const int endp = min(i - 1 + band, refLen - 1);  // last column of the previous row
         const bool quirk = i >= 1 && i <= band + 1 && end == refLen - 1 && endp == end && end <= 2 * band + 1;
-        const uint32_t qb = read[i];
+        const uint32_t qb = qb_next;
+        const uint32_t rw_in = rw_next;
+        if (i + 1 < readLen) qb_next = read[i + 1];
+        rw_next = i + 2 + BMAX < refLen ? (uint32_t)ref[i + 2 + BMAX] : 0u;
         const int j0 = i - BMAX;
         int hleft = 0, fgap = 0;
         int cur_h = H[0];
@@ -964,8 +978,7 @@ __device__ int tb_dp_thread(const TbConst& tc, const uint8_t* __restrict__ ref, 
         // slide the window bytes: the frame of row i+1 starts one column further right
 #pragma unroll
         for (int x = 0; x + 1 < WMAX; x++) rw[x] = rw[x + 1];
-        const int jn = i + 1 + BMAX;
-        rw[WMAX - 1] = jn < refLen ? (uint32_t)ref[jn] : 0u;
+        rw[WMAX - 1] = rw_in;
     }
     return mx;
 }
@@ -994,6 +1007,7 @@ sw_traceback_kernel(const int* __restrict__ list, int n_own, const int* __restri
         const int score = f.x;
 
         int nbody = 0;
+        uint32_t opsbuf[kTbOpsBuf];
         int ref_begin = -1, read_begin = 0, ref_end = f.y, read_end = f.z;
         const uint8_t* dirp = nullptr;
         constexpr int width_d = (2 * BMAX + 1 + 3) & ~3;
@@ -1039,11 +1053,11 @@ sw_traceback_kernel(const int* __restrict__ list, int n_own, const int* __restri
                 band *= 2;
             }
             if (!done) continue;
-            nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0, BMAX);
+            nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0, BMAX, opsbuf);
             if (nbody < 0) { res[pair].status = nbody; continue; }
         }
         tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen, r,
-                res, cig, cig_cap, cig_used, BMAX);
+                res, cig, cig_cap, cig_used, BMAX, opsbuf);
     }
 }
 
@@ -1131,10 +1145,11 @@ sw_traceback_warp_kernel(const int* __restrict__ list, int n, const int* __restr
     }
     __syncwarp();  // every lane's direction bytes are visible to lane 0
     if (ok && lane == 0) {
-        const int nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0);
+        uint32_t opsbuf[kTbOpsBuf];
+        const int nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0, -1, opsbuf);
         if (nbody < 0) res[pair].status = nbody;
         else tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen,
-                     r, res, cig, cig_cap, cig_used);
+                     r, res, cig, cig_cap, cig_used, -1, opsbuf);
     }
     __syncwarp();
     }  // pairs of this warp

@@ -64,6 +64,18 @@ __device__ int tb_dp_warp(const TbConst& tc, const uint8_t* __restrict__ ref, co
         for (int x = 0; x < nd; x++)
             if (kb + x < W) row[kb + x] = make_int2(0, 0);
     int mx = 0;
+    // register-resident instantiations keep the window bytes of the lane's diagonals in registers too: they slide by
+    // one column per row, so a row costs one global byte load (issued a row ahead) instead of D
+    uint32_t rwin[D > 0 ? D : 1];
+    uint32_t qb_next = 0;
+    if (D > 0) {
+#pragma unroll
+        for (int x = 0; x < (D > 0 ? D : 1); x++) {
+            const int j = kb - band + x;
+            rwin[x] = (unsigned)j < (unsigned)refLen ? (uint32_t)ref[j] : 0u;
+        }
+        qb_next = read[0];
+    }
     int out_h = 0, out_f = 0;      // (H, F) after this lane's last diagonal in its latest row
     int first_h = 0, first_e = 0;  // (H, E) of this lane's first diagonal in its latest row
     const int steps = 2 * readLen + 31;
@@ -79,9 +91,15 @@ __device__ int tb_dp_warp(const TbConst& tc, const uint8_t* __restrict__ ref, co
             const int end = min(i + band, refLen - 1);
             const int endp = min(i - 1 + band, refLen - 1);  // last column of the previous row
             const bool quirk = i >= 1 && i <= band + 1 && end == refLen - 1 && endp == end && end <= 2 * band + 1;
-            const uint32_t qb = read[i];
+            const uint32_t qb = D > 0 ? qb_next : (uint32_t)read[i];
             uint8_t* drow = dir + (long long)W * i - beg;
             const int j0 = kb + i - band;  // column of this lane's first diagonal
+            uint32_t rw_in = 0u;
+            if (D > 0) {  // what the next row of this lane needs, in flight while this row is computed
+                if (i + 1 < readLen) qb_next = read[i + 1];
+                const int jn = j0 + D;
+                if ((unsigned)jn < (unsigned)refLen) rw_in = ref[jn];
+            }
             int hleft = 0, fgap = 0;
             if (j0 > beg) { hleft = left_h; fgap = left_f; }  // else: row border (h_c[0] = 0, f = 0)
             // (H, E) of row i-1 at this lane's first diagonal is the diagonal neighbour of the first cell
@@ -99,13 +117,18 @@ __device__ int tb_dp_warp(const TbConst& tc, const uint8_t* __restrict__ ref, co
                     const int hdiag = (i >= 1 && j >= 1) ? cur.x : 0;
                     int h, e;
                     uint8_t dv;
-                    tb_cell(tc, i, up_h, up_e, hdiag, tb_sub(tc, qb, ref[j]), hleft, fgap, mx, h, e, dv);
+                    tb_cell(tc, i, up_h, up_e, hdiag, tb_sub(tc, qb, D > 0 ? rwin[x < (D > 0 ? D : 1) ? x : 0] : (uint32_t)ref[j]), hleft, fgap, mx, h, e, dv);
                     drow[j] = dv;
                     if (D > 0) st[x < D ? x : 0] = make_int2(h, e); else row[kb + x] = make_int2(h, e);
                     if (x == 0) { first_h = h; first_e = e; }
                     out_h = h; out_f = fgap;
                 }
                 cur = nxt;
+            }
+            if (D > 0) {
+#pragma unroll
+                for (int x = 0; x + 1 < (D > 0 ? D : 1); x++) rwin[x] = rwin[x + 1];
+                rwin[(D > 0 ? D : 1) - 1] = rw_in;
             }
         }
     }

@@ -177,6 +177,17 @@ int cudasw_multi_align_batch_windows(cudasw_multi_t* m, int64_t n_pairs, const u
 int cudasw_multi_get_stats(cudasw_multi_t* m, int idx, cudasw_stats* out, int64_t* first_pair, int64_t* n_pairs);
 const char* cudasw_multi_last_error(cudasw_multi_t* m); /* m may be NULL: last create() error */
 
+/* Blocking poll: waits up to timeout_ms (< 0: no limit) for the ticket; returns like cudasw_poll (0 = timed out). */
+int cudasw_wait(cudasw_t* h, int64_t ticket, int64_t timeout_ms, cudasw_result* res, uint32_t* cigar,
+                int32_t cigar_cap, int32_t* cigar_len);
+/* Dispatcher thread of the batch-collect layer (SURVEY.md 8b "Threading", 8f N1): flushes when max_pairs are pending or
+ * the oldest pending pair has waited max_delay_us, so that GRIDSS's worker threads (ParallelTransformIterator,
+ * AnnotateInexactHomology.java:17-21) only cudasw_submit and cudasw_wait. Modelled on BwaStreamingAligner's single
+ * driver thread with a size-triggered flush (BwaStreamingAligner.java:79-127). submit / poll / wait are thread-safe and
+ * do not block behind a running GPU batch. stop() flushes what is pending; destroy() stops the dispatcher. */
+int cudasw_dispatcher_start(cudasw_t* h, int64_t max_pairs, int64_t max_delay_us);
+int cudasw_dispatcher_stop(cudasw_t* h);
+
 int cudasw_get_stats(cudasw_t* h, cudasw_stats* out);
 /* Which score-pass kernel variant a query of `query_len` rows is dispatched to: lanes per pair (G),
  * rows per virtual lane (R), strips (1 unless strip-mined). For reporting (bench.py roofline line). */

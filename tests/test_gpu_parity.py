@@ -443,3 +443,50 @@ def test_multi_handle_windows(aligner):
         assert np.array_equal(res1[f], resm[f]), f
     assert all(_cig(res1, cig1, i) == _cig(resm, cigm, i) for i in range(len(segs)))
     ma.close()
+
+
+def test_dispatcher_thread_batches_concurrent_submitters(oracle, synth):
+    """worker threads only submit + wait; one native dispatcher thread turns the stream into GPU batches"""
+    import threading
+
+    import gridss_b200 as gb
+
+    al = gb.CudaAligner()
+    seqs, refs = synth.adversarial("mutated", 1200, seed=31, qmax=150, wmax=400)
+    m = oracle.model_align(seqs, refs, threads=8)
+    al.start_dispatcher(max_pairs=256, max_delay_ms=1.0)
+    got = [None] * len(seqs)
+    errs = []
+
+    def worker(k, nthreads):
+        try:
+            for i in range(k, len(seqs), nthreads):
+                t = al.submit(seqs[i], refs[i])
+                if i % 3 == 0:          # some wait at once (age-triggered flush), some collect later
+                    got[i] = al.wait(t, 20000)
+                else:
+                    got[i] = t
+            for i in range(k, len(seqs), nthreads):
+                if isinstance(got[i], int):
+                    got[i] = al.wait(got[i], 20000)
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+
+    ths = [threading.Thread(target=worker, args=(k, 6)) for k in range(6)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs[:1]
+    for i in range(len(seqs)):
+        assert got[i] is not None, i
+        assert (got[i].score, got[i].getStartPosition(), got[i].getCigar()) == m.tuple(i), i
+    assert al.outstanding() == 0 and al.processed() == 0
+    with pytest.raises(KeyError):
+        al.wait(10**9, 10)
+    # stop() flushes what is pending; the ticket can still be collected
+    t = al.submit(b"ACGTACGTAC", b"TTACGTACGTACTT")
+    al.stop_dispatcher()
+    a = al.wait(t, 5000)
+    assert a is not None and a.getCigar() == "10M"
+    al.close()
