@@ -1,0 +1,81 @@
+#!/usr/bin/env python
+"""Turns the raw ncu outputs of tools/gpu_session.sh (gpurun_out/) into the tracked summaries under profiles/.
+
+  python tools/profile_summaries.py r01z        # tag of the session
+"""
+import collections
+import csv
+import io
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+O = os.path.join(ROOT, "gpurun_out")
+P = os.path.join(ROOT, "profiles")
+KEYS = [
+    "gpu__time_duration.sum", "launch__grid_size", "launch__registers_per_thread", "launch__occupancy_limit_registers",
+    "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "smsp__inst_executed.sum", "sm__cycles_elapsed.avg", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "dram__throughput.avg.pct_of_peak_sustained_elapsed", "smsp__thread_inst_executed_per_inst_executed.ratio",
+    "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
+    "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio",
+]
+
+
+def launch_list(tag, cmd):
+    rows = list(csv.reader(l for l in open(os.path.join(O, f"launches_{tag}.csv")) if l.startswith('"')))
+    h = rows[0]
+    ki, vi, ui = h.index("Kernel Name"), h.index("Metric Value"), h.index("Metric Unit")
+    agg = collections.OrderedDict()
+    for r in rows[1:]:
+        k = re.sub(r"\(.*", "", r[ki])
+        v = float(r[vi].replace(",", ""))
+        v = v / 1e6 if r[ui] in ("ns", "nsecond") else v / 1e3 if r[ui] in ("us", "usecond") else v
+        a = agg.setdefault(k, [0, 0.0])
+        a[0] += 1
+        a[1] += v
+    tot = sum(a[1] for a in agg.values())
+    out = [f"# ncu launch list ({tag})", "", f"`ncu --metrics gpu__time_duration.sum --clock-control none -c 900 {cmd}`",
+           "(per-launch times are cold-cache and serialised: compare shares)", "", "| total ms | share | launches | kernel |", "|---|---|---|---|"]
+    for k, a in sorted(agg.items(), key=lambda x: -x[1][1])[:28]:
+        out.append(f"| {a[1]:.3f} | {100 * a[1] / tot:.2f}% | {a[0]} | `{k[:100]}` |")
+    out.append(f"| {tot:.3f} | 100% | {sum(a[0] for a in agg.values())} | all {len(agg)} kernels |")
+    open(os.path.join(P, f"launches_{tag}.md"), "w").write("\n".join(out) + "\n")
+    import shutil
+    shutil.copy(os.path.join(O, f"launches_{tag}.csv"), os.path.join(P, f"launches_{tag}.csv"))
+
+
+def full_capture(rep, name, title, cmd, notes=""):
+    raw = subprocess.run(["ncu", "-i", os.path.join(O, rep), "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    h, u, v = rows[0], rows[1], rows[2]
+    out = [f"# ncu --set full, {title}", "", f"`{cmd}`", "", "| metric | unit | value |", "|---|---|---|"]
+    for k in ["Kernel Name", "Grid Size"] + KEYS:
+        if k in h:
+            i = h.index(k)
+            out.append(f"| {k} | {u[i]} | {v[i]} |")
+    if notes:
+        out += ["", notes]
+    open(os.path.join(P, name), "w").write("\n".join(out) + "\n")
+    return {k: v[h.index(k)] for k in h if k in KEYS}
+
+
+if __name__ == "__main__":
+    tag = sys.argv[1]
+    cmd = "python bench.py --steps 2 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows"
+    launch_list(tag, cmd)
+    for rep, name, title, kre in ((f"prof_fwd_{tag}.ncu-rep", f"ncu_fwd_{tag}.md", "forward score kernel", "sw_score_kernel -s 2"),
+                                  (f"prof_tb_{tag}.ncu-rep", f"ncu_tb_{tag}.md", "one-thread traceback kernel", "sw_traceback_kernel -s 5"),
+                                  (f"prof_enc_{tag}.ncu-rep", f"ncu_enc_{tag}.md", "encode kernel (load phase)", "encode_kernel -s 9")):
+        if os.path.exists(os.path.join(O, rep)):
+            m = full_capture(rep, name, title, f"ncu --set full --clock-control none --import-source on -k regex:{kre} -c 1 {cmd}")
+            print(name, {k: m[k] for k in list(m)[:6]})
