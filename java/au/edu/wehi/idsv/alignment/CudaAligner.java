@@ -20,22 +20,32 @@ public class CudaAligner implements Aligner, AutoCloseable {
 		if (ref == null || ref.length == 0) throw new IllegalArgumentException("ref must be non-zero size");
 		return alignBatch(new byte[][] { seq }, new byte[][] { ref })[0];
 	}
-	/** One JNI round trip for the whole batch. */
-	public Alignment[] alignBatch(byte[][] seqs, byte[][] refs) {
+	// pinned staging (page-locked direct buffers from the native side), grown on demand and reused across batches
+	private java.nio.ByteBuffer pinSeq, pinRef, pinSeqOff, pinRefOff;
+	private java.nio.ByteBuffer pinned(java.nio.ByteBuffer cur, long bytes) {
+		if (cur != null && cur.capacity() >= bytes) { cur.clear(); return cur; }
+		if (cur != null) freePinned(cur);
+		java.nio.ByteBuffer b = allocPinned(Math.max(4096, bytes + bytes / 4));
+		if (b == null) throw new OutOfMemoryError("cudasw_host_alloc failed");
+		return b.order(java.nio.ByteOrder.LITTLE_ENDIAN);
+	}
+	/** One JNI round trip for the whole batch; the pairs are packed straight into pinned host buffers. */
+	public synchronized Alignment[] alignBatch(byte[][] seqs, byte[][] refs) {
 		int n = seqs.length;
-		long[] seqOff = new long[n + 1], refOff = new long[n + 1];
+		long tq = 0, tw = 0;
+		for (int i = 0; i < n; i++) { tq += seqs[i].length; tw += refs[i].length; }
+		pinSeq = pinned(pinSeq, tq); pinRef = pinned(pinRef, tw);
+		pinSeqOff = pinned(pinSeqOff, 8L * (n + 1)); pinRefOff = pinned(pinRefOff, 8L * (n + 1));
+		long so = 0, ro = 0;
+		pinSeqOff.putLong(0); pinRefOff.putLong(0);
 		for (int i = 0; i < n; i++) {
-			seqOff[i + 1] = seqOff[i] + seqs[i].length;
-			refOff[i + 1] = refOff[i] + refs[i].length;
-		}
-		byte[] seqBlob = new byte[(int) seqOff[n]], refBlob = new byte[(int) refOff[n]];
-		for (int i = 0; i < n; i++) {
-			System.arraycopy(seqs[i], 0, seqBlob, (int) seqOff[i], seqs[i].length);
-			System.arraycopy(refs[i], 0, refBlob, (int) refOff[i], refs[i].length);
+			pinSeq.put(seqs[i]); pinRef.put(refs[i]);
+			so += seqs[i].length; ro += refs[i].length;
+			pinSeqOff.putLong(so); pinRefOff.putLong(ro);
 		}
 		int[] start = new int[n], status = new int[n];
 		String[] cigar = new String[n];
-		int rc = alignBatch(handle, n, seqBlob, seqOff, refBlob, refOff, start, cigar, status);
+		int rc = alignBatchPinned(handle, n, pinSeq, pinSeqOff, pinRef, pinRefOff, start, cigar, status);
 		if (rc != 0) throw new IllegalStateException("cudasw_align_batch failed (" + rc + "): " + lastError(handle));
 		Alignment[] out = new Alignment[n];
 		for (int i = 0; i < n; i++) {
@@ -94,10 +104,18 @@ public class CudaAligner implements Aligner, AutoCloseable {
 		return out;
 	}
 	@Override
-	public void close() { if (handle != 0) { destroy(handle); handle = 0; } }
+	public synchronized void close() {
+		for (java.nio.ByteBuffer b : new java.nio.ByteBuffer[] { pinSeq, pinRef, pinSeqOff, pinRefOff }) if (b != null) freePinned(b);
+		pinSeq = pinRef = pinSeqOff = pinRefOff = null;
+		if (handle != 0) { destroy(handle); handle = 0; }
+	}
 	private static native long create(int match, int mismatch, int ambiguous, int gapOpen, int gapExtend, int device);
 	private static native void destroy(long handle);
 	private static native String lastError(long handle);
+	private static native java.nio.ByteBuffer allocPinned(long bytes);
+	private static native void freePinned(java.nio.ByteBuffer buf);
+	private static native int alignBatchPinned(long handle, int n, java.nio.ByteBuffer seqBlob, java.nio.ByteBuffer seqOff,
+			java.nio.ByteBuffer refBlob, java.nio.ByteBuffer refOff, int[] startOut, String[] cigarOut, int[] statusOut);
 	private static native int loadReference(long handle, byte[] bases, long[] contigOff);
 	private static native int alignBatchWindows(long handle, int n, byte[] seqBlob, long[] seqOff, int[] segContig, int[] segFlags,
 			long[] segStart, long[] segEnd, long[] winOff, int[] startOut, String[] cigarOut, int[] statusOut);

@@ -123,3 +123,34 @@ JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_alignBatchWin
     free(win);
     return rc;
 }
+
+/* Pinned staging as direct ByteBuffers (north_star: "packs ... sequences and reference windows into pinned host
+ * buffers"): the Java side packs a batch straight into page-locked memory, so cudasw_align_batch's H2D copies run at
+ * PCIe speed and overlap the kernels; no JVM-heap array is touched by the native side. */
+JNIEXPORT jobject JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_allocPinned(JNIEnv* env, jclass c, jlong bytes) {
+    void* p = NULL;
+    if (bytes <= 0 || cudasw_host_alloc((size_t)bytes, &p) != CUDASW_OK) return NULL;
+    return (*env)->NewDirectByteBuffer(env, p, bytes);
+}
+JNIEXPORT void JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_freePinned(JNIEnv* env, jclass c, jobject buf) {
+    void* p = buf ? (*env)->GetDirectBufferAddress(env, buf) : NULL;
+    if (p) cudasw_host_free(p);
+}
+/* All four inputs are direct buffers from allocPinned (offsets as little-endian int64, n+1 entries each). */
+JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_alignBatchPinned(JNIEnv* env, jclass c, jlong h, jint n,
+        jobject seqBlob, jobject seqOff, jobject refBlob, jobject refOff, jintArray startOut, jobjectArray cigarOut,
+        jintArray statusOut) {
+    const uint8_t* s = (const uint8_t*)(*env)->GetDirectBufferAddress(env, seqBlob);
+    const int64_t* so = (const int64_t*)(*env)->GetDirectBufferAddress(env, seqOff);
+    const uint8_t* r = (const uint8_t*)(*env)->GetDirectBufferAddress(env, refBlob);
+    const int64_t* ro = (const int64_t*)(*env)->GetDirectBufferAddress(env, refOff);
+    if (!s || !so || !r || !ro || n < 0) return CUDASW_EINVAL;
+    cudasw_result* res = (cudasw_result*)malloc(sizeof(cudasw_result) * (size_t)(n > 0 ? n : 1));
+    int64_t cap = (n > 0 ? so[n] : 0) + 4 * (int64_t)n + 16, used = 0;
+    uint32_t* cig = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)cap);
+    int rc = cudasw_align_batch((cudasw_t*)(intptr_t)h, n, s, so, r, ro, res, cig, cap, &used);
+    if (rc == CUDASW_OK) cudaswjni_deliver(env, n, res, cig, startOut, cigarOut, statusOut);
+    free(cig);
+    free(res);
+    return rc;
+}

@@ -27,5 +27,7 @@ struct JNINativeInterface_ {
     jlong* (*GetLongArrayElements)(JNIEnv*, jlongArray, jboolean*);
     void (*ReleaseLongArrayElements)(JNIEnv*, jlongArray, jlong*, jint);
     void (*SetObjectArrayElement)(JNIEnv*, jobjectArray, jsize, jobject);
+    jobject (*NewDirectByteBuffer)(JNIEnv*, void*, jlong);
+    void* (*GetDirectBufferAddress)(JNIEnv*, jobject);
 };
 #endif

@@ -93,5 +93,5 @@ def test_jni_glue_type_checks_against_the_header():
     # every native method CudaAligner.java declares has its JNI symbol in the glue
     java = open(os.path.join(ROOT, "java", "au", "edu", "wehi", "idsv", "alignment", "CudaAligner.java")).read()
     glue = open(src).read()
-    for name in re.findall(r"private static native \w+(?:\[\])? (\w+)\(", java):
+    for name in re.findall(r"private static native [\w.]+(?:\[\])? (\w+)\(", java):
         assert f"Java_au_edu_wehi_idsv_alignment_CudaAligner_{name}(" in glue, name
