@@ -45,6 +45,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seconds", type=float, default=180.0)
     ap.add_argument("--checker", default="reference", choices=["reference", "model"])
+    ap.add_argument("--c4-sample", type=int, default=0, help="instead: parity on the first N pairs of the C4 stream itself (seed 4004)")
     args = ap.parse_args()
     import gridss_b200 as g
     from gridss_b200.aligner import pack
@@ -61,6 +62,30 @@ def main():
     kinds = ["random", "mutated", "two_letter", "homopolymer", "dinuc", "tandem", "subst_block", "with_n", "zero", "tiny", "q_gt_w", "indel_heavy"]
     tot = {"pairs": 0, "cells": 0.0, "mismatches": 0, "undefined_in_reference": 0, "by_source": {}}
     examples = []
+    if args.c4_sample > 0:
+        from gridss_b200.shard import Checksum, pair_digests
+
+        cs_gpu, cs_ref = Checksum(), Checksum()
+        step = 250000
+        for first in range(0, args.c4_sample, step):
+            n = min(step, args.c4_sample - first)
+            sb, so, rb, ro = S.generate(4, n, first=first)
+            res, cig = al.align_blobs(sb, so, rb, ro)
+            m = check(sb, so, rb, ro, threads=cores)
+            bad, undef, bad_first = compare(res, cig, m)
+            cs_gpu.add(pair_digests(res, cig, first))
+            cs_ref.add(pair_digests(m.res, m.cig, first))
+            tot["pairs"] += n
+            tot["cells"] += float((np.diff(so).astype(np.float64) * np.diff(ro)).sum())
+            tot["mismatches"] += bad
+            tot["undefined_in_reference"] += undef
+        tot["by_source"] = {"C4 stream, seed 4004, pairs [0, %d)" % args.c4_sample: {"pairs": tot["pairs"], "mismatches": tot["mismatches"]}}
+        tot["checksum_gpu"] = repr(cs_gpu)
+        tot["checksum_reference"] = repr(cs_ref)
+        tot["checker"] = ("libsswjni.so as shipped by the reference" if use_ref else "oracle/ssw_model.c") + f", {cores} host threads"
+        print(json.dumps(tot), flush=True)
+        al.close()
+        return 1 if tot["mismatches"] or cs_gpu != cs_ref else 0
     t_end = time.time() + args.seconds
     rnd = 0
     while time.time() < t_end:
