@@ -177,8 +177,9 @@ def main():
     d_so = torch.from_numpy(so).cuda()
     d_ro = torch.from_numpy(ro).cuda()
     torch.cuda.synchronize()
-    res = np.zeros(n, dtype=g.RESULT_DTYPE)
-    cig = np.zeros(24 * n, dtype=np.uint32)
+    # result buffers of both arms are pinned, as the JNI shim's direct ByteBuffers are
+    pin_res0, pin_cig0 = PinnedBuffer(n * g.RESULT_DTYPE.itemsize), PinnedBuffer(4 * 24 * n)
+    res, cig = pin_res0.array.view(g.RESULT_DTYPE), pin_cig0.array.view(np.uint32)
 
     def barrier():
         torch.cuda.synchronize()

@@ -87,7 +87,8 @@ struct cudasw {
     cudaStream_t pack_stream = nullptr;  // encode / bin of chunk i+1 while chunk i is in its forward pass
     struct ChunkEvents { cudaEvent_t pack0, enc1, pack1, fwd0, fwd1; };
     std::vector<ChunkEvents> chunk_ev;
-    unsigned long long* d_strip = nullptr;  // bump counters of the strip-mining boundary buffers: [0] forward, [1] reverse
+    unsigned long long* d_strip = nullptr;  // [0], [1]: bump counters of the strip-mining boundary buffers (forward, reverse); [2], [3]: cells, padded cells
+    unsigned long long* h_cells = nullptr;  // pinned copy of d_strip[2..3]
     DevBuf<uint8_t> strip_fwd, strip_rev;
     int launch_variants(StreamSet& ss, bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool, uint64_t* launches);
     std::vector<int16_t> var_by_q;  // host copy of variant_of() for the stats
@@ -233,11 +234,12 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
                 if ((e = cudaEventCreateWithFlags(&j, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
         }
     }
-    if ((e = cudaMalloc(&h->d_strip, 2 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_strip, 4 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
     if ((e = cudaMallocHost(&h->h_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMallocHost(&h->h_cells, 2 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMallocHost(&h->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
 
@@ -273,6 +275,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     h->vt.n_single = 0;
     for (int i = 0; i < g_nvar; i++) {
         h->vt.rows[i] = g_var[i].rows;
+        h->vt.lanes[i] = g_var[i].G;
         if (!g_var[i].multi) h->vt.n_single = i + 1;
     }
 
@@ -326,6 +329,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     if (h->pack_stream) { cudaStreamSynchronize(h->pack_stream); cudaStreamDestroy(h->pack_stream); }
     for (auto& c : h->chunk_ev) { cudaEventDestroy(c.pack0); cudaEventDestroy(c.enc1); cudaEventDestroy(c.pack1); cudaEventDestroy(c.fwd0); cudaEventDestroy(c.fwd1); }
     if (h->d_strip) cudaFree(h->d_strip);
+    if (h->h_cells) cudaFreeHost(h->h_cells);
     h->strip_fwd.release(); h->strip_rev.release();
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -418,7 +422,7 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
     fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
                                                            keys.p + first, vals.p + first, d_hist, res.p + first, any_n,
-                                                           wflags.p + first, anchor.p + first);
+                                                           wflags.p + first, anchor.p + first, d_strip + 2);
     launches++;
     CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p + first, keys_alt.p + first, vals.p + first,
                                        vals_alt.p + first, (int)n, 0, 32, st));
@@ -781,6 +785,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
 
     CK(cudaEventRecord(ev[0], st));
     CK(cudaMemsetAsync(d_counters, 0, 8 * sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(d_strip + 2, 0, 2 * sizeof(unsigned long long), st));
     CK(cudaEventRecord(ev[1], st));
     CK(cudaStreamWaitEvent(pack_stream, ev[1], 0));  // the counters (any-N flag) are reset before the first encode
     // ---- H2D: everything is queued on the copy stream now, one event per chunk
@@ -852,6 +857,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(cudaMemcpyAsync(out, res.p, (size_t)n * sizeof(cudasw_result), cudaMemcpyDeviceToHost, st));
     unsigned long long ncopy = std::min<unsigned long long>(used, (unsigned long long)cigar_cap);
     if (ncopy) CK(cudaMemcpyAsync(cigar_blob, cig.p, (size_t)ncopy * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_cells, d_strip + 2, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(ev[6], st));
     CK(cudaStreamSynchronize(st));
     stats.d2h_bytes = (uint64_t)n * sizeof(cudasw_result) + ncopy * 4;
@@ -872,28 +878,8 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         cudaEventElapsedTime(&ms, chunk_ev[i].fwd0, chunk_ev[i].fwd1); stats.ms_forward += ms;
     }
     stats.ms_h2d = std::max(0.f, stats.ms_total - pack_first - stats.ms_forward - last_post_ms - stats.ms_d2h);
-    if (h_seq_off && h_ref_off) {
-        const bool have_multi = g_var[g_nvar - 1].multi;
-        const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
-                                      scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
-        if (var_by_q.empty()) {
-            var_by_q.resize(32768);
-            for (int q = 1; q < 32768; q++) var_by_q[q] = (int16_t)variant_of(vt, q);
-        }
-        uint64_t cells = 0, padded = 0;
-        for (int64_t i = 0; i < n; i++) {
-            int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
-            if (q <= 0 || w <= 0) continue;
-            cells += (uint64_t)q * (uint64_t)w;
-            if (q <= max_rows) {
-                int v = var_by_q[(size_t)q];
-                uint64_t strips = ((uint64_t)q + g_var[v].rows - 1) / g_var[v].rows;
-                padded += strips * (uint64_t)g_var[v].rows * (uint64_t)(w + 2 * g_var[v].G - 1);
-            }
-        }
-        stats.cells = cells;
-        stats.forward_cells_padded = padded;
-    }
+    stats.cells = h_cells[0];                 // counted by fwd_keys_kernel while binning (no per-pair host loop)
+    stats.forward_cells_padded = h_cells[1];
     if (used > (unsigned long long)cigar_cap) {
         set_error("cigar buffer too small");
         return CUDASW_ENOMEM;

@@ -27,21 +27,46 @@ struct cudasw_multi {
 namespace {
 thread_local std::string g_multi_create_error;
 
-// contiguous slices with balanced cost; cost_i = q_i * w_i + a constant for the per-pair passes
+// contiguous slices with balanced cost; cost_i = q_i * w_i + a constant for the per-pair passes.
+// Two levels so that the O(n) part runs on `parts` threads: per-block sums in parallel, a prefix over the (few)
+// blocks, then each cut is refined inside its block.
 std::vector<int64_t> balance(int64_t n, int parts, const int64_t* seq_off, const int64_t* ref_off) {
     std::vector<int64_t> cut((size_t)parts + 1, n);
     cut[0] = 0;
     if (parts <= 1 || n <= 0) return cut;
-    std::vector<double> pre((size_t)n + 1, 0.0);
-    for (int64_t i = 0; i < n; i++) {
+    auto cost = [&](int64_t i) {
         const double q = (double)std::max<int64_t>(seq_off[i + 1] - seq_off[i], 0);
         const double w = (double)std::max<int64_t>(ref_off[i + 1] - ref_off[i], 0);
-        pre[(size_t)i + 1] = pre[(size_t)i] + q * w + 20000.0;
+        return q * w + 20000.0;
+    };
+    const int64_t B = 4096;
+    const int64_t nb = (n + B - 1) / B;
+    std::vector<double> blk((size_t)nb, 0.0);
+    {
+        std::vector<std::thread> th;
+        const int nt = (int)std::min<int64_t>(parts, nb);
+        for (int t = 0; t < nt; t++)
+            th.emplace_back([&, t] {
+                for (int64_t b = t; b < nb; b += nt) {
+                    double s = 0.0;
+                    const int64_t e = std::min(n, (b + 1) * B);
+                    for (int64_t i = b * B; i < e; i++) s += cost(i);
+                    blk[(size_t)b] = s;
+                }
+            });
+        for (auto& x : th) x.join();
     }
+    std::vector<double> pre((size_t)nb + 1, 0.0);
+    for (int64_t b = 0; b < nb; b++) pre[(size_t)b + 1] = pre[(size_t)b] + blk[(size_t)b];
     for (int d = 1; d < parts; d++) {
-        const double want = pre[(size_t)n] * d / parts;
-        cut[(size_t)d] = std::lower_bound(pre.begin(), pre.end(), want) - pre.begin();
-        cut[(size_t)d] = std::max(cut[(size_t)d], cut[(size_t)d - 1]);
+        const double want = pre[(size_t)nb] * d / parts;
+        int64_t b = (std::upper_bound(pre.begin(), pre.end(), want) - pre.begin()) - 1;
+        b = std::min<int64_t>(std::max<int64_t>(b, 0), nb - 1);
+        double acc = pre[(size_t)b];
+        int64_t i = b * B;
+        const int64_t e = std::min(n, (b + 1) * B);
+        while (i < e && acc < want) acc += cost(i++);
+        cut[(size_t)d] = std::max(i, cut[(size_t)d - 1]);
     }
     return cut;
 }

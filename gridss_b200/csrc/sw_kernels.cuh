@@ -236,6 +236,7 @@ struct VariantTable {
     int n;          // all variants
     int n_single;   // the first n_single are single-strip, ascending by rows
     int rows[100];  // rows covered by variant v (rows per strip for the strip-mined ones)
+    int lanes[100]; // G of variant v
 };
 
 __host__ __device__ __forceinline__ int variant_of(const VariantTable& vt, int q) {
@@ -336,11 +337,30 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
                                 int max_cols, uint32_t* __restrict__ keys, int* __restrict__ vals,
                                 int* __restrict__ hist, cudasw_result* __restrict__ res,
                                 const int* __restrict__ any_n, const uint8_t* __restrict__ wflags,
-                                const uint16_t* __restrict__ anchor) {
+                                const uint16_t* __restrict__ anchor, unsigned long long* __restrict__ cell_counts) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
+    // cell_counts: [0] sum of q*w, [1] cells the forward kernels compute (padded rows, fill/drain columns)
+    unsigned long long my_cells = 0, my_padded = 0;
+    int64_t q = 0, w = 0;
+    if (p < n) {
+        q = seq_off[p + 1] - seq_off[p];
+        w = ref_off[p + 1] - ref_off[p];
+        if (q > 0 && w > 0) {
+            my_cells = (unsigned long long)q * (unsigned long long)w;
+            if (q <= max_rows) {
+                const int v0 = variant_of(vt, (int)q);
+                const unsigned long long strips = ((unsigned long long)q + vt.rows[v0] - 1) / vt.rows[v0];
+                my_padded = strips * (unsigned long long)vt.rows[v0] * (unsigned long long)(w + 2 * vt.lanes[v0] - 1);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+        my_padded += __shfl_xor_sync(0xffffffffu, my_padded, o);
+    }
+    if ((threadIdx.x & 31) == 0 && my_cells) { atomicAdd(cell_counts, my_cells); atomicAdd(cell_counts + 1, my_padded); }
     if (p >= n) return;
-    int64_t q = seq_off[p + 1] - seq_off[p];
-    int64_t w = ref_off[p + 1] - ref_off[p];
     cudasw_result r;
     r.score = 0; r.ref_begin = -1; r.ref_end = -1; r.read_begin = 0; r.read_end = 0;
     r.cigar_off = 0; r.cigar_len = 0; r.status = CUDASW_OK;
