@@ -20,9 +20,19 @@ from .aligner import (  # noqa: F401
     cigar_string,
     load_library,
 )
+from .callers import (  # noqa: F401
+    BreakendSummary,
+    BreakpointSummary,
+    breakpoint_homology_batch,
+    realign_batch,
+)
 
 __all__ = [
     "Aligner",
+    "BreakendSummary",
+    "BreakpointSummary",
+    "breakpoint_homology_batch",
+    "realign_batch",
     "AlignerFactory",
     "Alignment",
     "BatchingAligner",
