@@ -136,6 +136,8 @@ def main():
     ap.add_argument("--cpu-baseline-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-windows", action="store_true", help="skip the device-resident-reference e2e variant")
+    ap.add_argument("--no-homology", action="store_true", help="skip the caller-level line (cudasw_breakpoint_homology)")
+    ap.add_argument("--homology-breakpoints", type=int, default=500000)
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
 
@@ -269,6 +271,45 @@ def main():
                     "note": "cudasw_align_batch_windows: windows gathered on the GPU from the device-resident 2-bit reference "
                             "(loaded once, outside the timed region); results asserted identical to the shipped-bytes path"}
 
+    # ---- caller level: BreakpointHomology.calculate for a list of breakpoints through
+    # cudasw_breakpoint_homology, with GRIDSS's defaults (gridss.properties:88-89: 300 bp breakend, 10 bp margin). The
+    # "genome" is this shard's windows as one contig; 32 bytes per breakpoint (+ inserted bases) cross PCIe per step.
+    hom_line = None
+    if not args.no_homology:
+        glen = int(ro[-1])
+        if args.no_windows:
+            al.load_reference_blob(rb[:glen], np.array([0, glen], dtype=np.int64))
+        nb = args.homology_breakpoints
+        rng_h = np.random.default_rng(7007 + rank)
+        bp = np.zeros(nb, dtype=g.BREAKPOINT_DTYPE)
+        bp["pos1"] = rng_h.integers(1, glen + 1, size=nb)
+        near = rng_h.random(nb) < 0.5     # half of the events are small (window sizes shrink to the event size)
+        bp["pos2"] = np.where(near, np.minimum(glen, bp["pos1"] + rng_h.integers(0, 2000, size=nb)), rng_h.integers(1, glen + 1, size=nb))
+        bp["dir1"] = rng_h.integers(0, 2, size=nb)
+        bp["dir2"] = rng_h.integers(0, 2, size=nb)
+        ins_len = np.where(rng_h.random(nb) < 0.3, rng_h.integers(1, 30, size=nb), 0)
+        ins_off = np.zeros(nb + 1, dtype=np.int64)
+        ins_off[1:] = np.cumsum(ins_len)
+        ins_blob = np.frombuffer(b"ACGT", dtype=np.uint8)[rng_h.integers(0, 4, size=max(1, int(ins_off[-1])))].copy()
+        for _ in range(2):
+            hl, hr = al.breakpoint_homology(bp, ins_blob, ins_off, 300, 10)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            hl, hr = al.breakpoint_homology(bp, ins_blob, ins_off, 300, 10)
+            st_b = al.stats()
+        barrier()
+        hom_wall_ms = (time.perf_counter() - t0) * 1e3
+        hom_line = {"metric": "breakpoints annotated/s per GPU", "value": float(nb) * args.steps / (hom_wall_ms / 1e3),
+                    "alignments_per_s": float(st_b["pairs"]) * args.steps / (hom_wall_ms / 1e3), "breakpoints_per_step": nb,
+                    "pairs_per_step": int(st_b["pairs"]), "ms_per_step_wall": hom_wall_ms / args.steps, "ms_per_step_device": st_b["ms_total"],
+                    "h2d_bytes_per_step": int(st_b["h2d_bytes"]), "d2h_bytes_per_step": int(st_b["d2h_bytes"]),
+                    "gcups": float(st_b["cells"]) * args.steps / (hom_wall_ms / 1e3) / 1e9,
+                    "phases_ms": {k: round(float(st_b[k]), 3) for k in ("ms_h2d", "ms_pack", "ms_forward", "ms_reverse", "ms_traceback", "ms_d2h")},
+                    "maxBreakendLength": 300, "margin": 10, "with_homology": int(((hl > 0) | (hr > 0)).sum()),
+                    "note": "cudasw_breakpoint_homology: segment arithmetic on the host, queries and windows gathered from the "
+                            "device-resident 2-bit reference, score passes only (clip lengths are all the caller reads)"}
+
     # ---- max over ranks
     t = torch.tensor([dev_ms, wall_ms, e2e_wall_ms, fwd_ms, e2e_dev_ms], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -333,6 +374,8 @@ def main():
                                               "bytes_per_launch_pair": enc_bytes, "ms": phase["ms_encode"]}
         if win_line is not None:
             line["e2e_windows"] = win_line
+        if hom_line is not None:
+            line["callers"] = {"breakpoint_homology": hom_line}
         if not args.no_cpu_baseline and world >= 1:
             from oracle import oracle as O
             O.build()
@@ -352,6 +395,28 @@ def main():
                                     "sample": f"first {k} pairs of rank 0's C2 shard, {cores} host threads, "
                                               + ("libsswjni.so as shipped by the reference (-O0 SSE2 build)" if kind == "reference" else "oracle/ssw_model.c -O3"),
                                     "gcups": k * Q_LEN * W_LEN / dt / 1e9, "gpu_results_identical_on_sample": same}
+            if hom_line is not None:
+                # the same breakpoints the way the reference does them: host strings, two libsswjni calls each
+                from oracle import callers_restatement as R
+                kb = min(nb, 4000)
+                contig = [rb[:glen]]
+                prs, owners = [], []
+                for i in range(kb):
+                    b = bp[i]
+                    ins_b = ins_blob[ins_off[i]:ins_off[i + 1]].tobytes()
+                    nl, nr, pa, pb = R.homology_pairs(contig, (0, "fb"[b["dir1"]], int(b["pos1"]), 0, "fb"[b["dir2"]], int(b["pos2"])), ins_b, 300, 10)
+                    owners.append((nl, nr, len(prs) if pa else -1, len(prs) + (1 if pa else 0) if pb else -1))
+                    prs += [p for p in (pa, pb) if p]
+                t0 = time.perf_counter()
+                cpu_h = (O.ref_align if kind == "reference" else O.model_align)([p[0] for p in prs], [p[1] for p in prs], threads=cores)
+                dt_h = time.perf_counter() - t0
+                want = [R.homology_from_cigars(nl, nr, cpu_h.cigar(a) if a >= 0 else None, cpu_h.cigar(c) if c >= 0 else None)
+                        for nl, nr, a, c in owners]
+                same_h = want == list(zip(hl[:kb].tolist(), hr[:kb].tolist()))
+                hom_line["cpu_baseline"] = {"value": kb / dt_h, "unit": "breakpoints/s", "cores": cores, "kind": kind,
+                                            "sample": f"first {kb} breakpoints ({len(prs)} aligner calls), {cores} host threads, aligner time only "
+                                                      "(window strings prepared outside the timed region)",
+                                            "gpu_results_identical_on_sample": bool(same_h)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

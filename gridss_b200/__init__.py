@@ -10,6 +10,7 @@ from .aligner import (  # noqa: F401
     Aligner,
     AlignerFactory,
     Alignment,
+    BREAKPOINT_DTYPE,
     BatchingAligner,
     CudaAligner,
     CudaSwError,
@@ -23,7 +24,10 @@ from .aligner import (  # noqa: F401
 from .callers import (  # noqa: F401
     BreakendSummary,
     BreakpointSummary,
+    SmithWatermanStreamingAligner,
+    breakpoint_array,
     breakpoint_homology_batch,
+    breakpoint_homology_device,
     realign_batch,
 )
 
@@ -31,7 +35,11 @@ __all__ = [
     "Aligner",
     "BreakendSummary",
     "BreakpointSummary",
+    "BREAKPOINT_DTYPE",
+    "SmithWatermanStreamingAligner",
+    "breakpoint_array",
     "breakpoint_homology_batch",
+    "breakpoint_homology_device",
     "realign_batch",
     "AlignerFactory",
     "Alignment",

@@ -44,6 +44,8 @@ RESULT_DTYPE = np.dtype(
 # reverse-complemented (flags & WINDOW_REVCOMP)
 WINDOW_DTYPE = np.dtype([("contig", "<i4"), ("flags", "<i4"), ("start", "<i8"), ("end", "<i8")])
 WINDOW_REVCOMP = 1
+# cudasw_breakpoint (include/cudasw.h): exact 1-based positions, dir 0 = forward / 1 = backward
+BREAKPOINT_DTYPE = np.dtype([("contig1", "<i4"), ("dir1", "<i4"), ("pos1", "<i8"), ("contig2", "<i4"), ("dir2", "<i4"), ("pos2", "<i8")])
 _OPS = "MIDNSHP=X"
 
 
@@ -91,6 +93,7 @@ ABI = [
     ("cudasw_reference_load", ctypes.c_int, [_vp, _i32, _vp, _vp]),
     ("cudasw_reference_fetch", ctypes.c_int, [_vp, _vp, _i32, _vp, _i64]),
     ("cudasw_align_batch_windows", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_breakpoint_homology", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _i32, _i32, _vp, _vp]),
     ("cudasw_multi_create", ctypes.c_int, [ctypes.POINTER(_Scoring), _vp, ctypes.c_int, ctypes.POINTER(_vp)]),
     ("cudasw_multi_destroy", None, [_vp]),
     ("cudasw_multi_device_count", ctypes.c_int, [_vp]),
@@ -352,6 +355,27 @@ class CudaAligner(Aligner):
             if rc != 0:
                 raise CudaSwError(f"cudasw_align_batch_windows failed ({rc}): {self._err()}")
             return res, cig[: used.value]
+
+    def breakpoint_homology(self, bp: np.ndarray, ins_blob=None, ins_off=None, max_breakend_length: int = 300, margin: int = 10):
+        """BreakpointHomology.calculate (BreakpointHomology.java:38-103) for BREAKPOINT_DTYPE[n] against the loaded
+        reference -> (localHomologyLength int32[n], remoteHomologyLength int32[n]). The defaults are
+        variantcalling.maxBreakendHomologyLength / breakendHomologyAlignmentMargin of gridss.properties:88-89."""
+        assert bp.dtype == BREAKPOINT_DTYPE
+        n = len(bp)
+        local = np.zeros(n, dtype=np.int32)
+        remote = np.zeros(n, dtype=np.int32)
+        if ins_off is not None:
+            ins_off = np.ascontiguousarray(ins_off, dtype=np.int64)
+            assert len(ins_off) == n + 1
+            if ins_blob is None or len(ins_blob) == 0:
+                ins_blob = np.zeros(1, dtype=np.uint8)
+        bp = np.ascontiguousarray(bp)
+        rc = self._lib.cudasw_breakpoint_homology(
+            self._h, n, bp.ctypes.data, None if ins_off is None else ins_blob.ctypes.data,
+            None if ins_off is None else ins_off.ctypes.data, max_breakend_length, margin, local.ctypes.data, remote.ctypes.data)
+        if rc != 0:
+            raise (ValueError if rc == CUDASW_EINVAL else CudaSwError)(f"cudasw_breakpoint_homology failed ({rc}): {self._err()}")
+        return local, remote
 
     def variant_for(self, query_len: int) -> tuple[int, int, int]:
         """(lanes per pair, rows per virtual lane, strips) of the score kernel a query length maps to."""

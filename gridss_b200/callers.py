@@ -17,7 +17,7 @@ from typing import Sequence
 
 import numpy as np
 
-from .aligner import WINDOW_DTYPE, WINDOW_REVCOMP, CudaAligner, cigar_string, pack
+from .aligner import BREAKPOINT_DTYPE, WINDOW_DTYPE, WINDOW_REVCOMP, CudaAligner, cigar_string, pack
 
 FWD, BWD = "f", "b"
 _COMP = bytes.maketrans(b"ACGTNacgtn", b"TGCANtgcan")
@@ -183,6 +183,27 @@ def breakpoint_homology_batch(aligner: CudaAligner, contigs: Sequence[bytes], br
     return [tuple(x) for x in out]
 
 
+def breakpoint_array(breakpoints: Sequence[BreakpointSummary]) -> np.ndarray:
+    a = np.zeros(len(breakpoints), dtype=BREAKPOINT_DTYPE)
+    for k, b in enumerate(breakpoints):
+        a[k] = (b.referenceIndex, int(b.direction == BWD), b.position, b.referenceIndex2, int(b.direction2 == BWD), b.position2)
+    return a
+
+
+def breakpoint_homology_device(aligner: CudaAligner, breakpoints, inserted: Sequence[str | bytes | None] | None,
+                               maxBreakendLength: int, margin: int):
+    """Same answers as breakpoint_homology_batch through cudasw_breakpoint_homology: the library derives every query
+    and window segment itself, gathers both on the device and skips the traceback (only clip lengths are read).
+    `breakpoints` is a list of BreakpointSummary or a BREAKPOINT_DTYPE array."""
+    bp = breakpoints if isinstance(breakpoints, np.ndarray) else breakpoint_array(breakpoints)
+    blob = off = None
+    if inserted is not None:
+        ins = [b"" if i is None else (i.encode("ascii") if isinstance(i, str) else bytes(i)) for i in inserted]
+        blob, off = pack(ins)
+    local, remote = aligner.breakpoint_homology(bp, blob, off, maxBreakendLength, margin)
+    return list(zip(local.tolist(), remote.tolist()))
+
+
 _CIG = re.compile(r"(\d+)([MIDNSHP=X])")
 
 
@@ -227,3 +248,50 @@ def realign_batch(aligner: CudaAligner, contig_len: Sequence[int], reads, window
         new_cigar = cigar_string(cig[r["cigar_off"]: r["cigar_off"] + r["cigar_len"]])
         out.append((starts[k] + int(r["ref_begin"]), new_cigar))   # :647
     return out
+
+
+class SmithWatermanStreamingAligner:
+    """SmithWatermanStreamingAligner.java:16-69 (and the loop of SmithWatermanFastqAligner.java:24-45): every read is
+    aligned against one WHOLE contig. The reference aligns inside asyncAlign; here reads queue up and flush() (or
+    reaching `batch` queued reads) issues one GPU batch whose windows all name the same contig-long segment of the
+    device-resident reference. Records come back in submission order as (readName, referenceIndex,
+    alignmentStart (1-based), cigar)."""
+
+    def __init__(self, aligner: CudaAligner, contig_len: Sequence[int], referenceIndex: int, batch: int = 4096):
+        self.aligner, self.referenceIndex, self.batch = aligner, referenceIndex, batch
+        self._win = np.zeros(1, dtype=WINDOW_DTYPE)
+        self._win[0] = (referenceIndex, 0, 0, contig_len[referenceIndex])
+        self._pending: list[tuple[str, bytes]] = []
+        self._done: list[tuple[str, int, int, str]] = []
+
+    def asyncAlign(self, readName: str, bases: bytes) -> None:
+        if not bases:
+            raise ValueError("seq and ref must be non-zero size")   # SswJniAligner.java:45-50
+        self._pending.append((readName, bytes(bases)))
+        if len(self._pending) >= self.batch:
+            self.flush()
+
+    def flush(self) -> None:
+        if not self._pending:
+            return
+        n = len(self._pending)
+        sb, so = pack([b for _, b in self._pending])
+        res, cig = self.aligner.align_blobs_windows(sb, so, np.repeat(self._win, n), np.arange(n + 1, dtype=np.int64))
+        for (name, _), r in zip(self._pending, res):
+            words = cig[r["cigar_off"]: r["cigar_off"] + r["cigar_len"]]
+            self._done.append((name, self.referenceIndex, int(r["ref_begin"]) + 1, cigar_string(words)))   # :36-38
+        self._pending.clear()
+
+    def processedAlignmentRecords(self) -> int:
+        return len(self._done)
+
+    def outstandingAlignmentRecord(self) -> int:
+        return len(self._pending)
+
+    def getAlignment(self):
+        if not self._done:
+            self.flush()
+        return self._done.pop(0)
+
+    def close(self) -> None:
+        self.flush()

@@ -14,6 +14,7 @@
 #include <cstring>
 #include <chrono>
 #include <condition_variable>
+#include <atomic>
 #include <mutex>
 #include <thread>
 #include <unordered_set>
@@ -66,6 +67,34 @@ struct DevBuf {
 
 }  // namespace
 
+// Queries named as segments instead of shipped as bytes: pair i = segs[seg_off[i] .. seg_off[i+1]) concatenated (or
+// slots [i*stride, (i+1)*stride) when stride > 0; empty slots have start == end); a segment with contig < 0 is
+// bytes [start, end) of `lit`. w_stride > 0: the WINDOW descriptors handed to run() are fixed-stride too.
+struct QuerySegs {
+    const WindowSeg* segs;
+    const int64_t* seg_off;
+    int stride;
+    const uint8_t* lit;
+    int64_t lit_bytes;
+    int w_stride;
+};
+
+// pinned host staging that grows on demand (cudasw_breakpoint_homology)
+template <typename T>
+struct PinBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMallocHost(reinterpret_cast<void**>(&p), n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
 struct cudasw {
     int device = 0;
     cudasw_scoring scoring{};
@@ -115,6 +144,15 @@ struct cudasw {
     DevBuf<uint32_t> ref2bit, refN;
     DevBuf<int64_t> d_contig_off, d_seg_off;
     DevBuf<WindowSeg> d_segs;
+    // queries assembled on the device (cudasw_breakpoint_homology): their segments and the literal bytes between them
+    DevBuf<WindowSeg> d_qsegs;
+    DevBuf<int64_t> d_qseg_off;
+    DevBuf<uint8_t> d_lit;
+    PinBuf<WindowSeg> hom_qs, hom_ws;
+    PinBuf<int64_t> hom_seq_off, hom_ref_off;
+    PinBuf<uint8_t> hom_lit;
+    PinBuf<cudasw_result> hom_res;
+    std::mutex hom_mu;  // one cudasw_breakpoint_homology call at a time owns the staging above
     std::vector<int64_t> contig_off;  // n_contigs + 1, linear base coordinates
     int* d_hist = nullptr;  // 256 ints: pairs per (flavour, variant) slot
     uint32_t* d_pool = nullptr;  // {poolA, poolB}
@@ -144,16 +182,18 @@ struct cudasw {
     void set_error(const std::string& s) { error = s; }
     int pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so, const uint8_t* d_ref,
                    const int64_t* d_ro, int64_t q_lo, int64_t q_hi, int64_t w_lo, int64_t w_hi, bool gather,
-                   uint64_t* launches_out);
+                   uint64_t* launches_out, bool qgather = false, int q_stride = 0, int w_stride = 0);
     int forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* d_so, const int64_t* d_ro, uint64_t* launches_out);
-    int post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out);
+    int post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out,
+                   bool ends_only = false);
     int size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off);
     float last_post_ms = 0.f;
     int run(int64_t n, const uint8_t* d_seq, const int64_t* d_seq_off, const uint8_t* d_ref,
             const int64_t* d_ref_off, int64_t total_q, int64_t total_w, cudasw_result* out,
             uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used, bool inputs_on_host,
             const uint8_t* h_seq, const int64_t* h_seq_off, const uint8_t* h_ref,
-            const int64_t* h_ref_off, const WindowSeg* h_segs = nullptr, const int64_t* h_seg_off = nullptr);
+            const int64_t* h_ref_off, const WindowSeg* h_segs = nullptr, const int64_t* h_seg_off = nullptr,
+            const QuerySegs* qsegs = nullptr, bool ends_only = false);
 };
 
 static uint32_t pack2(int v) { return ((uint32_t)v & 0xFFFFu) | (((uint32_t)v & 0xFFFFu) << 16); }
@@ -312,6 +352,8 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
     h->cub_tmp.release(); h->tb_pool.release(); h->tb_band.release(); h->tb_esc.release(); h->wflags.release(); h->anchor.release();
     h->ref2bit.release(); h->refN.release(); h->d_contig_off.release(); h->d_seg_off.release(); h->d_segs.release();
+    h->d_qsegs.release(); h->d_qseg_off.release(); h->d_lit.release();
+    h->hom_qs.release(); h->hom_ws.release(); h->hom_seq_off.release(); h->hom_ref_off.release(); h->hom_lit.release(); h->hom_res.release();
     if (h->d_hist) cudaFree(h->d_hist);
     if (h->d_pool) cudaFree(h->d_pool);
     if (h->d_counters) cudaFree(h->d_counters);
@@ -382,7 +424,7 @@ int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairI
 // never overlap each other (both are host-synchronised), so they share d_hist, h_hist and the sort workspace.
 int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so,
                        const uint8_t* d_ref, const int64_t* d_ro, int64_t q_lo, int64_t q_hi,
-                       int64_t w_lo, int64_t w_hi, bool gather, uint64_t* launches_out) {
+                       int64_t w_lo, int64_t w_hi, bool gather, uint64_t* launches_out, bool qgather, int q_stride, int w_stride) {
     cudaStream_t st = pack_stream;
     uint64_t launches = 0;
     const int64_t n = cnt;
@@ -392,17 +434,26 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
         const int64_t tq = q_hi - q_lo, tw = w_hi - w_lo;
         int64_t thr = (tq + 31) / 32;
         int blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
-        if (tq > 0) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u, nullptr); launches++; }
+        if (tq > 0 && !qgather) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u, nullptr); launches++; }
         thr = (tw + 31) / 32;
         blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
         if (tw > 0 && !gather) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u, any_n); launches++; }
     }
     PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
+    if (qgather) {
+        // queries assembled from reference segments and literal bytes, in the query encoding
+        window_gather_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, d_qsegs.p + (q_stride ? first * q_stride : 0),
+                                                                         q_stride ? nullptr : d_qseg_off.p + first, io.seq_off,
+                                                                         d_contig_off.p, ref2bit.p, refN.p, enc_seq.p,
+                                                                         nullptr, nullptr, 0, d_lit.p, 0u, q_stride);
+        launches++;
+    }
     if (gather) {
         // windows come out of the device-resident 2-bit reference already encoded, with their N flags
-        window_gather_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, d_segs.p, d_seg_off.p + first, io.ref_off,
+        window_gather_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, d_segs.p + (w_stride ? first * w_stride : 0),
+                                                                         w_stride ? nullptr : d_seg_off.p + first, io.ref_off,
                                                                          d_contig_off.p, ref2bit.p, refN.p, enc_ref.p,
-                                                                         wflags.p + first, any_n, 0);
+                                                                         wflags.p + first, any_n, 0, nullptr, 0x80u, w_stride);
     } else {
         CK(cudaEventRecord(chunk_ev[ci].enc1, st));
         window_flags_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, st>>>((int)n, enc_ref.p, io.ref_off, any_n, wflags.p + first);
@@ -453,7 +504,8 @@ int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* 
 }
 
 // Reverse pass + traceback of one chunk whose forward pass has been queued (waits for it by event).
-int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out) {
+int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out,
+                       bool ends_only) {
     cudaStream_t st = post_set.main;
     CK(cudaStreamWaitEvent(st, chunk_ev[ci].fwd1, 0));
     cudaStream_t* aux = post_set.aux;
@@ -486,10 +538,17 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[4], st));
 
+    if (ends_only) {  // the caller reads clip lengths only: no traceback, no CIGAR
+        ends_only_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, rev_c, res_c);
+        launches++;
+        CK(cudaEventRecord(ev[5], st));
+        CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
     // ---- traceback (+ retry rounds when the scratch pool runs out); the CIGAR counter [1] runs on across rounds.
     // Pairs are sorted by estimated banded cells: the widest go to the warp-cooperative kernel (one warp each, on
     // an auxiliary stream), the rest to the one-thread-per-pair kernel in descending cost order.
-    {
+    if (!ends_only) {
         // default: the one-thread kernel keeps bands up to kTbThreadBand in registers, wider pairs take a warp each;
         // CUDASW_TB_WIDE_CELLS additionally sends every pair above that many banded cells to the warp kernel (0 = all)
         long long wide_cells = -1;
@@ -669,14 +728,18 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
                 int64_t total_w, cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap,
                 int64_t* cigar_used, bool inputs_on_host, const uint8_t* h_seq,
                 const int64_t* h_seq_off, const uint8_t* h_ref, const int64_t* h_ref_off,
-                const WindowSeg* h_segs, const int64_t* h_seg_off) {
+                const WindowSeg* h_segs, const int64_t* h_seg_off, const QuerySegs* qsegs, bool ends_only) {
     std::lock_guard<std::mutex> lock(mu);
     const bool gather = h_segs != nullptr;
+    const bool qgather = qsegs != nullptr;
+    const int q_stride = qsegs ? qsegs->stride : 0, w_stride = qsegs ? qsegs->w_stride : 0;
     error.clear();
     stats = cudasw_stats{};
     if (cigar_used) *cigar_used = 0;
     if (n < 0 || n > 0x7fffff00ll) { set_error("n_pairs out of range"); return CUDASW_EINVAL; }
     if (n == 0) return CUDASW_OK;
+    const int64_t n_wsegs = !gather ? 0 : (w_stride ? n * w_stride : h_seg_off[n]);
+    const int64_t n_qsegs = !qgather ? 0 : (q_stride ? n * q_stride : qsegs->seg_off[n]);
     if (!out || (!cigar_blob && cigar_cap > 0) || cigar_cap < 0) { set_error("null output"); return CUDASW_EINVAL; }
     if (total_q < 0 || total_w < 0) { set_error("offsets must be non-decreasing from 0"); return CUDASW_EINVAL; }
     CK(cudaSetDevice(device));
@@ -794,7 +857,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     const int64_t* d_so = d_seq_off_in;
     const int64_t* d_ro = d_ref_off_in;
     if (inputs_on_host) {
-        CK(raw_seq.ensure((size_t)total_q + 16));
+        if (!qgather) CK(raw_seq.ensure((size_t)total_q + 16));
         if (!gather) CK(raw_ref.ensure((size_t)total_w + 16));
         CK(seq_off.ensure(n + 1));
         CK(ref_off.ensure(n + 1));
@@ -803,21 +866,35 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         CK(cudaMemcpyAsync(seq_off.p, h_seq_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
         CK(cudaMemcpyAsync(ref_off.p, h_ref_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
         if (gather) {
-            const int64_t nsegs = h_seg_off[n];
+            const int64_t nsegs = w_stride ? n * w_stride : h_seg_off[n];
             CK(d_segs.ensure((size_t)std::max<int64_t>(nsegs, 1)));
-            CK(d_seg_off.ensure(n + 1));
-            CK(cudaMemcpyAsync(d_seg_off.p, h_seg_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
+            if (!w_stride) {
+                CK(d_seg_off.ensure(n + 1));
+                CK(cudaMemcpyAsync(d_seg_off.p, h_seg_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
+            }
             if (nsegs > 0) CK(cudaMemcpyAsync(d_segs.p, h_segs, (size_t)nsegs * sizeof(WindowSeg), cudaMemcpyHostToDevice, copy_stream));
+        }
+        if (qgather) {
+            const int64_t nsegs = q_stride ? n * q_stride : qsegs->seg_off[n];
+            CK(d_qsegs.ensure((size_t)std::max<int64_t>(nsegs, 1)));
+            CK(d_lit.ensure((size_t)qsegs->lit_bytes + 16));
+            if (!q_stride) {
+                CK(d_qseg_off.ensure(n + 1));
+                CK(cudaMemcpyAsync(d_qseg_off.p, qsegs->seg_off, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, copy_stream));
+            }
+            if (nsegs > 0) CK(cudaMemcpyAsync(d_qsegs.p, qsegs->segs, (size_t)nsegs * sizeof(WindowSeg), cudaMemcpyHostToDevice, copy_stream));
+            if (qsegs->lit_bytes > 0) CK(cudaMemcpyAsync(d_lit.p, qsegs->lit, (size_t)qsegs->lit_bytes, cudaMemcpyHostToDevice, copy_stream));
         }
         for (size_t i = 0; i < chunks.size(); i++) {
             const Chunk& c = chunks[i];
-            if (c.q_hi > c.q_lo) CK(cudaMemcpyAsync(raw_seq.p + c.q_lo, h_seq + c.q_lo, (size_t)(c.q_hi - c.q_lo), cudaMemcpyHostToDevice, copy_stream));
+            if (c.q_hi > c.q_lo && !qgather) CK(cudaMemcpyAsync(raw_seq.p + c.q_lo, h_seq + c.q_lo, (size_t)(c.q_hi - c.q_lo), cudaMemcpyHostToDevice, copy_stream));
             if (c.w_hi > c.w_lo && !gather) CK(cudaMemcpyAsync(raw_ref.p + c.w_lo, h_ref + c.w_lo, (size_t)(c.w_hi - c.w_lo), cudaMemcpyHostToDevice, copy_stream));
             CK(cudaEventRecord(h2d_done[i], copy_stream));
         }
         d_seq = raw_seq.p; d_ref = raw_ref.p; d_so = seq_off.p; d_ro = ref_off.p;
-        stats.h2d_bytes = (uint64_t)total_q + (uint64_t)(n + 1) * 16 +
-                          (gather ? (uint64_t)(n + 1) * 8 + (uint64_t)h_seg_off[n] * sizeof(WindowSeg) : (uint64_t)total_w);
+        stats.h2d_bytes = (qgather ? (q_stride ? 0 : (uint64_t)(n + 1) * 8) + (uint64_t)n_qsegs * sizeof(WindowSeg) + (uint64_t)qsegs->lit_bytes
+                                   : (uint64_t)total_q) + (uint64_t)(n + 1) * 16 +
+                          (gather ? (w_stride ? 0 : (uint64_t)(n + 1) * 8) + (uint64_t)n_wsegs * sizeof(WindowSeg) : (uint64_t)total_w);
     }
 
     // ---- the chunk pipeline: pack(i) | forward(i) | post(i-1), see pack_chunk
@@ -830,11 +907,11 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     for (size_t i = 0; i < chunks.size(); i++) {
         const Chunk& c = chunks[i];
         if (inputs_on_host) CK(cudaStreamWaitEvent(pack_stream, h2d_done[i], 0));
-        int rc = pack_chunk(i, c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, gather, &launches);
+        int rc = pack_chunk(i, c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, gather, &launches, qgather, q_stride, w_stride);
         if (rc == CUDASW_OK) rc = size_strip_buffers(c.first, c.cnt, h_seq_off, h_ref_off);
         if (rc == CUDASW_OK) rc = forward_chunk(i, c.first, c.cnt, d_so, d_ro, &launches);
         if (rc == CUDASW_OK && serial) rc = cudaStreamSynchronize(st) == cudaSuccess ? CUDASW_OK : CUDASW_ECUDA;
-        if (rc == CUDASW_OK && post_per_chunk && i > 0) rc = post_chunk(i - 1, chunks[i - 1].first, chunks[i - 1].cnt, d_so, d_ro, cigar_cap, &launches);
+        if (rc == CUDASW_OK && post_per_chunk && i > 0) rc = post_chunk(i - 1, chunks[i - 1].first, chunks[i - 1].cnt, d_so, d_ro, cigar_cap, &launches, ends_only);
         if (rc != CUDASW_OK) { drain(); return rc; }
     }
     {
@@ -842,8 +919,8 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         // pass was measured slower on B200 (C2: 253 vs 237 ms per 1 M pairs): their latency-bound CTAs displace
         // forward CTAs that fill the register file. CUDASW_POST_PER_CHUNK=1 keeps that experiment available.
         const Chunk& c = chunks.back();
-        int rc = post_per_chunk ? post_chunk(chunks.size() - 1, c.first, c.cnt, d_so, d_ro, cigar_cap, &launches)
-                                : post_chunk(chunks.size() - 1, 0, n, d_so, d_ro, cigar_cap, &launches);
+        int rc = post_per_chunk ? post_chunk(chunks.size() - 1, c.first, c.cnt, d_so, d_ro, cigar_cap, &launches, ends_only)
+                                : post_chunk(chunks.size() - 1, 0, n, d_so, d_ro, cigar_cap, &launches, ends_only);
         if (rc != CUDASW_OK) { drain(); return rc; }
     }
     CK(cudaEventRecord(ev[5], st));
@@ -987,6 +1064,166 @@ extern "C" int cudasw_align_batch_windows(cudasw_t* h, int64_t n, const uint8_t*
     int64_t tq = n > 0 ? seq_off[n] : 0, tw = n > 0 ? ref_off[n] : 0;
     return h->run(n, nullptr, nullptr, nullptr, nullptr, tq, tw, out, cigar_blob, cigar_cap, cigar_used, true,
                   seq_blob, seq_off, nullptr, ref_off.data(), reinterpret_cast<const WindowSeg*>(win), win_off);
+}
+
+// ---- BreakpointHomology.calculate for a list of breakpoints (BreakpointHomology.java:38-103).
+// Everything the reference does with host strings becomes segment arithmetic here: the breakend query
+// (localBsSeq + inserted + remoteBsSeq) and both windows (localSeq + localRef, and the reverse complement of
+// remoteRef + remoteSeq) are lists of reference segments, so 32 bytes per breakpoint go to the device, both
+// sequences of both pairs are gathered from the 2-bit reference there, and only the score passes run: the homology
+// lengths are functions of the two clip lengths (read_begin, q - read_end - 1).
+namespace {
+struct Seg { int32_t contig; int64_t start, end; bool rc; bool some; };
+// BreakendSummary.getAnchorSequence (BreakendSummary.java:73-106) as a segment; dir 0 = forward, 1 = backward
+inline Seg anchor_seg(const std::vector<int64_t>& coff, int32_t contig, int32_t dir, int64_t pos, int64_t length) {
+    int64_t a_start, a_end;
+    if (dir == 0) { a_end = pos; a_start = a_end - length + 1; }
+    else { a_start = pos; a_end = a_start + length - 1; }
+    a_start = std::max<int64_t>(1, a_start);
+    a_end = std::min<int64_t>(coff[contig + 1] - coff[contig], a_end);
+    return Seg{contig, a_start - 1, a_end, dir != 0, a_start <= a_end};
+}
+inline int64_t seg_len(const Seg& s) { return s.some ? s.end - s.start : 0; }
+inline WindowSeg slot(const Seg& s, bool flip) {  // an empty anchor keeps its slot with start == end
+    return s.some ? WindowSeg{s.contig, (s.rc != flip) ? 1 : 0, s.start, s.end} : WindowSeg{0, 0, 0, 0};
+}
+inline uint8_t comp_base(uint8_t c) {
+    switch (c) {
+        case 'A': return 'T'; case 'C': return 'G'; case 'G': return 'C'; case 'T': return 'A';
+        case 'a': return 't'; case 'c': return 'g'; case 'g': return 'c'; case 't': return 'a';
+        default: return c;
+    }
+}
+}  // namespace
+
+extern "C" int cudasw_breakpoint_homology(cudasw_t* h, int64_t n, const cudasw_breakpoint* bp, const uint8_t* ins_blob,
+                                          const int64_t* ins_off, int32_t max_breakend_length, int32_t margin,
+                                          int32_t* local_hom, int32_t* remote_hom) {
+    if (!h) return CUDASW_EINVAL;
+    if (n < 0 || n > 0x3fffff00ll || (n > 0 && (!bp || !local_hom || !remote_hom)) || max_breakend_length < 0 || margin < 0) {
+        h->error = "bad argument";
+        return CUDASW_EINVAL;
+    }
+    if (n == 0) return CUDASW_OK;
+    if (ins_off && (ins_off[0] != 0 || (!ins_blob && ins_off[n] > 0))) { h->error = "bad inserted-sequence blob"; return CUDASW_EINVAL; }
+    if (h->contig_off.empty()) { h->error = "no reference loaded (cudasw_reference_load)"; return CUDASW_EINVAL; }
+    std::lock_guard<std::mutex> hom_lock(h->hom_mu);
+    const std::vector<int64_t>& coff = h->contig_off;
+    const int32_t ncontig = (int32_t)coff.size() - 1;
+    // Fixed layout, so breakpoints can be planned independently (and in parallel): breakpoint k owns pairs 2k (local
+    // window) and 2k+1 (remote window); a pair owns 3 query slots and 2 window slots; the literal blob holds, per
+    // breakpoint, the inserted sequence as the breakend reads it followed by its reverse complement. A call the
+    // reference skips (empty breakend or window) is a pair of length 0, which the engine rejects without work.
+    const int64_t np = 2 * n;
+    const int64_t lit_bytes = ins_off ? 2 * ins_off[n] : 0;
+    auto alloc_fail = [&](cudaError_t e) { h->error = std::string("pinned staging: ") + cudaGetErrorString(e); return CUDASW_ENOMEM; };
+    cudaError_t ce;
+    if ((ce = h->hom_qs.ensure((size_t)np * 3)) != cudaSuccess || (ce = h->hom_ws.ensure((size_t)np * 2)) != cudaSuccess ||
+        (ce = h->hom_seq_off.ensure((size_t)np + 1)) != cudaSuccess || (ce = h->hom_ref_off.ensure((size_t)np + 1)) != cudaSuccess ||
+        (ce = h->hom_lit.ensure((size_t)lit_bytes + 16)) != cudaSuccess || (ce = h->hom_res.ensure((size_t)np)) != cudaSuccess)
+        return alloc_fail(ce);
+    WindowSeg* qs = h->hom_qs.p;
+    WindowSeg* ws = h->hom_ws.p;
+    int64_t* seq_off = h->hom_seq_off.p;   // first lengths (slot p + 1), then their running sums
+    int64_t* ref_off = h->hom_ref_off.p;
+    uint8_t* lit = h->hom_lit.p;
+    std::vector<int32_t> n_bs((size_t)np);  // [2k] = |localBsSeq|, [2k+1] = |remoteBsSeq|
+    std::atomic<int64_t> bad{-1};
+    auto plan = [&](int64_t k0, int64_t k1) {
+        for (int64_t k = k0; k < k1; k++) {
+            const cudasw_breakpoint& b = bp[k];
+            const int64_t ins_len = ins_off ? ins_off[k + 1] - ins_off[k] : 0;
+            if (b.contig1 < 0 || b.contig1 >= ncontig || b.contig2 < 0 || b.contig2 >= ncontig || ((b.dir1 | b.dir2) & ~1) || ins_len < 0) {
+                bad.store(k);
+                return;
+            }
+            int64_t seq_len = max_breakend_length, ref_len = (int64_t)max_breakend_length + ins_len + margin;
+            if (b.contig1 == b.contig2) {  // BreakpointSummary.getEventSize (BreakpointSummary.java:226-236)
+                const int64_t d = b.pos2 > b.pos1 ? b.pos2 - b.pos1 : b.pos1 - b.pos2;
+                int64_t ev;
+                if (b.dir1 == b.dir2) ev = d;
+                else if ((b.pos1 < b.pos2 && b.dir1 == 0) || (b.pos2 < b.pos1 && b.dir1 == 1)) ev = d - 1;
+                else ev = d + 1;
+                seq_len = std::min(seq_len, ev);
+                ref_len = std::min(ref_len, ev);
+            }
+            const int64_t adv1 = b.dir1 == 0 ? b.pos1 + ref_len : b.pos1 - ref_len;  // BreakendSummary.advance
+            const int64_t adv2 = b.dir2 == 0 ? b.pos2 + ref_len : b.pos2 - ref_len;
+            const Seg local_seq = anchor_seg(coff, b.contig1, b.dir1, b.pos1, ref_len);
+            const Seg local_bs = anchor_seg(coff, b.contig1, b.dir1, b.pos1, seq_len);
+            const Seg local_ref = anchor_seg(coff, b.contig1, b.dir1, adv1, ref_len);
+            // the remote pieces are the reverse complements of these anchors (:64-66)
+            const Seg remote_seq = anchor_seg(coff, b.contig2, b.dir2, b.pos2, ref_len);
+            const Seg remote_bs = anchor_seg(coff, b.contig2, b.dir2, b.pos2, seq_len);
+            const Seg remote_ref = anchor_seg(coff, b.contig2, b.dir2, adv2, ref_len);
+            n_bs[(size_t)(2 * k)] = (int32_t)seg_len(local_bs);
+            n_bs[(size_t)(2 * k + 1)] = (int32_t)seg_len(remote_bs);
+            const int64_t q = seg_len(local_bs) + ins_len + seg_len(remote_bs);
+            // inserted sequence as the breakend reads it (:45-47), then its reverse complement for the second pair
+            const int64_t lit0 = ins_off ? 2 * ins_off[k] : 0;
+            if (ins_len > 0) {
+                const uint8_t* src = ins_blob + ins_off[k];
+                uint8_t* fwd_ins = lit + lit0;
+                uint8_t* rc_ins = fwd_ins + ins_len;
+                if (b.dir1 == 1) for (int64_t x = 0; x < ins_len; x++) fwd_ins[x] = comp_base(src[ins_len - 1 - x]);
+                else for (int64_t x = 0; x < ins_len; x++) fwd_ins[x] = src[x];
+                for (int64_t x = 0; x < ins_len; x++) rc_ins[x] = comp_base(fwd_ins[ins_len - 1 - x]);
+            }
+            const int64_t w_local = seg_len(local_seq) + seg_len(local_ref);
+            const int64_t w_remote = seg_len(remote_ref) + seg_len(remote_seq);
+            WindowSeg* q0 = qs + 6 * k;
+            WindowSeg* w0 = ws + 4 * k;
+            // pair 2k: align(breakend, localSeq + localRef)  (:76-78)
+            q0[0] = slot(local_bs, false);
+            q0[1] = WindowSeg{-1, 0, lit0, lit0 + ins_len};
+            q0[2] = slot(remote_bs, true);
+            w0[0] = slot(local_seq, false);
+            w0[1] = slot(local_ref, false);
+            // pair 2k+1: align(rc(breakend), rc(remoteRef + remoteSeq))  (:86-94); rc(rc(anchor)) = the anchor itself
+            q0[3] = slot(remote_bs, false);
+            q0[4] = WindowSeg{-1, 0, lit0 + ins_len, lit0 + 2 * ins_len};
+            q0[5] = slot(local_bs, true);
+            w0[2] = slot(remote_seq, false);
+            w0[3] = slot(remote_ref, false);
+            const bool a = q > 0 && w_local > 0, c = q > 0 && w_remote > 0;
+            seq_off[2 * k + 1] = a ? q : 0; ref_off[2 * k + 1] = a ? w_local : 0;
+            seq_off[2 * k + 2] = c ? q : 0; ref_off[2 * k + 2] = c ? w_remote : 0;
+        }
+    };
+    {
+        const int nthreads = n < 32768 ? 1 : (int)std::min<int64_t>(std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u), n / 16384);
+        if (nthreads <= 1) plan(0, n);
+        else {
+            std::vector<std::thread> th;
+            for (int t = 0; t < nthreads; t++) th.emplace_back(plan, n * t / nthreads, n * (t + 1) / nthreads);
+            for (auto& t : th) t.join();
+        }
+    }
+    if (bad.load() >= 0) {
+        h->error = "breakpoint " + std::to_string(bad.load()) + ": contig, direction or inserted-sequence offsets out of range";
+        return CUDASW_EINVAL;
+    }
+    seq_off[0] = ref_off[0] = 0;
+    for (int64_t p = 0; p < np; p++) { seq_off[p + 1] += seq_off[p]; ref_off[p + 1] += ref_off[p]; }
+    for (int64_t k = 0; k < n; k++) { local_hom[k] = 0; remote_hom[k] = 0; }
+    if (seq_off[np] == 0 || ref_off[np] == 0) return CUDASW_OK;  // nothing to align anywhere
+    cudasw_result* res = h->hom_res.p;
+    const QuerySegs qsegs{qs, nullptr, 3, lit, lit_bytes, 2};
+    const int rc = h->run(np, nullptr, nullptr, nullptr, nullptr, seq_off[np], ref_off[np], res, nullptr, 0, nullptr, true,
+                          nullptr, seq_off, nullptr, ref_off, ws, nullptr, &qsegs, true);
+    if (rc != CUDASW_OK) return rc;
+    for (int64_t p = 0; p < np; p++) {
+        const int64_t q = seq_off[p + 1] - seq_off[p];
+        if (q == 0 || ref_off[p + 1] == ref_off[p]) continue;  // a call the reference skips (:75-76, :86)
+        const cudasw_result& r = res[p];
+        if (r.status != CUDASW_OK) { h->error = "pair failed with status " + std::to_string(r.status); return r.status; }
+        const int64_t lead = r.read_begin, tail = q - r.read_end - 1;   // the clips of SswJniAligner.java:52-59
+        // homology = bases of the OTHER side's breakend sequence that aligned; nothing if the anchor is clipped
+        const int64_t other = n_bs[(size_t)(p ^ 1)];
+        const int32_t v = lead > 0 ? 0 : (int32_t)std::max<int64_t>(0, other - tail);
+        if (p & 1) local_hom[p >> 1] = v; else remote_hom[p >> 1] = v;
+    }
+    return CUDASW_OK;
 }
 
 extern "C" int cudasw_reference_fetch(cudasw_t* h, const cudasw_window* win, int32_t n_win, uint8_t* out, int64_t out_cap) {

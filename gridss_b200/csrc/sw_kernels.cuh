@@ -154,11 +154,15 @@ struct WindowSeg {
 // Expands window segments straight into the ENCODED window layout the score kernels read (no ASCII round trip):
 // one warp per pair, 4 bases per lane and iteration, 32-bit stores once the destination is aligned.
 // ascii != 0 writes upper-case "ACGTN" instead (getSubsequenceAt, for cudasw_reference_fetch).
+// The same kernel assembles QUERIES on the device (xor_mask 0 = the query encoding): a segment with contig < 0 takes
+// bytes [start, end) of the literal blob `lit` (e.g. the untemplated sequence between the two breakend anchors,
+// BreakpointHomology.java:67).
 __global__ void __launch_bounds__(256)
 window_gather_kernel(int n, const WindowSeg* __restrict__ segs, const int64_t* __restrict__ seg_off,
                      const int64_t* __restrict__ ref_off, const int64_t* __restrict__ contig_off,
                      const uint32_t* __restrict__ two_bit, const uint32_t* __restrict__ nmask,
-                     uint8_t* __restrict__ out, uint8_t* __restrict__ flags, int* __restrict__ any_n, int ascii) {
+                     uint8_t* __restrict__ out, uint8_t* __restrict__ flags, int* __restrict__ any_n, int ascii,
+                     const uint8_t* __restrict__ lit = nullptr, uint32_t xor_mask = 0x80u, int seg_stride = 0) {
     const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (p >= n) return;
@@ -166,18 +170,29 @@ window_gather_kernel(int n, const WindowSeg* __restrict__ segs, const int64_t* _
     const int64_t wlen = ref_off[p + 1] - ref_off[p];
     int64_t done = 0;
     bool seen_n = false;
+    bool literal = false;  // contig < 0: bytes [start, end) of `lit` (raw ASCII, never reverse-complemented here)
     auto fetch = [&](int64_t g, bool rc) -> uint32_t {
-        uint32_t code = (two_bit[g >> 4] >> (2 * (int)(g & 15))) & 3u;
-        if (rc) code = 3u - code;
-        if ((nmask[g >> 5] >> (int)(g & 31)) & 1u) { code = 4u; seen_n = true; }
+        uint32_t code;
+        if (literal) {
+            code = base_code(lit[g]);
+            if (code == 4u) seen_n = true;
+        } else {
+            code = (two_bit[g >> 4] >> (2 * (int)(g & 15))) & 3u;
+            if (rc) code = 3u - code;
+            if ((nmask[g >> 5] >> (int)(g & 31)) & 1u) { code = 4u; seen_n = true; }
+        }
         if (ascii) return code == 0 ? 'A' : code == 1 ? 'C' : code == 2 ? 'G' : code == 3 ? 'T' : 'N';
-        return (code * 0x11u) ^ 0x80u;
+        return (code * 0x11u) ^ xor_mask;
     };
-    for (int64_t s = seg_off[p]; s < seg_off[p + 1] && done < wlen; s++) {
+    // seg_stride > 0: every pair owns exactly that many descriptor slots (empty ones have start == end), no offsets
+    const int64_t s_lo = seg_stride > 0 ? (int64_t)p * seg_stride : seg_off[p];
+    const int64_t s_hi = seg_stride > 0 ? s_lo + seg_stride : seg_off[p + 1];
+    for (int64_t s = s_lo; s < s_hi && done < wlen; s++) {
         const WindowSeg sg = segs[s];
         const int64_t len = min(sg.end - sg.start, wlen - done);  // the host sized ref_off from the same segments
-        const bool rc = (sg.flags & 1) != 0;
-        const int64_t g0 = contig_off[sg.contig] + sg.start;
+        literal = sg.contig < 0;
+        const bool rc = !literal && (sg.flags & 1) != 0;
+        const int64_t g0 = literal ? sg.start : contig_off[sg.contig] + sg.start;
         uint8_t* d = dst + done;
         const int64_t head = min((int64_t)((4 - (reinterpret_cast<uintptr_t>(d) & 3)) & 3), len);
         if (lane < head) d[lane] = (uint8_t)fetch(rc ? g0 + len - 1 - lane : g0 + lane, rc);
@@ -932,6 +947,29 @@ __device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begi
         if (tail) o[nbody] = ((uint32_t)(q - read_end - 1) << 4) | CUDASW_CIGAR_S;
     } else {
         r.status = CUDASW_ENOMEM;
+    }
+    res[pair] = r;
+}
+
+// Results without a CIGAR (callers that only read the clip lengths, BreakpointHomology.java:82-84,96-98): the ends of
+// the forward pass and the begins of the reverse pass, exactly as tb_emit reports them; cigar_len = 0.
+__global__ void ends_only_kernel(int n, const int4* __restrict__ fwd, const int4* __restrict__ rev,
+                                 cudasw_result* __restrict__ res) {
+    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n) return;
+    cudasw_result r = res[pair];
+    if (r.status != CUDASW_OK) return;
+    const int4 f = fwd[pair];
+    r.score = f.x;
+    r.cigar_off = 0; r.cigar_len = 0;
+    if (f.x <= 0) {
+        r.ref_begin = -1; r.ref_end = -1; r.read_begin = 0; r.read_end = 0;
+    } else {
+        const int4 rv = rev[pair];
+        if (rv.w != 0) r.status = CUDASW_ENOMEM;
+        else if (rv.x != f.x) r.status = CUDASW_ECUDA;
+        r.ref_end = f.y; r.read_end = f.z;
+        r.ref_begin = f.y - rv.y; r.read_begin = f.z - rv.z;
     }
     res[pair] = r;
 }

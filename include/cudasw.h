@@ -131,6 +131,26 @@ int cudasw_align_batch_windows(cudasw_t* h, int64_t n_pairs, const uint8_t* seq_
                                const cudasw_window* win, const int64_t* win_off, cudasw_result* out,
                                uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used);
 
+/* ---- BreakpointHomology.calculate for a list of breakpoints (SURVEY.md 8a A7, 8f N1+N3).
+ * Replaces the loop body of AnnotateInexactHomology / AnnotateInexactHomologyBedpe.java:68 around
+ * BreakpointHomology.calculate(lookup, bs, insertedSequence, maxBreakendLength, margin)
+ * (alignment/BreakpointHomology.java:38-103): for every breakpoint two alignments of the breakend sequence
+ * (local anchor + inserted sequence + remote anchor) against the local and the remote reference context, and from their
+ * clip lengths the two homology lengths. Needs a loaded reference (cudasw_reference_load): 32 bytes per breakpoint
+ * (+ its inserted bases) go to the device, queries and windows are gathered there, only the score passes run.
+ * Positions are 1-based and exact (start == end), as the reference requires (:39-41); dir 0 = forward, 1 = backward
+ * (BreakendDirection). ins_off (n + 1 offsets into ins_blob) may be NULL = no inserted sequence anywhere.
+ * Returns CUDASW_EINVAL for a contig / direction out of range (the reference throws). */
+typedef struct cudasw_breakpoint {
+    int32_t contig1, dir1;
+    int64_t pos1;
+    int32_t contig2, dir2;
+    int64_t pos2;
+} cudasw_breakpoint;
+int cudasw_breakpoint_homology(cudasw_t* h, int64_t n, const cudasw_breakpoint* bp, const uint8_t* ins_blob,
+                               const int64_t* ins_off, int32_t max_breakend_length, int32_t margin,
+                               int32_t* local_hom, int32_t* remote_hom);
+
 /* Device-memory helpers so a torch-free host (the JNI shim, the ctypes mirror) can stage inputs. */
 int cudasw_device_alloc(cudasw_t* h, size_t bytes, void** dptr);
 int cudasw_device_free(cudasw_t* h, void* dptr);

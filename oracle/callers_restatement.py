@@ -1,4 +1,4 @@
-"""Test infrastructure: one-pair-at-a-time string restatements of the reference's two callers of
+"""TEST INFRASTRUCTURE (like everything under oracle/; never imported by gridss_b200/): one-pair-at-a-time string restatements of the reference's two callers of
 Aligner.align_smith_waterman, written the way the reference does it (host strings, one aligner call each), to
 check gridss_b200/callers.py's batched / window-descriptor formulation against.
 
@@ -58,9 +58,12 @@ def soft_clips(cigar: str):
     return first(ops), first(ops[::-1])
 
 
-def homology_strings(align, contigs, bp, inserted, max_breakend_length, margin):
+def homology_pairs(contigs, bp, inserted, max_breakend_length, margin):
+    """The two aligner calls of BreakpointHomology.calculate as (seq, ref) byte pairs (None where the reference skips
+    the call), plus the lengths of localBsSeq and remoteBsSeq."""
     r1, d1, p1, r2, d2, p2 = bp
-    ins = (inserted or "").encode()
+    ins = inserted or b""
+    ins = ins.encode() if isinstance(ins, str) else bytes(ins)
     if d1 == "b":
         ins = rc(ins)
     seq_len = max_breakend_length
@@ -78,17 +81,28 @@ def homology_strings(align, contigs, bp, inserted, max_breakend_length, margin):
     breakend = local_bs + ins + remote_bs
     local = local_seq + local_ref
     remote = remote_ref + remote_seq
+    pair_a = (breakend, local) if breakend and local else None
+    pair_b = (rc(breakend), rc(remote)) if breakend and remote else None
+    return len(local_bs), len(remote_bs), pair_a, pair_b
+
+
+def homology_from_cigars(n_local_bs, n_remote_bs, cigar_a, cigar_b):
+    """(localHomologyLength, remoteHomologyLength) from the CIGARs of the two calls (None = call skipped)."""
     local_h = remote_h = 0
-    if breakend:
-        if local:
-            _, cigar = align(breakend, local)
-            lead, tail = soft_clips(cigar)
-            remote_h = 0 if lead > 0 else max(0, len(remote_bs) - tail)
-        if remote:
-            _, cigar = align(rc(breakend), rc(remote))
-            lead, tail = soft_clips(cigar)
-            local_h = 0 if lead > 0 else max(0, len(local_bs) - tail)
+    if cigar_a is not None:
+        lead, tail = soft_clips(cigar_a)
+        remote_h = 0 if lead > 0 else max(0, n_remote_bs - tail)
+    if cigar_b is not None:
+        lead, tail = soft_clips(cigar_b)
+        local_h = 0 if lead > 0 else max(0, n_local_bs - tail)
     return local_h, remote_h
+
+
+def homology_strings(align, contigs, bp, inserted, max_breakend_length, margin):
+    nl, nr, pair_a, pair_b = homology_pairs(contigs, bp, inserted, max_breakend_length, margin)
+    cig_a = align(*pair_a)[1] if pair_a else None
+    cig_b = align(*pair_b)[1] if pair_b else None
+    return homology_from_cigars(nl, nr, cig_a, cig_b)
 
 
 def realign_strings(align, contigs, read, window, extend):

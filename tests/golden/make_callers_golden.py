@@ -4,7 +4,7 @@ Known answers of the reference's caller-level tests, transcr
   BreakpointHomologyTest.java:43-224   (expected local / remote homology lengths)
   SAMRecordUtilTest.java:375-382       (realign: expected start and CIGAR)
 The `random` contig of the reference's test genome (src/test/resources/small.fa) is test data the realign case needs;
-only its first 400 bases are stored. Every expected value is re-derived here by a plain string restatement of
+only its first 600 bases are stored, and the 251-base chr1 excerpt of issue #778. Every expected value is re-derived here by a plain string restatement of
 BreakpointHomology.calculate / SAMRecordUtil.realign driven through the reference's shipped libsswjni.so
 (oracle/_ref), so a transcription slip fails at generation time.
 """
@@ -15,9 +15,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
 from oracle import oracle as O  # noqa: E402
-from callers_restatement import homology_strings, realign_strings  # noqa: E402
+from oracle.callers_restatement import homology_strings, realign_strings  # noqa: E402
 
 SMALL_FA = "/root/reference/src/test/resources/small.fa"
 
@@ -70,7 +69,6 @@ def main():
     assert O.have_reference(), "oracle/_ref is needed to regenerate"
     fa = read_fasta(SMALL_FA)
     assert set(fa["polyA"]) == {"A"} and len(fa["polyA"]) == 10000
-    random400 = fa["random"][:400]
     cases = []
     for cite, contigs, bp, ins, mbl, margin, expect in HOMOLOGY:
         real = [b"A" * 10000] if contigs is POLYA else [c.encode() for c in contigs]
@@ -78,15 +76,44 @@ def main():
         assert tuple(got) == tuple(expect), (cite, got, expect)
         cases.append({"cite": cite, "contigs": contigs, "breakpoint": list(bp), "inserted": ins, "maxBreakendLength": mbl,
                       "margin": margin, "local": expect[0], "remote": expect[1]})
-    # SAMRecordUtilTest.java:375-382: Read(2, 101, "100M"), bases RANDOM[100:199] + "N", window 0, extend -> 99M1S @ 101
-    bases = random400[100:199] + "N"
-    contigs = [b"A" * 10, b"ACGT" * 4, random400.encode()]
-    got = realign_strings(align_one, contigs, (2, 101, "100M", bases.encode()), 0, True)
-    assert got == (101, "99M1S"), got
-    realign = [{"cite": "SAMRecordUtilTest.java:375-382", "random400": random400, "read": [2, 101, "100M", bases],
-                "windowSize": 0, "extend": True, "start": 101, "cigar": "99M1S"}]
-    json.dump({"homology": cases, "realign": realign}, open(os.path.join(HERE, "golden_callers.json"), "w"), indent=1)
-    print("wrote golden_callers.json:", len(cases), "homology cases,", len(realign), "realign case")
+    # realign. A read is (referenceIndex, alignmentStart, cigar, bases); AssemblyFactory.createAnchoredBreakend
+    # (AssemblyFactory.java:186-197) makes a FWD assembly "<anchored>M<rest>S" starting at pos - anchored + 1 and a
+    # BWD one "<rest>S<anchored>M" starting at pos; the tests' breakend position is the alignment end (FWD) or
+    # start (BWD) of the realigned record.
+    R = fa["random"]
+    random600 = R[:600]
+    chr1 = read_fasta("/root/reference/src/test/resources/chr1_170849600_170849850.fa")
+    chr1 = next(iter(chr1.values()))
+    asm778 = ("ATCCATCCCTATGACCCAAACATCTCCCACCAGGCCTCATGTTCAATATTAAAGATCACATTTCAACTTGAGATTTGGAGGGGACAAACATACAAATCATATCATT"
+              "ATCTCTCTCCCCACTTCTCTCTTTATCAATCCCTCCCTCTTTGTCAATCTTAGCCTTGGCCTTCAGATTTTACCACTTGATTTTTCACATTTTCTGTATTCTTAAT"
+              "GATTATTATATTTTCATGTTCTTGCTAATCTATATCATGGTTAGAAATCAAAGCATGCCGAAATTTCTCTCTTACTTTTTTTGCTGTT")
+    assert len(asm778) == 300
+    small = ["@polyA10000", "ACGT" * 4, "@random600"]
+    realign = [
+        ("SAMRecordUtilTest.java:375-382", small, (2, 101, "100M", R[100:199] + "N"), 0, True, 101, "99M1S"),
+        ("SAMRecordAssemblyEvidenceTest.java:166-180 (#778)", [chr1], (0, 103, "203S97M", asm778), 50, True, 114, "212S88M"),
+        ("SAMRecordAssemblyEvidenceTest.java:182-188", small, (0, 1, "10M12S", "AAAAAAAAAATTAAAAAAAAAA"), 50, True, None, "10M2I10M"),
+        ("SAMRecordAssemblyEvidenceTest.java:229-237", small, (0, 1, "5M3S", "AAAATTTT"), 50, True, 1, "4M4S"),
+        ("SAMRecordAssemblyEvidenceTest.java:261-266 (BWD)", small, (2, 300, "101S100M", "N" + R[179:279] + R[299:399]), 50, True, None, "1S100M20D100M"),
+        ("SAMRecordAssemblyEvidenceTest.java:268-272 (FWD)", small, (2, 300, "100M101S", R[299:399] + R[419:519] + "N"), 50, True, None, "100M20D100M1S"),
+        ("SAMRecordAssemblyEvidenceTest.java:274-281", small, (2, 1, "90S210M", "N" * 100 + R[0:100] + R[110:210]), 50, True, None, "100S100M10D100M"),
+        ("SAMRecordAssemblyEvidenceTest.java:283-290", small, (2, 1, "110S200M", "N" * 100 + R[0:100] + "N" * 10 + R[100:200]), 50, True, None, "100S100M10I100M"),
+    ]
+    for startpos in range(250, 351):   # SAMRecordAssemblyEvidenceTest.java:239-258: +-50 bp sweep, both directions
+        realign.append((f"SAMRecordAssemblyEvidenceTest.java:241-248 (BWD @{startpos})", small,
+                        (2, startpos, "50S100M", "N" * 50 + R[299:399]), 50, True, 300, "50S100M"))
+        realign.append((f"SAMRecordAssemblyEvidenceTest.java:250-257 (FWD @{startpos})", small,
+                        (2, startpos, "100M50S", R[299:399] + "N" * 50), 50, True, 300, "100M50S"))
+    out_realign = []
+    for cite, contigs, read, window, extend, start, cigar in realign:
+        real = [b"A" * 10000 if c == "@polyA10000" else random600.encode() if c == "@random600" else c.encode() for c in contigs]
+        got = realign_strings(align_one, real, (read[0], read[1], read[2], read[3].encode()), window, extend)
+        assert got[1] == cigar and (start is None or got[0] == start), (cite, got, start, cigar)
+        out_realign.append({"cite": cite, "contigs": contigs, "read": list(read), "windowSize": window, "extend": extend,
+                            "start": got[0], "cigar": cigar})
+    json.dump({"random600": random600, "homology": cases, "realign": out_realign},
+              open(os.path.join(HERE, "golden_callers.json"), "w"), indent=1)
+    print("wrote golden_callers.json:", len(cases), "homology cases,", len(out_realign), "realign cases")
 
 
 if __name__ == "__main__":

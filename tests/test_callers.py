@@ -9,7 +9,7 @@ import os
 import numpy as np
 import pytest
 
-from callers_restatement import homology_strings, rc, realign_strings
+from oracle.callers_restatement import homology_strings, rc, realign_strings
 from gridss_b200 import callers as C
 from gridss_b200.aligner import RESULT_DTYPE, WINDOW_REVCOMP
 
@@ -17,7 +17,13 @@ GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden_
 
 
 def contigs_of(case):
-    return [b"A" * 10000] if case["contigs"] == ["@polyA10000"] else [c.encode() for c in case["contigs"]]
+    named = {"@polyA10000": b"A" * 10000, "@random600": GOLD["random600"].encode()}
+    return [named.get(c) or c.encode() for c in case["contigs"]]
+
+
+def read_of(case):
+    r = case["read"]
+    return (r[0], r[1], r[2], r[3].encode())
 
 
 class OracleWindowAligner:
@@ -99,9 +105,7 @@ def test_restatement_reproduces_reference_expectations(oracle):
         got = homology_strings(f, contigs_of(c), tuple(c["breakpoint"]), c["inserted"], c["maxBreakendLength"], c["margin"])
         assert got == (c["local"], c["remote"]), c["cite"]
     for c in GOLD["realign"]:
-        contigs = [b"A" * 10, b"ACGT" * 4, c["random400"].encode()]
-        read = (c["read"][0], c["read"][1], c["read"][2], c["read"][3].encode())
-        assert realign_strings(f, contigs, read, c["windowSize"], c["extend"]) == (c["start"], c["cigar"])
+        assert realign_strings(f, contigs_of(c), read_of(c), c["windowSize"], c["extend"]) == (c["start"], c["cigar"]), c["cite"]
 
 
 def test_batched_homology_known_answers_cpu(oracle):
@@ -160,11 +164,11 @@ def test_event_size_and_exactness():
 
 def test_batched_realign_cpu(oracle):
     c = GOLD["realign"][0]
-    contigs = [b"A" * 10, b"ACGT" * 4, c["random400"].encode()]
+    contigs = contigs_of(c)
     al = OracleWindowAligner(oracle, contigs)
-    read = (c["read"][0], c["read"][1], c["read"][2], c["read"][3].encode())
+    read = read_of(c)
     rng = np.random.default_rng(9)
-    g = c["random400"]
+    g = GOLD["random600"][:400]
     reads = [read, (2, 101, "100M", b""), (2, 50, "10S80M10S", (g[30:80] + g[95:145]).encode()),
              (2, 380, "5S30M", g[360:395].encode()), (2, 1, "20M3S", ("TTT" + g[:20]).encode())]
     for _ in range(40):
@@ -179,11 +183,66 @@ def test_batched_realign_cpu(oracle):
     for window, extend in ((0, True), (10, False), (500, True)):
         got = C.realign_batch(al, [len(x) for x in contigs], reads, window, extend)
         assert got == [realign_strings(f, contigs, r, window, extend) for r in reads]
-    assert C.realign_batch(al, [len(x) for x in contigs], [read], 0, True) == [(c["start"], c["cigar"])]
     assert C.realign_batch(al, [len(x) for x in contigs], reads[1:2], 0, True) == [(101, "100M")]   # no bases: unchanged
 
 
+def realign_known_answers(make_aligner):
+    """Every realign case of the reference's tests, grouped by genome so each group is one batch."""
+    groups = {}
+    for c in GOLD["realign"]:
+        groups.setdefault((tuple(c["contigs"]), c["windowSize"], c["extend"]), []).append(c)
+    for (_, window, extend), cases in groups.items():
+        contigs = contigs_of(cases[0])
+        got = C.realign_batch(make_aligner(contigs), [len(x) for x in contigs], [read_of(c) for c in cases], window, extend)
+        for c, g in zip(cases, got):
+            assert g == (c["start"], c["cigar"]), c["cite"]
+
+
+def test_batched_realign_known_answers_cpu(oracle):
+    realign_known_answers(lambda contigs: OracleWindowAligner(oracle, contigs))
+
+
+def streaming_case(make_aligner, oracle, n_reads=60, contig_len=600, batch=16):
+    rng = np.random.default_rng(21)
+    contig = GOLD["random600"][:contig_len].encode() if contig_len <= 600 else random_genome(rng, 1, contig_len)[0]
+    contigs = [b"ACGT" * 5, b"A" * 30, contig]
+    sw = C.SmithWatermanStreamingAligner(make_aligner(contigs), [len(x) for x in contigs], 2, batch=batch)
+    reads = []
+    for k in range(n_reads):
+        p, q = int(rng.integers(0, contig_len - 120)), int(rng.integers(20, 120))
+        b = bytearray(contig[p:p + q])
+        if k % 3 == 0:
+            b[q // 2:q // 2] = b"TTTT"
+        if k % 4 == 0:
+            b = bytearray(b"GGGGGG") + b
+        reads.append((f"r{k}", bytes(b)))
+    for name, b in reads:
+        sw.asyncAlign(name, b)
+    assert sw.processedAlignmentRecords() == n_reads // batch * batch and sw.outstandingAlignmentRecord() == n_reads % batch
+    sw.flush()
+    assert sw.processedAlignmentRecords() == n_reads and sw.outstandingAlignmentRecord() == 0
+    want = oracle.model_align([b for _, b in reads], [contig.upper()] * n_reads)
+    for i, (name, b) in enumerate(reads):
+        score, start, cigar = want.tuple(i)
+        assert sw.getAlignment() == (name, 2, start + 1, cigar)      # SmithWatermanStreamingAligner.java:36-38
+    with pytest.raises(ValueError):
+        sw.asyncAlign("empty", b"")
+
+
+def test_streaming_whole_contig_aligner_cpu(oracle):
+    streaming_case(lambda contigs: OracleWindowAligner(oracle, contigs), oracle)
+
+
 # ---------------------------------------------------------------- GPU: through the C ABI
+
+
+@pytest.mark.gpu
+def test_streaming_whole_contig_aligner_gpu(aligner, oracle):
+    def loaded(contigs):
+        aligner.load_reference(contigs)
+        return aligner
+    streaming_case(loaded, oracle)
+    streaming_case(loaded, oracle, n_reads=300, contig_len=12000, batch=128)
 
 
 @pytest.mark.gpu
@@ -224,11 +283,10 @@ def test_batched_homology_gpu_matches_oracle(aligner, oracle):
 
 @pytest.mark.gpu
 def test_batched_realign_gpu(aligner, oracle):
-    c = GOLD["realign"][0]
-    contigs = [b"A" * 10, b"ACGT" * 4, c["random400"].encode()]
-    aligner.load_reference(contigs)
-    read = (c["read"][0], c["read"][1], c["read"][2], c["read"][3].encode())
-    assert C.realign_batch(aligner, [len(x) for x in contigs], [read], 0, True) == [(c["start"], c["cigar"])]
+    def loaded(contigs):
+        aligner.load_reference(contigs)
+        return aligner
+    realign_known_answers(loaded)
     rng = np.random.default_rng(13)
     genome = random_genome(rng, n_contigs=2, length=50000)
     aligner.load_reference(genome)
@@ -246,3 +304,64 @@ def test_batched_realign_gpu(aligner, oracle):
     lens = [len(x) for x in genome]
     for window, extend in ((0, True), (25, False)):
         assert C.realign_batch(aligner, lens, reads, window, extend) == C.realign_batch(ref, lens, reads, window, extend)
+
+
+@pytest.mark.gpu
+def test_device_homology_known_answers(aligner):
+    """cudasw_breakpoint_homology: the reference tests' expected lengths, segments derived and gathered by the library."""
+    for c in GOLD["homology"]:
+        contigs = contigs_of(c)
+        aligner.load_reference(contigs)
+        got = C.breakpoint_homology_device(aligner, [bp_of(c["breakpoint"])], [c["inserted"]], c["maxBreakendLength"], c["margin"])
+        assert got == [(c["local"], c["remote"])], c["cite"]
+        st = aligner.stats()
+        assert st["d2h_bytes"] == 32 * st["pairs"]      # clip lengths only: no traceback ran, no CIGAR came back
+
+
+@pytest.mark.gpu
+def test_device_homology_contig_bounds(aligner):
+    contigs = [b"C" * 11, b"A" * 11]
+    aligner.load_reference(contigs)
+    bps = C.breakpoint_array([bp_of(b) for b in bounds_cases(1)])
+    for mbl in range(1, 13):
+        for margin in range(0, 13):
+            local, remote = aligner.breakpoint_homology(bps, None, None, mbl, margin)
+            assert not local.any() and not remote.any(), (mbl, margin)
+
+
+@pytest.mark.gpu
+def test_device_homology_matches_batched_and_restatement(aligner, oracle):
+    rng = np.random.default_rng(17)
+    contigs = random_genome(rng, n_contigs=4, length=20000)
+    contigs[1] = contigs[1].lower()
+    bps, ins = random_breakpoints(rng, contigs, 30000)
+    ins = [i.lower() if k % 5 == 0 else i for k, i in enumerate(ins)]
+    aligner.load_reference(contigs)
+    f = model_align_one(oracle)
+    for mbl, margin in ((20, 10), (300, 10), (100, 100), (0, 5)):
+        got = C.breakpoint_homology_device(aligner, [bp_of(b) for b in bps], ins, mbl, margin)
+        want = C.breakpoint_homology_batch(aligner, contigs, [bp_of(b) for b in bps], ins, mbl, margin)
+        assert got == want
+        assert got[:150] == [homology_strings(f, [c.upper() for c in contigs], b, i, mbl, margin) for b, i in zip(bps[:150], ins[:150])]
+    # no inserted sequence at all: ins_off may be NULL
+    a = C.breakpoint_homology_device(aligner, [bp_of(b) for b in bps[:2000]], None, 300, 10)
+    b = C.breakpoint_homology_device(aligner, [bp_of(b) for b in bps[:2000]], [""] * 2000, 300, 10)
+    assert a == b
+    assert C.breakpoint_homology_device(aligner, [], None, 300, 10) == []
+
+
+@pytest.mark.gpu
+def test_device_homology_rejects_bad_breakpoints(aligner):
+    import gridss_b200 as g
+    aligner.load_reference([b"ACGT" * 10])
+    bad = np.zeros(1, dtype=g.BREAKPOINT_DTYPE)
+    bad[0] = (0, 0, 5, 3, 1, 6)
+    with pytest.raises(ValueError):
+        aligner.breakpoint_homology(bad, None, None, 10, 0)
+    bad[0] = (0, 2, 5, 0, 1, 6)
+    with pytest.raises(ValueError):
+        aligner.breakpoint_homology(bad, None, None, 10, 0)
+    fresh = g.CudaAligner()
+    bad[0] = (0, 0, 5, 0, 1, 6)
+    with pytest.raises(ValueError):     # no reference loaded
+        fresh.breakpoint_homology(bad, None, None, 10, 0)
