@@ -103,6 +103,31 @@ public class CudaAligner implements Aligner, AutoCloseable {
 		}
 		return out;
 	}
+	/**
+	 * BreakpointHomology.calculate(lookup, bs, insertedSequence, maxBreakendLength, margin) for a whole list of exact
+	 * breakpoints in one native call (replaces the per-variant loop of AnnotateInexactHomology /
+	 * AnnotateInexactHomologyBedpe.java:68). Arrays are parallel; dir 0 = BreakendDirection.Forward, 1 = Backward;
+	 * positions are 1-based; insertedSequence[i] may be null. Returns {localHomologyLength[], remoteHomologyLength[]}.
+	 */
+	public int[][] breakpointHomology(int[] referenceIndex, int[] direction, long[] position, int[] referenceIndex2, int[] direction2,
+			long[] position2, String[] insertedSequence, int maxBreakendLength, int margin) {
+		int n = referenceIndex.length;
+		long[] insOff = new long[n + 1];
+		for (int i = 0; i < n; i++) insOff[i + 1] = insOff[i] + (insertedSequence == null || insertedSequence[i] == null ? 0 : insertedSequence[i].length());
+		byte[] insBlob = new byte[(int) Math.max(1, insOff[n])];
+		for (int i = 0; i < n; i++) {
+			if (insOff[i + 1] > insOff[i]) {
+				byte[] b = insertedSequence[i].getBytes(java.nio.charset.StandardCharsets.US_ASCII);
+				System.arraycopy(b, 0, insBlob, (int) insOff[i], b.length);
+			}
+		}
+		int[] local = new int[n], remote = new int[n];
+		int rc = breakpointHomology(handle, n, referenceIndex, direction, position, referenceIndex2, direction2, position2, insBlob, insOff,
+				maxBreakendLength, margin, local, remote);
+		if (rc == -1) throw new IllegalArgumentException("Breakpoint position must be exact and inside the reference: " + lastError(handle));
+		if (rc != 0) throw new IllegalStateException("cudasw_breakpoint_homology failed (" + rc + "): " + lastError(handle));
+		return new int[][] { local, remote };
+	}
 	@Override
 	public synchronized void close() {
 		for (java.nio.ByteBuffer b : new java.nio.ByteBuffer[] { pinSeq, pinRef, pinSeqOff, pinRefOff }) if (b != null) freePinned(b);
@@ -119,6 +144,8 @@ public class CudaAligner implements Aligner, AutoCloseable {
 	private static native int loadReference(long handle, byte[] bases, long[] contigOff);
 	private static native int alignBatchWindows(long handle, int n, byte[] seqBlob, long[] seqOff, int[] segContig, int[] segFlags,
 			long[] segStart, long[] segEnd, long[] winOff, int[] startOut, String[] cigarOut, int[] statusOut);
+	private static native int breakpointHomology(long handle, int n, int[] contig1, int[] dir1, long[] pos1, int[] contig2, int[] dir2,
+			long[] pos2, byte[] insBlob, long[] insOff, int maxBreakendLength, int margin, int[] localOut, int[] remoteOut);
 	private static native int alignBatch(long handle, int n, byte[] seqBlob, long[] seqOff, byte[] refBlob, long[] refOff,
 			int[] startOut, String[] cigarOut, int[] statusOut);
 }

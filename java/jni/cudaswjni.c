@@ -86,6 +86,44 @@ JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_loadReference
     return rc;
 }
 
+/* BreakpointHomology.calculate for n breakpoints (alignment/BreakpointHomology.java:38-103): parallel arrays in,
+ * the two homology lengths out. */
+JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_breakpointHomology(JNIEnv* env, jclass c, jlong h, jint n,
+        jintArray contig1, jintArray dir1, jlongArray pos1, jintArray contig2, jintArray dir2, jlongArray pos2,
+        jbyteArray insBlob, jlongArray insOff, jint maxBreakendLength, jint margin, jintArray localOut, jintArray remoteOut) {
+    cudasw_breakpoint* bp = (cudasw_breakpoint*)malloc(sizeof(cudasw_breakpoint) * (size_t)(n > 0 ? n : 1));
+    int32_t* out = (int32_t*)malloc(sizeof(int32_t) * 2 * (size_t)(n > 0 ? n : 1));
+    if (!bp || !out) { free(bp); free(out); return CUDASW_ENOMEM; }
+    jint* c1 = (*env)->GetIntArrayElements(env, contig1, NULL);
+    jint* d1 = (*env)->GetIntArrayElements(env, dir1, NULL);
+    jlong* p1 = (*env)->GetLongArrayElements(env, pos1, NULL);
+    jint* c2 = (*env)->GetIntArrayElements(env, contig2, NULL);
+    jint* d2 = (*env)->GetIntArrayElements(env, dir2, NULL);
+    jlong* p2 = (*env)->GetLongArrayElements(env, pos2, NULL);
+    for (jint i = 0; i < n; i++) {
+        bp[i].contig1 = c1[i]; bp[i].dir1 = d1[i]; bp[i].pos1 = p1[i];
+        bp[i].contig2 = c2[i]; bp[i].dir2 = d2[i]; bp[i].pos2 = p2[i];
+    }
+    (*env)->ReleaseIntArrayElements(env, contig1, c1, JNI_ABORT);
+    (*env)->ReleaseIntArrayElements(env, dir1, d1, JNI_ABORT);
+    (*env)->ReleaseLongArrayElements(env, pos1, p1, JNI_ABORT);
+    (*env)->ReleaseIntArrayElements(env, contig2, c2, JNI_ABORT);
+    (*env)->ReleaseIntArrayElements(env, dir2, d2, JNI_ABORT);
+    (*env)->ReleaseLongArrayElements(env, pos2, p2, JNI_ABORT);
+    jbyte* ib = (*env)->GetByteArrayElements(env, insBlob, NULL);
+    jlong* io = (*env)->GetLongArrayElements(env, insOff, NULL);
+    int rc = cudasw_breakpoint_homology((cudasw_t*)(intptr_t)h, n, bp, (const uint8_t*)ib, (const int64_t*)io, maxBreakendLength,
+                                        margin, out, out + (n > 0 ? n : 1));
+    (*env)->ReleaseLongArrayElements(env, insOff, io, JNI_ABORT);
+    (*env)->ReleaseByteArrayElements(env, insBlob, ib, JNI_ABORT);
+    if (rc == CUDASW_OK) {
+        (*env)->SetIntArrayRegion(env, localOut, 0, n, (const jint*)out);
+        (*env)->SetIntArrayRegion(env, remoteOut, 0, n, (const jint*)(out + (n > 0 ? n : 1)));
+    }
+    free(bp); free(out);
+    return rc;
+}
+
 /* Windows named as segments: parallel arrays (contig, flags, start, end) of nSeg entries + winOff[n+1]. */
 JNIEXPORT jint JNICALL Java_au_edu_wehi_idsv_alignment_CudaAligner_alignBatchWindows(JNIEnv* env, jclass c, jlong h, jint n,
         jbyteArray seqBlob, jlongArray seqOff, jintArray segContig, jintArray segFlags, jlongArray segStart,

@@ -24,6 +24,9 @@ struct JNINativeInterface_ {
     void (*ReleasePrimitiveArrayCritical)(JNIEnv*, jarray, void*, jint);
     jint* (*GetIntArrayElements)(JNIEnv*, jintArray, jboolean*);
     void (*ReleaseIntArrayElements)(JNIEnv*, jintArray, jint*, jint);
+    jbyte* (*GetByteArrayElements)(JNIEnv*, jbyteArray, jboolean*);
+    void (*ReleaseByteArrayElements)(JNIEnv*, jbyteArray, jbyte*, jint);
+    void (*SetIntArrayRegion)(JNIEnv*, jintArray, jsize, jsize, const jint*);
     jlong* (*GetLongArrayElements)(JNIEnv*, jlongArray, jboolean*);
     void (*ReleaseLongArrayElements)(JNIEnv*, jlongArray, jlong*, jint);
     void (*SetObjectArrayElement)(JNIEnv*, jobjectArray, jsize, jobject);
