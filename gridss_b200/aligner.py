@@ -100,6 +100,7 @@ ABI = [
     ("cudasw_multi_align_batch", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
     ("cudasw_multi_reference_load", ctypes.c_int, [_vp, _i32, _vp, _vp]),
     ("cudasw_multi_align_batch_windows", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_multi_breakpoint_homology", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _i32, _i32, _vp, _vp]),
     ("cudasw_multi_get_stats", ctypes.c_int, [_vp, ctypes.c_int, ctypes.POINTER(Stats), ctypes.POINTER(_i64), ctypes.POINTER(_i64)]),
     ("cudasw_multi_last_error", ctypes.c_char_p, [_vp]),
     ("cudasw_device_alloc", ctypes.c_int, [_vp, _sz, ctypes.POINTER(_vp)]),
@@ -356,6 +357,8 @@ class CudaAligner(Aligner):
                 raise CudaSwError(f"cudasw_align_batch_windows failed ({rc}): {self._err()}")
             return res, cig[: used.value]
 
+    _homology_fn = "cudasw_breakpoint_homology"
+
     def breakpoint_homology(self, bp: np.ndarray, ins_blob=None, ins_off=None, max_breakend_length: int = 300, margin: int = 10):
         """BreakpointHomology.calculate (BreakpointHomology.java:38-103) for BREAKPOINT_DTYPE[n] against the loaded
         reference -> (localHomologyLength int32[n], remoteHomologyLength int32[n]). The defaults are
@@ -370,11 +373,11 @@ class CudaAligner(Aligner):
             if ins_blob is None or len(ins_blob) == 0:
                 ins_blob = np.zeros(1, dtype=np.uint8)
         bp = np.ascontiguousarray(bp)
-        rc = self._lib.cudasw_breakpoint_homology(
+        rc = getattr(self._lib, self._homology_fn)(
             self._h, n, bp.ctypes.data, None if ins_off is None else ins_blob.ctypes.data,
             None if ins_off is None else ins_off.ctypes.data, max_breakend_length, margin, local.ctypes.data, remote.ctypes.data)
         if rc != 0:
-            raise (ValueError if rc == CUDASW_EINVAL else CudaSwError)(f"cudasw_breakpoint_homology failed ({rc}): {self._err()}")
+            raise (ValueError if rc == CUDASW_EINVAL else CudaSwError)(f"{self._homology_fn} failed ({rc}): {self._err()}")
         return local, remote
 
     def variant_for(self, query_len: int) -> tuple[int, int, int]:
@@ -527,6 +530,9 @@ class MultiGpuAligner(Aligner):
         assert win.dtype == WINDOW_DTYPE
         return self._call(self._lib.cudasw_multi_align_batch_windows, "cudasw_multi_align_batch_windows", len(seq_off) - 1,
                           (seq_blob.ctypes.data, seq_off.ctypes.data, win.ctypes.data, win_off.ctypes.data), res, cig)
+
+    _homology_fn = "cudasw_multi_breakpoint_homology"
+    breakpoint_homology = CudaAligner.breakpoint_homology   # same marshalling, the multi-GPU entry point
 
     def align_batch(self, seqs: Sequence[bytes], refs: Sequence[bytes]) -> list[Alignment]:
         if len(seqs) != len(refs):

@@ -245,3 +245,43 @@ extern "C" int cudasw_multi_align_batch_windows(cudasw_multi_t* m, int64_t n, co
                           return cudasw_align_batch_windows(m->eng[(size_t)d], cnt, seq_blob + sb, so.data(), win + wb, wo.data(), o, cg, cap, used);
                       });
 }
+
+// BreakpointHomology.calculate across all GPUs: equal contiguous slices of the breakpoint list (every breakpoint costs
+// about the same two alignments), each against that GPU's replica of the reference; outputs land at the original
+// ordinals. No exchange step.
+extern "C" int cudasw_multi_breakpoint_homology(cudasw_multi_t* m, int64_t n, const cudasw_breakpoint* bp, const uint8_t* ins_blob,
+                                                const int64_t* ins_off, int32_t max_breakend_length, int32_t margin,
+                                                int32_t* local_hom, int32_t* remote_hom) {
+    if (!m) return CUDASW_EINVAL;
+    std::lock_guard<std::mutex> lock(m->mu);
+    m->error.clear();
+    if (n < 0 || (n > 0 && (!bp || !local_hom || !remote_hom))) { m->error = "bad argument"; return CUDASW_EINVAL; }
+    if (n == 0) return CUDASW_OK;
+    const int parts = (int)m->eng.size();
+    std::vector<int64_t> cut((size_t)parts + 1);
+    for (int d = 0; d <= parts; d++) cut[(size_t)d] = n * d / parts;
+    m->last_first = cut;
+    std::vector<int> rcs((size_t)parts, CUDASW_OK);
+    std::vector<std::thread> th;
+    for (int d = 0; d < parts; d++) {
+        th.emplace_back([&, d] {
+            const int64_t first = cut[(size_t)d], cnt = cut[(size_t)d + 1] - first;
+            if (cnt == 0) return;
+            std::vector<int64_t> io;
+            if (ins_off) {
+                io.resize((size_t)cnt + 1);
+                for (int64_t i = 0; i <= cnt; i++) io[(size_t)i] = ins_off[first + i] - ins_off[first];
+            }
+            rcs[(size_t)d] = cudasw_breakpoint_homology(m->eng[(size_t)d], cnt, bp + first, ins_off ? ins_blob + ins_off[first] : nullptr,
+                                                        ins_off ? io.data() : nullptr, max_breakend_length, margin, local_hom + first,
+                                                        remote_hom + first);
+        });
+    }
+    for (auto& t : th) t.join();
+    for (int d = 0; d < parts; d++)
+        if (rcs[(size_t)d] != CUDASW_OK) {
+            m->error = "device " + std::to_string(m->devices[(size_t)d]) + ": " + cudasw_last_error(m->eng[(size_t)d]);
+            return rcs[(size_t)d];
+        }
+    return CUDASW_OK;
+}

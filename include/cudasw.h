@@ -193,6 +193,11 @@ int cudasw_multi_reference_load(cudasw_multi_t* m, int32_t n_contigs, const uint
 int cudasw_multi_align_batch_windows(cudasw_multi_t* m, int64_t n_pairs, const uint8_t* seq_blob, const int64_t* seq_off,
                                      const cudasw_window* win, const int64_t* win_off, cudasw_result* out,
                                      uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used);
+/* cudasw_breakpoint_homology over all GPUs of the handle (equal contiguous slices of the list, reference replicated by
+ * cudasw_multi_reference_load). */
+int cudasw_multi_breakpoint_homology(cudasw_multi_t* m, int64_t n, const cudasw_breakpoint* bp, const uint8_t* ins_blob,
+                                     const int64_t* ins_off, int32_t max_breakend_length, int32_t margin,
+                                     int32_t* local_hom, int32_t* remote_hom);
 /* Stats of GPU `idx` for the last batch and the slice [first_pair, first_pair + n_pairs) it was given. */
 int cudasw_multi_get_stats(cudasw_multi_t* m, int idx, cudasw_stats* out, int64_t* first_pair, int64_t* n_pairs);
 const char* cudasw_multi_last_error(cudasw_multi_t* m); /* m may be NULL: last create() error */

@@ -365,3 +365,27 @@ def test_device_homology_rejects_bad_breakpoints(aligner):
     bad[0] = (0, 0, 5, 0, 1, 6)
     with pytest.raises(ValueError):     # no reference loaded
         fresh.breakpoint_homology(bad, None, None, 10, 0)
+
+
+@pytest.mark.gpu
+def test_multi_handle_homology_matches_single(aligner):
+    """cudasw_multi_breakpoint_homology: the list cut over the GPUs of the box (twice the same GPU on a 1-GPU box)."""
+    import torch
+
+    import gridss_b200 as g
+    n_dev = torch.cuda.device_count()
+    ma = g.MultiGpuAligner(devices=list(range(n_dev)) if n_dev > 1 else [0, 0])
+    rng = np.random.default_rng(23)
+    contigs = random_genome(rng, n_contigs=3, length=15000)
+    bps, ins = random_breakpoints(rng, contigs, 9001)
+    aligner.load_reference(contigs)
+    ma.load_reference(contigs)
+    bp = C.breakpoint_array([bp_of(b) for b in bps])
+    blob, off = g.aligner.pack([i.encode() for i in ins])
+    for mbl, margin in ((300, 10), (25, 0)):
+        l1, r1 = aligner.breakpoint_homology(bp, blob, off, mbl, margin)
+        lm, rm = ma.breakpoint_homology(bp, blob, off, mbl, margin)
+        assert np.array_equal(l1, lm) and np.array_equal(r1, rm)
+    l0, r0 = ma.breakpoint_homology(bp, None, None, 300, 10)
+    assert np.array_equal(l0, aligner.breakpoint_homology(bp, None, None, 300, 10)[0])
+    ma.close()
