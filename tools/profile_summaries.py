@@ -71,7 +71,8 @@ def full_capture(rep, name, title, cmd, notes=""):
 
 if __name__ == "__main__":
     tag = sys.argv[1]
-    cmd = "python bench.py --steps 2 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows"
+    cmd = "python bench.py --steps 2 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows --no-homology"
+    hcmd = "python bench.py --steps 1 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows --homology-breakpoints 100000"
     launch_list(tag, cmd)
     for rep, name, title, kre in ((f"prof_fwd_{tag}.ncu-rep", f"ncu_fwd_{tag}.md", "forward score kernel", "sw_score_kernel -s 2"),
                                   (f"prof_tb_{tag}.ncu-rep", f"ncu_tb_{tag}.md", "one-thread traceback kernel", "sw_traceback_kernel -s 5"),
@@ -79,3 +80,8 @@ if __name__ == "__main__":
         if os.path.exists(os.path.join(O, rep)):
             m = full_capture(rep, name, title, f"ncu --set full --clock-control none --import-source on -k regex:{kre} -c 1 {cmd}")
             print(name, {k: m[k] for k in list(m)[:6]})
+    rep = f"prof_gather_{tag}.ncu-rep"
+    if os.path.exists(os.path.join(O, rep)):
+        m = full_capture(rep, f"ncu_gather_{tag}.md", "query gather of cudasw_breakpoint_homology (window_gather_kernel, 200 k pairs x 3 segment slots)",
+                         f"ncu --set full --clock-control none --import-source on -k regex:window_gather_kernel -s 4 -c 1 {hcmd}")
+        print("gather", {k: m[k] for k in list(m)[:6]})
