@@ -305,7 +305,8 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
             one[8 + c] = wd;
         }
         for (int l = 0; l < 32; l++) memcpy(pool + 16 * l, one, sizeof one);
-        if ((e = cudaMalloc(&h->d_pool, sizeof pool)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        if ((e = cudaMalloc(&h->d_pool, sizeof pool + 64)) != cudaSuccess) return fail(cudaGetErrorString(e));  // + 8 step-statistics words (CUSW_STEP_STATS builds)
+        cudaMemset(h->d_pool, 0, sizeof pool + 64);
         if ((e = cudaMemcpy(h->d_pool, pool, sizeof pool, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(cudaGetErrorString(e));
         h->sc.pool_dev = h->d_pool;
     }
@@ -925,7 +926,14 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     }
     CK(cudaEventRecord(ev[5], st));
 #ifdef CUSW_STEP_STATS
-    fprintf(stderr, "[cudasw step stats, forward+reverse warp-steps] quiet %llu, quiet attempt failed %llu, full %llu\n", h_counters[4], h_counters[5], h_counters[6]);
+    {
+        unsigned long long ss[8];
+        CK(cudaStreamSynchronize(st));
+        CK(cudaMemcpy(ss, d_pool + 512, sizeof ss, cudaMemcpyDeviceToHost));
+        CK(cudaMemset(d_pool + 512, 0, sizeof ss));
+        fprintf(stderr, "[cudasw step stats, forward+reverse warp-steps] quiet %llu, quiet attempt failed %llu, full %llu, chained quiet %llu, chain step failed %llu, chains %llu\n",
+                ss[0], ss[1], ss[2], ss[3], ss[4], ss[5]);
+    }
 #endif
 
     // ---- D2H

@@ -572,7 +572,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 
     uint32_t best = sc.BB;
     int col_lo = -1, col_hi = -1, row_lo = 0, row_hi = 0;
-    bool pend_lo = false, pend_hi = false;  // column recorded, row search still owed
+    uint32_t pend = 0u;  // `changed` word of the last step: a non-zero half = column recorded, row search still owed
     uint32_t Hout = sc.BB, Fout = 0u, Hdiag_top = sc.BB, Emax = 0u;
     constexpr uint32_t kOut = PROF ? 0x80u : kWindowPad;  // PROF: 'A'; state reset / maximum mask take care of it
     uint32_t Rsel = kOut | (kOut << 8);
@@ -590,6 +590,19 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         top_next = sc.BB & 0xFFFFu;
         if (read_top && (unsigned)c < (unsigned)w) top_next = bnd_in[c];
     }
+
+    // ---- quiet chains (CHAIN flavours only; see qstep below)
+#ifdef CUSW_NO_CHAIN  // A/B switch for tools/exp_build_run.sh
+    constexpr bool CHAIN = false;
+#else
+    constexpr bool CHAIN = PROF && !REV && !MULTI;
+#endif
+    bool chain = false;  // warp-uniform: the previous step was a verified quiet step
+    bool skipq = false;  // warp-uniform: the step about to be redone by `step` is known not to be quiet
+    int tt = 0;          // step counter (warp-uniform), c == tt - 2 * lig
+    // steps [2G, t_hi) are interior for every lane of the warp: both halves inside [2, w), columns up to c + 2 loadable
+    // from a pair of steps that starts at tt + 2 < t_hi
+    const int t_hi = CHAIN ? __reduce_min_sync(0xffffffffu, active ? w : 0) - 1 : 0;
 
     auto step = [&](uint32_t (&Ho)[R], uint32_t (&Hn)[R]) {
         // ---- inputs from the virtual lane above
@@ -646,7 +659,8 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 #endif
         {
             const uint32_t live = __vimax3_s16x2(Emax, Fin, cBB);
-            if (__all_sync(0xffffffffu, live == cBB)) {
+            // (skipq: a chained quiet step has just failed on this very step, see below: no second attempt)
+            if (!(CHAIN && skipq) && __all_sync(0xffffffffu, live == cBB)) {
 #ifdef CUSW_STEP_STATS
                 tried = true;
 #endif
@@ -684,7 +698,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             Emax = __viaddmax_s16x2(Emax, cNGE2, cm - cGO2);
         }
 #ifdef CUSW_STEP_STATS
-        if ((threadIdx.x & 31) == 0) atomicAdd(sp.used + (quiet ? 4 : tried ? 5 : 6), 1ull);
+        if ((threadIdx.x & 31) == 0) atomicAdd((unsigned long long*)(sc.pool_dev + 512) + (quiet ? 0 : tried ? 1 : 2), 1ull);
 #endif
         Hout = Hn[R - 1];
         Fout = F;
@@ -710,19 +724,108 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         const uint32_t nb = __vmaxs2(best, cm);
         const uint32_t changed = nb ^ best;
         const bool imp_lo = (changed & 0xFFFFu) != 0u, imp_hi = (changed >> 16) != 0u;
-        if ((pend_lo && !imp_lo) || (pend_hi && !imp_hi)) {
+        const bool due_lo = (pend & 0xFFFFu) != 0u && !imp_lo, due_hi = (pend >> 16) != 0u && !imp_hi;
+        if (due_lo || due_hi) {
             const uint32_t cnt = first_row_of(Ho, best, cBB);
-            if (pend_lo && !imp_lo) row_lo = (int)(cnt & 0xFFFFu);
-            if (pend_hi && !imp_hi) row_hi = (int)(cnt >> 16);
+            if (due_lo) row_lo = (int)(cnt & 0xFFFFu);
+            if (due_hi) row_hi = (int)(cnt >> 16);
         }
         if (imp_lo) col_lo = c;
         if (imp_hi) col_hi = c - 1;
-        pend_lo = imp_lo;
-        pend_hi = imp_hi;
+        pend = changed;
         best = nb;
         ++c;
+        ++tt;
+        if (CHAIN) { chain = quiet && tt >= 2 * G; skipq = false; }
     };
 
+    // ---- chained quiet step. After a verified quiet step every F handed down is dead and every E of the warp
+    // is dead, and a quiet step keeps both so: the next step needs neither the F shuffle nor the pre-vote, and on
+    // interior columns neither the border reset nor the range masks. The step is speculative like the quiet path
+    // of `step`: nothing is committed unless the whole warp stayed at or below gap_open; otherwise the caller
+    // redoes it with `step` from the untouched Ho. E[] is not read here and is rewritten (any dead value is as
+    // good as another, see above) by the caller when the chain ends, so its registers are free inside a chain.
+    uint32_t rb2 = 0u;  // inside a chain: window byte of column c + 1 (rb_next holds column c)
+    auto qstep = [&](uint32_t (&Ho)[R], uint32_t (&Hn)[R]) -> bool {
+        uint32_t rH = __shfl_up_sync(0xffffffffu, Hout, 1, G);
+        if (lig == 0) rH = cBB;
+        const uint32_t Hin = prmt(rH, Hout, 0x5432u);
+        const uint32_t Rnew = prmt(Rsel, rb_next, 0x3204u);
+        const uint32_t Rs = Rnew + 0x4400u;
+        uint32_t diag = Hdiag_top;
+        uint32_t cm = cBB;
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const uint32_t s = prmt(Q[k], QB[PROF ? k : 0], Rs);
+            const uint32_t h = __viaddmax_s16x2(diag, s, cBB);
+            diag = Ho[k];
+            Hn[k] = h;
+            if (k & 1) cm = __vimax3_s16x2(cm, Hn[k - 1], h);
+        }
+        const uint32_t thr = (R & 1) ? __vimax3_s16x2(cm, Hn[R - 1], cGOBB) : __vmaxs2(cm, cGOBB);
+        if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
+#ifdef CUSW_STEP_STATS
+        {
+            const bool okq = __all_sync(0xffffffffu, thr == cGOBB);
+            if ((threadIdx.x & 31) == 0) atomicAdd((unsigned long long*)(sc.pool_dev + 512) + (okq ? 3 : 4), 1ull);
+        }
+#endif
+        if (!__all_sync(0xffffffffu, thr == cGOBB)) return false;
+        Hdiag_top = Hin;
+        rb_next = rb2;  // loaded a whole step ago
+        rb2 = (uint32_t)rptr[c + 2];
+        Rsel = Rnew;
+        Hout = Hn[R - 1];
+        const uint32_t nb = __vmaxs2(best, cm);
+        const uint32_t changed = nb ^ best;
+        if ((changed | pend) != 0u) {  // rare on quiet columns: an improvement now or a row search owed
+            const bool imp_lo = (changed & 0xFFFFu) != 0u, imp_hi = (changed >> 16) != 0u;
+            const bool due_lo = (pend & 0xFFFFu) != 0u && !imp_lo, due_hi = (pend >> 16) != 0u && !imp_hi;
+            if (due_lo || due_hi) {
+                const uint32_t cnt = first_row_of(Ho, best, cBB);
+                if (due_lo) row_lo = (int)(cnt & 0xFFFFu);
+                if (due_hi) row_hi = (int)(cnt >> 16);
+            }
+            if (imp_lo) col_lo = c;
+            if (imp_hi) col_hi = c - 1;
+            pend = changed;
+            best = nb;
+        }
+        ++c;
+        ++tt;
+        return true;
+    };
+    if (CHAIN) {
+        while (tt < t_end_warp) {
+            if (chain) {
+                bool odd = false;
+#ifdef CUSW_STEP_STATS
+                if ((threadIdx.x & 31) == 0 && tt + 2 < t_hi) atomicAdd((unsigned long long*)(sc.pool_dev + 512) + 5, 1ull);
+#endif
+                if (tt + 2 < t_hi) rb2 = (uint32_t)rptr[c + 1];
+                while (tt + 2 < t_hi) {  // both steps of the pair are interior
+#ifdef CUSW_NO_SKIPQ
+                    if (!qstep(HA, HB)) break;
+                    if (!qstep(HB, HA)) { odd = true; break; }
+#else
+                    if (!qstep(HA, HB)) { skipq = true; break; }
+                    if (!qstep(HB, HA)) { skipq = true; odd = true; break; }
+#endif
+                }
+                if (odd) {  // the state after an odd number of steps lives in HB: realign the ping-pong
+#pragma unroll
+                    for (int k = 0; k < R; k++) HA[k] = HB[k];
+                }
+                chain = false;
+#pragma unroll
+                for (int k = 0; k < R; k++) E[k] = 0u;
+                Emax = 0u;
+            }
+            // (a realigned chain makes the step count odd: the extra step at the end only sees pad columns)
+            step(HA, HB);
+            step(HB, HA);
+        }
+    } else
     for (int t = 0; t < t_end_warp; t += 2) {
         step(HA, HB);
         step(HB, HA);
@@ -742,10 +845,10 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         }
     }
 
-    if (pend_lo || pend_hi) {  // the last step wrote HA
+    if (pend != 0u) {  // the last step wrote HA
         const uint32_t cnt = first_row_of(HA, best, cBB);
-        if (pend_lo) row_lo = (int)(cnt & 0xFFFFu);
-        if (pend_hi) row_hi = (int)(cnt >> 16);
+        if ((pend & 0xFFFFu) != 0u) row_lo = (int)(cnt & 0xFFFFu);
+        if ((pend >> 16) != 0u) row_hi = (int)(cnt >> 16);
     }
 
     // ---- fold this strip's virtual lanes into the running key: max score, then min column, then min row
