@@ -351,7 +351,7 @@ def main():
                 "bound": "int32_alu", "kernel": "sw_score_kernel<G=%d,R=%d,REV=false,PROF=true> (forward score pass, query-profile flavour)" % al.variant_for(Q_LEN)[:2],
                 "achieved": achieved_laneops / 1e12, "peak": peak_laneops / 1e12, "unit": "T lane-op/s",
                 "frac": achieved_laneops / peak_laneops,
-                "traffic": 4523.0 * n, "traffic_unit": "bytes per forward launch (dram__bytes_read+write from profiles/ncu_fwd_r01y.md: 226.1 MB per 50 000 pairs = 4523 B/pair; algorithmic q+w = 4300 B/pair)",
+                "traffic": 4511.0 * n, "traffic_unit": "bytes per forward launch (dram__bytes_read+write from profiles/ncu_fwd_r01j.md: 225.6 MB per 50 000 pairs = 4511 B/pair; algorithmic q+w = 4300 B/pair)",
                 "gcups_kernel": fwd_cups / 1e9, "int_ops_per_cell": INT_OPS_PER_CELL, "packing": 2,
                 "peak_source": f"{sms} SMs x 128 lanes x {f_sm / 1e6:.0f} MHz (median SM clock sampled during the run); "
                                "HBM is not the bound: ~3.6 B of input per 1000 cells",

@@ -386,7 +386,8 @@ int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairI
     cudaStream_t st = ss.main;
     int nonempty = 0;
     for (int v = 0; v < 2 * g_nvar; v++) nonempty += h_hist[v] > 0;
-    const bool spread = nonempty > 1;
+    static const bool no_spread = getenv("CUDASW_NO_SPREAD") != nullptr;  // experiment hook: variant launches one after the other
+    const bool spread = nonempty > 1 && !no_spread;
     if (spread) CK(cudaEventRecord(ss.fork_ev, st));
     bool used[kAux] = {};
     int64_t start = 0;

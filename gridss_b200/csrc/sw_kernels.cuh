@@ -592,17 +592,29 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     }
 
     // ---- quiet chains (CHAIN flavours only; see qstep below)
-#ifdef CUSW_NO_CHAIN  // A/B switch for tools/exp_build_run.sh
+#ifndef CUSW_CHAIN_MAXG  // A/B switches for tools/exp_build_run.sh
+#define CUSW_CHAIN_MAXG 32
+#endif
+#ifndef CUSW_CHAIN_GATE
+#define CUSW_CHAIN_GATE 3
+#endif
+#ifdef CUSW_NO_CHAIN
     constexpr bool CHAIN = false;
 #else
-    constexpr bool CHAIN = PROF && !REV && !MULTI;
+    constexpr bool CHAIN = PROF && !REV && !MULTI && G <= CUSW_CHAIN_MAXG;
 #endif
     bool chain = false;  // warp-uniform: the previous step was a verified quiet step
     bool skipq = false;  // warp-uniform: the step about to be redone by `step` is known not to be quiet
     int tt = 0;          // step counter (warp-uniform), c == tt - 2 * lig
     // steps [2G, t_hi) are interior for every lane of the warp: both halves inside [2, w), columns up to c + 2 loadable
     // from a pair of steps that starts at tt + 2 < t_hi
-    const int t_hi = CHAIN ? __reduce_min_sync(0xffffffffu, active ? w : 0) - 1 : 0;
+    // Chains pay when most of the sweep is away from the alignment (measured, profiles/chain_sweep_r01j.txt): they are
+    // switched off for warps whose shortest window is below CUSW_CHAIN_GATE times the rows of a group.
+    int t_hi = 0;
+    if (CHAIN) {
+        const int w_min = __reduce_min_sync(0xffffffffu, active ? w : 0);
+        t_hi = w_min >= CUSW_CHAIN_GATE * S ? w_min - 1 : 0;
+    }
 
     auto step = [&](uint32_t (&Ho)[R], uint32_t (&Hn)[R]) {
         // ---- inputs from the virtual lane above
@@ -736,7 +748,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         best = nb;
         ++c;
         ++tt;
-        if (CHAIN) { chain = quiet && tt >= 2 * G; skipq = false; }
+        if (CHAIN) { chain = quiet && tt >= 2 * G && tt + 2 < t_hi; skipq = false; }
     };
 
     // ---- chained quiet step. After a verified quiet step every F handed down is dead and every E of the warp
@@ -812,14 +824,19 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
                     if (!qstep(HB, HA)) { skipq = true; odd = true; break; }
 #endif
                 }
+#ifdef CUSW_CHAIN_REALIGN
                 if (odd) {  // the state after an odd number of steps lives in HB: realign the ping-pong
 #pragma unroll
                     for (int k = 0; k < R; k++) HA[k] = HB[k];
                 }
+#endif
                 chain = false;
 #pragma unroll
                 for (int k = 0; k < R; k++) E[k] = 0u;
                 Emax = 0u;
+#ifndef CUSW_CHAIN_REALIGN
+                if (odd) { step(HB, HA); continue; }  // a third copy of `step` instead of realigning the ping-pong (measured faster)
+#endif
             }
             // (a realigned chain makes the step count odd: the extra step at the end only sees pad columns)
             step(HA, HB);

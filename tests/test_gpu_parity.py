@@ -490,3 +490,46 @@ def test_dispatcher_thread_batches_concurrent_submitters(oracle, synth):
     a = al.wait(t, 5000)
     assert a is not None and a.getCigar() == "10M"
     al.close()
+
+
+def _low_score_pair(rng, q, w, plants):
+    """Query over {G,T}, window over {A,C}: nothing matches except the planted k-mers, so the whole forward pass
+    runs on quiet steps (every H <= gapOpen when k <= 6) and the end cell comes from the tie-breaks alone."""
+    qs = rng.choice(np.frombuffer(b"GT", dtype=np.uint8), size=q)
+    ws = rng.choice(np.frombuffer(b"AC", dtype=np.uint8), size=w)
+    for k in plants:
+        if k > q or k > w:
+            continue
+        i = int(rng.integers(0, q - k + 1))
+        j = int(rng.integers(0, w - k + 1))
+        ws[j:j + k] = qs[i:i + k]
+    return qs.tobytes(), ws.tobytes()
+
+
+@pytest.mark.parametrize("q", [30, 100, 150, 300, 304, 600, 1000])
+def test_quiet_chain_edges_vs_oracle(aligner, oracle, q):
+    """The chained quiet steps of the forward kernel (sw_kernels.cuh, qstep): windows around the 3 x rows gate, maxima
+    that are found and tie-broken inside chains (scores <= gapOpen), chains broken at either ping-pong parity by
+    planted 7..12-mers, windows of different length in one warp."""
+    rng = np.random.default_rng(900 + q)
+    rows = aligner.variant_for(q)[0] * aligner.variant_for(q)[1] * 2
+    seqs, refs = [], []
+    for w in (3 * rows - 2, 3 * rows - 1, 3 * rows, 3 * rows + 1, 3 * rows + 2, 3 * rows + 3, 3 * rows + 64, 4000, 4001):
+        if w < q:
+            continue
+        for rep in range(24):
+            kind = rep % 4
+            if kind == 0:    # only short plants: everything is decided on quiet steps
+                plants = [int(rng.integers(1, 7)) for _ in range(int(rng.integers(1, 12)))]
+            elif kind == 1:  # equal plants: first column, then smallest row
+                plants = [5] * int(rng.integers(2, 10))
+            elif kind == 2:  # events that break chains, at arbitrary steps
+                plants = [int(rng.integers(7, 13)) for _ in range(int(rng.integers(1, 30)))]
+            else:            # a mix
+                plants = [int(rng.integers(1, 13)) for _ in range(int(rng.integers(1, 40)))]
+            s, r = _low_score_pair(rng, q, w, plants)
+            seqs.append(s)
+            refs.append(r)
+    bad, undef = _compare(aligner, oracle, seqs, refs)
+    assert bad == [], bad[:5]
+    assert undef == 0
