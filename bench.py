@@ -351,12 +351,12 @@ def main():
                 "bound": "int32_alu", "kernel": "sw_score_kernel<G=%d,R=%d,REV=false,PROF=true> (forward score pass, query-profile flavour)" % al.variant_for(Q_LEN)[:2],
                 "achieved": achieved_laneops / 1e12, "peak": peak_laneops / 1e12, "unit": "T lane-op/s",
                 "frac": achieved_laneops / peak_laneops,
-                "traffic": 4511.0 * n, "traffic_unit": "bytes per forward launch (dram__bytes_read+write from profiles/ncu_fwd_r01j.md: 225.6 MB per 50 000 pairs = 4511 B/pair; algorithmic q+w = 4300 B/pair)",
+                "traffic": 4534.0 * n, "traffic_unit": "bytes per forward launch (dram__bytes_read+write from profiles/ncu_fwd_r01k.md: 226.7 MB per 50 000 pairs = 4534 B/pair; algorithmic q+w = 4300 B/pair)",
                 "gcups_kernel": fwd_cups / 1e9, "int_ops_per_cell": INT_OPS_PER_CELL, "packing": 2,
                 "peak_source": f"{sms} SMs x 128 lanes x {f_sm / 1e6:.0f} MHz (median SM clock sampled during the run); "
                                "HBM is not the bound: ~3.6 B of input per 1000 cells",
                 "note": "achieved counts the ALGORITHMIC 12 integer ops per cell (SURVEY.md 8d); the kernel executes fewer: 5 ALU-pipe "
-                        "instructions per packed cell pair, and 2.5 on quiet steps where no gap can be open (exact skip). The DPX/PRMT "
+                        "instructions per packed cell pair, and 2.5 on quiet steps where no gap can be open (exact skip; chained quiet steps also shed most per-step overhead). The DPX/PRMT "
                         "instructions issue at 64 lanes/clk/SM (measured_dpx_issue_peak), half the nominal INT32 rate used as peak.",
                 "measured_dpx_issue_peak_Tlaneops": measured.get("VIADDMNMX.S16x2_Tlaneops"),
                 "measured_cellmix_ceiling_TCUPS": measured.get("cellmix_TCUPS"),

@@ -388,6 +388,11 @@ int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairI
     for (int v = 0; v < 2 * g_nvar; v++) nonempty += h_hist[v] > 0;
     static const bool no_spread = getenv("CUDASW_NO_SPREAD") != nullptr;  // experiment hook: variant launches one after the other
     const bool spread = nonempty > 1 && !no_spread;
+    // Quiet-chain flavour of the forward kernels: faster launch by launch (C2 -11 %, C3's variants -2.5 % serialised),
+    // slower when many different variants share the SMs (C3 with 52 variants side by side: +7.5 %; larger code and
+    // register footprints next to each other, profiles/c3_probe_r01j.txt). CUDASW_CHAIN=0/1 forces either flavour.
+    static const char* chain_env = getenv("CUDASW_CHAIN");
+    const bool chained = chain_env ? atoi(chain_env) != 0 : nonempty <= kAux;
     if (spread) CK(cudaEventRecord(ss.fork_ev, st));
     bool used[kAux] = {};
     int64_t start = 0;
@@ -403,7 +408,7 @@ int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairI
                 s = ss.aux[a];
                 if (!used[a]) { CK(cudaStreamWaitEvent(s, ss.fork_ev, 0)); used[a] = true; }
             }
-            (reverse ? (xr ? V.revx : V.rev) : (xr ? V.fwdx : V.fwd))(order + start, c, io, fwd_c, out_c, sc, spool, s);
+            (reverse ? (xr ? V.revx : V.rev) : (xr ? V.fwdx : chained ? V.fwdc : V.fwd))(order + start, c, io, fwd_c, out_c, sc, spool, s);
             (*launches)++;
         }
         start += c;

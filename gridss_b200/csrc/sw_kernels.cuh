@@ -470,7 +470,9 @@ __device__ __forceinline__ uint32_t first_row_of(const uint32_t (&H)[R], uint32_
 template <int R, bool PROF>
 constexpr int score_min_blocks() { return (PROF ? 5 : 4) * R + 32 <= 128 ? 4 : (PROF ? 5 : 4) * R + 32 <= 168 ? 3 : 2; }
 
-template <int G, int R, bool REV, bool MULTI, bool PROF>
+// CHN: the quiet-chain flavour of the forward pass (see qstep below). Both flavours are built: the host takes the
+// chained one unless many different variants run side by side (cudasw.cu, launch_variants).
+template <int G, int R, bool REV, bool MULTI, bool PROF, bool CHN = false>
 __global__ void __launch_bounds__(128, score_min_blocks<R, PROF>())
 sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4* __restrict__ fwd,
                 int4* __restrict__ out, ScoreConst sc, StripPool sp) {
@@ -592,17 +594,10 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     }
 
     // ---- quiet chains (CHAIN flavours only; see qstep below)
-#ifndef CUSW_CHAIN_MAXG  // A/B switches for tools/exp_build_run.sh
-#define CUSW_CHAIN_MAXG 32
-#endif
-#ifndef CUSW_CHAIN_GATE
+#ifndef CUSW_CHAIN_GATE  // A/B switch for tools/exp_build_run.sh
 #define CUSW_CHAIN_GATE 3
 #endif
-#ifdef CUSW_NO_CHAIN
-    constexpr bool CHAIN = false;
-#else
-    constexpr bool CHAIN = PROF && !REV && !MULTI && G <= CUSW_CHAIN_MAXG;
-#endif
+    constexpr bool CHAIN = CHN && PROF && !REV && !MULTI;
     bool chain = false;  // warp-uniform: the previous step was a verified quiet step
     bool skipq = false;  // warp-uniform: the step about to be redone by `step` is known not to be quiet
     int tt = 0;          // step counter (warp-uniform), c == tt - 2 * lig

@@ -16,6 +16,7 @@ struct Variant {
     bool multi;
     score_launch_fn fwd, rev;    // query-profile flavour (window free of N)
     score_launch_fn fwdx, revx;  // xor-selector flavour (any symbols)
+    score_launch_fn fwdc;        // query-profile forward pass with quiet chains (strip-mined variants: same as fwd)
 };
 
 // defined in score_variants.cu, one per -DSCORE_G

@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--seconds", type=float, default=180.0)
     ap.add_argument("--checker", default="reference", choices=["reference", "model"])
     ap.add_argument("--c4-sample", type=int, default=0, help="instead: parity on the first N pairs of the C4 stream itself (seed 4004)")
+    ap.add_argument("--c5", type=int, default=0, help="instead: parity on the first N pairs of C5 (10 kb contigs vs 20 kb windows, seed 5005)")
     args = ap.parse_args()
     import gridss_b200 as g
     from gridss_b200.aligner import pack
@@ -86,6 +87,27 @@ def main():
         print(json.dumps(tot), flush=True)
         al.close()
         return 1 if tot["mismatches"] or cs_gpu != cs_ref else 0
+    if args.c5 > 0:
+        # the long-contig case takes the reference's 16-bit rerun and its band doubling
+        step = 250
+        for first in range(0, args.c5, step):
+            n = min(step, args.c5 - first)
+            sb, so, rb, ro = S.generate(5, n, first=first)
+            res, cig = al.align_blobs(sb, so, rb, ro)
+            m = check(sb, so, rb, ro, threads=cores)
+            bad, undef, bad_first = compare(res, cig, m)
+            tot["pairs"] += n
+            tot["cells"] += float((np.diff(so).astype(np.float64) * np.diff(ro)).sum())
+            tot["mismatches"] += bad
+            tot["undefined_in_reference"] += undef
+            if bad and len(examples) < 5:
+                examples.append({"source": "C5", "pair": first + bad_first})
+        tot["by_source"] = {"C5 stream, seed 5005, pairs [0, %d)" % args.c5: {"pairs": tot["pairs"], "mismatches": tot["mismatches"]}}
+        tot["checker"] = ("libsswjni.so as shipped by the reference" if use_ref else "oracle/ssw_model.c") + f", {cores} host threads"
+        tot["examples"] = examples
+        print(json.dumps(tot), flush=True)
+        al.close()
+        return 1 if tot["mismatches"] else 0
     t_end = time.time() + args.seconds
     rnd = 0
     while time.time() < t_end:

@@ -11,7 +11,7 @@ timeout 600 python bench.py > $O/bench_$TAG.json 2> $O/bench_$TAG.err; echo "ben
 tail -c 600 $O/bench_$TAG.err
 timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$TAG.json 2>> $O/bench_$TAG.err; echo "ref exit $?"
 timeout 600 python tools/bench_configs.py 1:10000 1:400000 2:1000000 3:1000000 4:1000000 5:1000 > $O/configs_$TAG.txt 2>&1; echo "configs exit $?"
-timeout 200 python tests/fuzz_gpu.py --seconds 60 > $O/fuzz_$TAG.json 2> $O/fuzz_$TAG.err; echo "fuzz exit $?"
+CUDASW_CHAIN=1 timeout 200 python tests/fuzz_gpu.py --seconds 60 > $O/fuzz_$TAG.json 2> $O/fuzz_$TAG.err; echo "fuzz exit $?"
 for p in int_peak; do
   [ -x tools/$p ] && timeout 120 tools/$p > $O/${p}_$TAG.txt 2>&1
 done
