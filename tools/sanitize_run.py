@@ -12,7 +12,7 @@ al = g.CudaAligner()
 for kind in ("mutated", "with_n", "indel_heavy", "tiny", "q_gt_w", "zero", "tandem"):
     seqs, refs = S.adversarial(kind, 150, seed=3, qmax=260, wmax=700)
     al.align_batch(seqs, refs)
-for cfg, n in ((1, 300), (3, 120), (5, 2)):
+for cfg, n in ((1, 300), (2, 200), (3, 120), (5, 2)):  # uniform batches (C1, C2) take the quiet-chain flavour; CUDASW_CHAIN=1 forces it everywhere
     sb, so, rb, ro = S.generate(cfg, n)
     al.align_blobs(sb, so, rb, ro)
 # wide-band traceback paths
