@@ -158,7 +158,13 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (gridss_b200 has no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
+    saved_stdout = -1
     if world > 1:
+        # stdout carries exactly one JSON line: whatever native libraries print there meanwhile (NCCL's
+        # "NCCL version ..." banner at the first collective) is sent to stderr until the line is due
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     S.build()
     n = args.pairs
@@ -417,6 +423,9 @@ def main():
                                             "sample": f"first {kb} breakpoints ({len(prs)} aligner calls), {cores} host threads, aligner time only "
                                                       "(window strings prepared outside the timed region)",
                                             "gpu_results_identical_on_sample": bool(same_h)}
+        if saved_stdout >= 0:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
