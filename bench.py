@@ -82,6 +82,27 @@ class ClockSampler(threading.Thread):
                 "power_w_max": max(pw) if pw else None, "reasons": sorted(reasons), "samples": len(self.samples)}
 
 
+def bind_to_gpu_numa_node(torch, local):
+    """One process per GPU: run this rank's host threads (and first-touch its pinned staging buffers) on the NUMA node
+    the GPU hangs off, so that H2D copies do not cross the socket interconnect. Best effort; returns the node or None."""
+    try:
+        p = torch.cuda.get_device_properties(local)
+        dev = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        base = "/sys/bus/pci/devices/" + dev
+        node = int(open(base + "/numa_node").read())
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if node < 0 or len(cpus) < 2:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 def reference_arm(steps: int, warmup: int, n_gpus: int, budget_s: float = 150.0):
     """The reference's own CPU implementation of the path on this box's host cores."""
     from oracle import oracle as O
@@ -168,6 +189,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     S.build()
     n = args.pairs
+    numa = bind_to_gpu_numa_node(torch, local) if world > 1 and not os.environ.get("CUDASW_NO_NUMA_BIND") else None
     al = g.CudaAligner(1, -4, -4, 6, 1, device=local)
 
     # ---- inputs: this rank's shard of the counter-based C2 stream, in pinned host memory
@@ -340,7 +362,7 @@ def main():
             "warmup": warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "s16x2", "data": "synthetic",
             "config": {"workload": WORKLOAD, "arithmetic": "packed int16 (s16x2) score passes, int32 traceback", "pairs_per_gpu_per_step": n, "query_len": Q_LEN, "window_len": W_LEN,
-                       "sharding": f"pair-partition x{world}, no collective", "l2": "inputs (4.3 GB/step/GPU) exceed the 126 MB L2; no flush needed",
+                       "sharding": f"pair-partition x{world}, no collective" + (f", ranks bound to their GPU's NUMA node" if numa is not None else ""), "l2": "inputs (4.3 GB/step/GPU) exceed the 126 MB L2; no flush needed",
                        "bit_exact_checked": "tests/test_gpu_parity.py; bench asserts e2e == resident results"},
             "gcups": total_cells / (dev_ms / 1e3) / 1e9,
             "wall_ms_per_step": wall_ms / args.steps,
