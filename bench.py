@@ -7,8 +7,10 @@ synthetic 300-bp breakend contigs vs 4 kb windows, 1M pairs per GPU, SURVEY.md ย
 
   value : whole-job alignments/s with the raw ASCII inputs already resident in HBM
           (cudasw_align_batch_device), device-timed with CUDA events on the library's stream.
-  e2e   : the same through the reference-facing C-ABI call with HOST (pinned) buffers
-          (cudasw_align_batch): H2D of every pair and D2H of every result inside the timed region.
+  e2e   : the same through the reference-facing C-ABI call with HOST (pinned) buffers holding the
+          shim's packed layout (cudasw_align_batch_packed: 2 bits per base + N mask, 3/8 of the ASCII
+          bytes): H2D of every pair and D2H of every result inside the timed region. `e2e_ascii` is the
+          same with raw ASCII host blobs (cudasw_align_batch), `e2e_windows` with windows named.
   roofline : the forward score-pass kernel against the INT32 issue peak (SURVEY.md ยง8d).
   cpu_baseline : the reference's own shipped libsswjni.so on this box's host cores (bounded sample).
 
@@ -159,6 +161,8 @@ def main():
     ap.add_argument("--no-windows", action="store_true", help="skip the device-resident-reference e2e variant")
     ap.add_argument("--no-homology", action="store_true", help="skip the caller-level line (cudasw_breakpoint_homology)")
     ap.add_argument("--homology-breakpoints", type=int, default=500000)
+    ap.add_argument("--no-worst-case", action="store_true", help="skip the zero-quiet-steps forward line")
+    ap.add_argument("--worst-case-pairs", type=int, default=1_000_000)
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
 
@@ -257,21 +261,51 @@ def main():
     checksum = int(res["score"].astype(np.int64).sum()) ^ int(res["ref_begin"].astype(np.int64).sum() << 8)
     statuses_ok = bool((res["status"] == 0).all())
 
-    # ---- e2e: host buffers through the C ABI (H2D + D2H inside)
+    from gridss_b200.shard import pair_digests
+    dig_resident = pair_digests(res, cig, first_ordinal=first)  # ordinal, status, coordinates and every CIGAR word
+
+    # ---- e2e (headline): the shim's packed host layout through cudasw_align_batch_packed (H2D + D2H inside).
+    # Packing is the caller's job (it replaces the array copies + clean() the reference does per pair while it builds
+    # the call, SswJniAligner.java:42-44); its host rate is reported beside the line, outside the timed region.
+    w2q, wnq = g.packed_words(int(so[-1]))
+    w2w, wnw = g.packed_words(int(ro[-1]))
+    pin_q2, pin_qn, pin_w2, pin_wn = PinnedBuffer(4 * w2q), PinnedBuffer(4 * wnq), PinnedBuffer(4 * w2w), PinnedBuffer(4 * wnw)
+    q2, qn, w2, wn = (b.array.view(np.uint32) for b in (pin_q2, pin_qn, pin_w2, pin_wn))
+    pack_threads = max(1, min(16, (os.cpu_count() or 1) // max(1, world)))
+    t0 = time.perf_counter()
+    _, _, amb_q = g.pack_bases(sb, q2, qn, n=int(so[-1]), threads=pack_threads)
+    _, _, amb_w = g.pack_bases(rb, w2, wn, n=int(ro[-1]), threads=pack_threads)
+    host_pack_s = time.perf_counter() - t0
+
+    def step_packed():
+        r, c = al.align_blobs_packed(q2, qn if amb_q else None, so_p, w2, wn if amb_w else None, ro_p, res=res_p, cig=cig_p)
+        return al.stats(), r, c
+
     for _ in range(2):
-        step_host()
+        step_packed()
     barrier()
     t0 = time.perf_counter()
     e2e_dev_ms = 0.0
     e2e_phase = {}
     for _ in range(args.steps):
-        st_h, r_h = step_host()
+        st_h, r_h, c_h = step_packed()
         e2e_dev_ms += st_h["ms_total"]
         for k in ("ms_h2d", "ms_pack", "ms_forward", "ms_reverse", "ms_traceback", "ms_d2h"):
             e2e_phase[k] = e2e_phase.get(k, 0.0) + st_h[k] / args.steps
     barrier()
     e2e_wall_ms = (time.perf_counter() - t0) * 1e3
-    assert np.array_equal(r_h["score"], res["score"]) and np.array_equal(r_h["ref_begin"], res["ref_begin"])
+    assert np.array_equal(pair_digests(r_h, c_h, first_ordinal=first), dig_resident), "packed e2e results differ from the resident path"
+
+    # ---- e2e_ascii: raw ASCII host blobs through cudasw_align_batch (round 1's e2e)
+    for _ in range(2):
+        step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        st_a, r_a = step_host()
+    barrier()
+    ascii_wall_ms = (time.perf_counter() - t0) * 1e3
+    assert np.array_equal(pair_digests(r_a, cig_p, first_ordinal=first), dig_resident), "ASCII e2e results differ from the resident path"
 
     # ---- e2e with the windows named instead of shipped: the windows of this shard are loaded once
     # as one device-resident 2-bit "contig"; each step then copies queries + 24-byte descriptors only
@@ -293,11 +327,12 @@ def main():
             st_w = al.stats()
         barrier()
         win_wall_ms = (time.perf_counter() - t0) * 1e3
-        assert np.array_equal(r_w["score"], res["score"]) and np.array_equal(r_w["ref_begin"], res["ref_begin"]) and np.array_equal(r_w["cigar_len"], res["cigar_len"])
-        win_line = {"value": float(n) * args.steps / (win_wall_ms / 1e3), "unit": "alignments/s per GPU", "h2d_bytes_per_step": int(st_w["h2d_bytes"]),
+        assert np.array_equal(pair_digests(r_w, _c, first_ordinal=first), dig_resident), "windows e2e results differ from the resident path"
+        win_line = {"value": None, "unit": "alignments/s", "h2d_bytes_per_step": int(st_w["h2d_bytes"]),
                     "d2h_bytes_per_step": int(st_w["d2h_bytes"]), "ms_per_step_wall": win_wall_ms / args.steps,
                     "note": "cudasw_align_batch_windows: windows gathered on the GPU from the device-resident 2-bit reference "
-                            "(loaded once, outside the timed region); results asserted identical to the shipped-bytes path"}
+                            "(loaded once, outside the timed region); result digests (coordinates + every CIGAR word) asserted identical to the resident path; "
+                            "value = all ranks' pairs / max-over-ranks time"}
 
     # ---- caller level: BreakpointHomology.calculate for a list of breakpoints through
     # cudasw_breakpoint_homology, with GRIDSS's defaults (gridss.properties:88-89: 300 bp breakend, 10 bp margin). The
@@ -333,16 +368,47 @@ def main():
                     "pairs_per_step": int(st_b["pairs"]), "ms_per_step_wall": hom_wall_ms / args.steps, "ms_per_step_device": st_b["ms_total"],
                     "h2d_bytes_per_step": int(st_b["h2d_bytes"]), "d2h_bytes_per_step": int(st_b["d2h_bytes"]),
                     "gcups": float(st_b["cells"]) * args.steps / (hom_wall_ms / 1e3) / 1e9,
+                    "forward_tcups": float(st_b["cells"]) / (st_b["ms_forward"] / 1e3) / 1e12 if st_b["ms_forward"] else None,
                     "phases_ms": {k: round(float(st_b[k]), 3) for k in ("ms_h2d", "ms_pack", "ms_forward", "ms_reverse", "ms_traceback", "ms_d2h")},
                     "maxBreakendLength": 300, "margin": 10, "with_homology": int(((hl > 0) | (hr > 0)).sum()),
                     "note": "cudasw_breakpoint_homology: segment arithmetic on the host, queries and windows gathered from the "
                             "device-resident 2-bit reference, score passes only (clip lengths are all the caller reads)"}
 
     # ---- max over ranks
-    t = torch.tensor([dev_ms, wall_ms, e2e_wall_ms, fwd_ms, e2e_dev_ms], dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, wall_ms, e2e_wall_ms, fwd_ms, e2e_dev_ms, ascii_wall_ms, win_wall_ms if win_line is not None else 0.0,
+                      hom_wall_ms if hom_line is not None else 0.0], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, wall_ms, e2e_wall_ms, fwd_ms, e2e_dev_ms = [float(x) for x in t.tolist()]
+    dev_ms, wall_ms, e2e_wall_ms, fwd_ms, e2e_dev_ms, ascii_wall_ms, win_wall_ms, hom_wall_max_ms = [float(x) for x in t.tolist()]
+    if win_line is not None:
+        win_line["value"] = float(n) * world * args.steps / (win_wall_ms / 1e3)
+        win_line["ms_per_step_wall"] = win_wall_ms / args.steps
+    if hom_line is not None:
+        hom_line["value_all_gpus"] = float(args.homology_breakpoints) * world * args.steps / (hom_wall_max_ms / 1e3)
+
+    # ---- worst case for the forward kernel: query == a slice of a window of the same length, so the alignment (and the
+    # E/F values it leaves behind) crosses every step of the sweep and no step is quiet. Rank 0 only; explains `value`.
+    worst = None
+    if rank == 0 and not args.no_worst_case:
+        nw = args.worst_case_pairs
+        rng_w = np.random.default_rng(9009)
+        wq = np.frombuffer(b"ACGT", dtype=np.uint8)[rng_w.integers(0, 4, size=(nw, Q_LEN), dtype=np.uint8)]
+        wso = np.arange(nw + 1, dtype=np.int64) * Q_LEN
+        d_wq = torch.from_numpy(wq.reshape(-1)).cuda()
+        d_wso = torch.from_numpy(wso).cuda()
+        for _ in range(3):
+            al.align_blobs_device(d_wq.data_ptr(), d_wso.data_ptr(), d_wq.data_ptr(), d_wso.data_ptr(), wso, wso)
+        wms = wfwd = 0.0
+        for _ in range(args.steps):
+            r_wc, _ = al.align_blobs_device(d_wq.data_ptr(), d_wso.data_ptr(), d_wq.data_ptr(), d_wso.data_ptr(), wso, wso)
+            st_wc = al.stats()
+            wms += st_wc["ms_total"]
+            wfwd += st_wc["ms_forward"]
+        assert (r_wc["score"] == Q_LEN).all() and (r_wc["cigar_len"] == 1).all()
+        worst = {"workload": f"{nw} pairs, query == window ({Q_LEN} x {Q_LEN}, identical sequences): zero quiet steps",
+                 "alignments_per_s": nw * args.steps / (wms / 1e3), "forward_tcups": nw * float(Q_LEN) * Q_LEN * args.steps / (wfwd / 1e3) / 1e12,
+                 "ms_per_step": wms / args.steps, "ms_forward": wfwd / args.steps, "inputs": "resident in HBM"}
+        del d_wq, d_wso
 
     line = None
     if rank == 0:
@@ -355,43 +421,72 @@ def main():
         fwd_cups = cells_per_step * args.steps / (fwd_ms / 1e3)  # one GPU's kernel (rank max time)
         peak_laneops = sms * 128 * f_sm  # INT32 lane-ops/s at the clock seen during the run
         achieved_laneops = fwd_cups * INT_OPS_PER_CELL / 2.0  # packed s16x2: two cells per lane-op
-        int_peak_file = os.path.join(ROOT, "profiles", "int_peak_r01.json")
-        measured = json.load(open(int_peak_file)) if os.path.exists(int_peak_file) else {}
+        # the integer pipes measured on THIS box in THIS run (tools/int_peak.cu, dependent-free asm streams, < 1 s)
+        measured = {}
+        ip = os.path.join(ROOT, "tools", "int_peak")
+        if os.path.exists(ip):
+            try:
+                env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(local) if "CUDA_VISIBLE_DEVICES" not in os.environ else os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local])
+                measured = json.loads(subprocess.run([ip], capture_output=True, text=True, timeout=120, env=env).stdout.strip().splitlines()[-1])
+            except Exception as e:  # noqa: BLE001
+                measured = {"error": repr(e)}
+        # ALU-pipe instructions the forward kernel executes per packed cell pair: from the committed ncu capture of this
+        # kernel on this workload (profiles/fwd_alu_mix.json, written by tools/profile_summaries.py), NOT from this run
+        mix_file = os.path.join(ROOT, "profiles", "fwd_alu_mix.json")
+        mix = json.load(open(mix_file)) if os.path.exists(mix_file) else {}
+        alu_issue = measured.get("VIADDMNMX.S16x2_Tlaneops")
+        alu_pipe_frac = None
+        if mix.get("alu_lane_ops_per_cell") and alu_issue:
+            alu_pipe_frac = fwd_cups * mix["alu_lane_ops_per_cell"] / (alu_issue * 1e12)
         line = {
             "metric": "alignments/sec", "value": value, "unit": "alignments/s", "n_gpus": world, "steps": args.steps,
             "warmup": warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "s16x2", "data": "synthetic",
             "config": {"workload": WORKLOAD, "arithmetic": "packed int16 (s16x2) score passes, int32 traceback", "pairs_per_gpu_per_step": n, "query_len": Q_LEN, "window_len": W_LEN,
-                       "sharding": f"pair-partition x{world}, no collective" + (f", ranks bound to their GPU's NUMA node" if numa is not None else ""), "l2": "inputs (4.3 GB/step/GPU) exceed the 126 MB L2; no flush needed",
-                       "bit_exact_checked": "tests/test_gpu_parity.py; bench asserts e2e == resident results"},
+                       "sharding": f"pair-partition x{world}, no collective" + (f", ranks bound to their GPU's NUMA node {numa}" if numa is not None else ", no NUMA node exposed for the GPU in sysfs (no binding)" if world > 1 else ""),
+                       "l2": "inputs (4.3 GB/step/GPU) exceed the 126 MB L2; no flush needed",
+                       "bit_exact_checked": "tests/test_gpu_parity.py; bench asserts equal result digests (coordinates + every CIGAR word) across the resident, packed, ASCII and windows paths"},
             "gcups": total_cells / (dev_ms / 1e3) / 1e9,
             "wall_ms_per_step": wall_ms / args.steps,
             "phases_ms": {k: round(v, 3) for k, v in phase.items()},
             "e2e": {"value": float(n) * world * args.steps / (e2e_wall_ms / 1e3), "unit": "alignments/s",
                     "h2d_bytes_per_step": int(st_h["h2d_bytes"]), "d2h_bytes_per_step": int(st_h["d2h_bytes"]),
                     "gcups": total_cells / (e2e_wall_ms / 1e3) / 1e9, "ms_per_step_wall": e2e_wall_ms / args.steps,
-                    "ms_per_step_device": e2e_dev_ms / args.steps, "host_buffers": "pinned (cudasw_host_alloc)",
+                    "ms_per_step_device": e2e_dev_ms / args.steps,
+                    "entry_point": "cudasw_align_batch_packed (2 bits per base + N mask: the shim's pinned-buffer layout)",
+                    "host_buffers": "pinned (cudasw_host_alloc)",
+                    "host_pack": {"seconds": host_pack_s, "threads": pack_threads, "gb_per_s_ascii_in": (int(so[-1]) + int(ro[-1])) / host_pack_s / 1e9,
+                                  "note": "cudasw_pack_bases over this step's 4.3 GB, outside the timed region: it replaces the per-pair array copies + clean() "
+                                          "the reference's wrapper does while building a call (SswJniAligner.java:42-44,71-79)"},
                     "phases_ms": {k: round(v, 3) for k, v in e2e_phase.items()},
                     "pipeline": "H2D in geometric chunks on a copy stream, overlapped with the previous chunk's kernels; ms_h2d = copy time not hidden"},
+            "e2e_ascii": {"value": float(n) * world * args.steps / (ascii_wall_ms / 1e3), "unit": "alignments/s", "h2d_bytes_per_step": int(st_a["h2d_bytes"]),
+                          "d2h_bytes_per_step": int(st_a["d2h_bytes"]), "ms_per_step_wall": ascii_wall_ms / args.steps,
+                          "entry_point": "cudasw_align_batch (raw ASCII host blobs; round 1's e2e)"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {
                 "bound": "int32_alu", "kernel": "sw_score_kernel<G=%d,R=%d,REV=false,PROF=true> (forward score pass, query-profile flavour)" % al.variant_for(Q_LEN)[:2],
                 "achieved": achieved_laneops / 1e12, "peak": peak_laneops / 1e12, "unit": "T lane-op/s",
                 "frac": achieved_laneops / peak_laneops,
-                "traffic": 4534.0 * n, "traffic_unit": "bytes per forward launch (dram__bytes_read+write from profiles/ncu_fwd_r01k.md: 226.7 MB per 50 000 pairs = 4534 B/pair; algorithmic q+w = 4300 B/pair)",
+                "traffic": mix.get("dram_bytes_per_pair", 0) * n if mix.get("dram_bytes_per_pair") else None,
+                "traffic_source": ("%s (dram__bytes_read+write per pair x pairs per launch) - from that committed ncu capture, NOT measured by this run; algorithmic q+w = 4300 B/pair" % mix.get("source")) if mix else None,
                 "gcups_kernel": fwd_cups / 1e9, "int_ops_per_cell": INT_OPS_PER_CELL, "packing": 2,
-                "peak_source": f"{sms} SMs x 128 lanes x {f_sm / 1e6:.0f} MHz (median SM clock sampled during the run); "
-                               "HBM is not the bound: ~3.6 B of input per 1000 cells",
-                "note": "achieved counts the ALGORITHMIC 12 integer ops per cell (SURVEY.md 8d); the kernel executes fewer: 5 ALU-pipe "
-                        "instructions per packed cell pair, and 2.5 on quiet steps where no gap can be open (exact skip; chained quiet steps also shed most per-step overhead). The DPX/PRMT "
-                        "instructions issue at 64 lanes/clk/SM (measured_dpx_issue_peak), half the nominal INT32 rate used as peak.",
-                "measured_dpx_issue_peak_Tlaneops": measured.get("VIADDMNMX.S16x2_Tlaneops"),
+                "peak_source": f"{sms} SMs x 128 lanes x {f_sm / 1e6:.0f} MHz (nominal INT32 lane rate at the median SM clock sampled during the run); "
+                               "measured on this box in this run by tools/int_peak (dependent-free asm streams): see measured_issue_rates_Tlaneops",
+                "measured_issue_rates_Tlaneops": {k.replace("_Tlaneops", ""): v for k, v in measured.items() if k.endswith("_Tlaneops")} or measured,
+                "alu_pipe_frac": alu_pipe_frac,
+                "alu_pipe_frac_how": "ALU-pipe lane-ops the kernel EXECUTES per cell (%s, from %s) x cells/s of this run / the measured VIADDMNMX.S16x2 issue rate; "
+                                     "this is the fraction of the pipe the kernel actually lives on" % (mix.get("alu_lane_ops_per_cell"), mix.get("source")),
+                "note": "frac counts the ALGORITHMIC 12 integer ops per cell of SURVEY.md 8d against the nominal INT32 rate and can exceed 1: one VIADDMNMX does three of "
+                        "those ops, and quiet steps (no gap can be open) skip the E/F updates exactly. alu_pipe_frac is the bounded yardstick.",
                 "measured_cellmix_ceiling_TCUPS": measured.get("cellmix_TCUPS"),
                 "frac_of_measured_cellmix_ceiling": (fwd_cups / 1e12 / measured["cellmix_TCUPS"]) if measured.get("cellmix_TCUPS") else None,
             },
             "result_checksum": checksum, "all_status_ok": statuses_ok,
         }
+        if worst is not None:
+            line["worst_case"] = worst
         peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
         hbm_peak = json.load(open(peaks_file)).get("hbm_gbs") if os.path.exists(peaks_file) else None
         if phase.get("ms_encode"):
@@ -418,11 +513,24 @@ def main():
             t0 = time.perf_counter()
             cpu = run(sb[: so[k]], so[: k + 1], rb[: ro[k]], ro[: k + 1], threads=cores)
             dt = time.perf_counter() - t0
-            same = bool(np.array_equal(cpu.res["score"], res["score"][:k]) and np.array_equal(cpu.res["ref_begin"], res["ref_begin"][:k]))
+            # full result digests on both sides: ordinal, status, coordinates and every CIGAR word
+            same = bool(np.array_equal(pair_digests(cpu.res, cpu.cig, first_ordinal=first), dig_resident[:k]))
             line["cpu_baseline"] = {"value": k / dt, "unit": "alignments/s", "cores": cores, "kind": kind,
                                     "sample": f"first {k} pairs of rank 0's C2 shard, {cores} host threads, "
                                               + ("libsswjni.so as shipped by the reference (-O0 SSE2 build)" if kind == "reference" else "oracle/ssw_model.c -O3"),
-                                    "gcups": k * Q_LEN * W_LEN / dt / 1e9, "gpu_results_identical_on_sample": same}
+                                    "gcups": k * Q_LEN * W_LEN / dt / 1e9, "gpu_results_identical_on_sample": same,
+                                    "identity_check": "pair digests over coordinates and every CIGAR word (gridss_b200.shard.pair_digests)"}
+            if kind == "reference":
+                # the same algorithm compiled -O3 (oracle/ssw_model.c, scalar), so the ratio is not flattered
+                # by the reference's -O0 build flags
+                k3 = int(min(n, max(k0, k // 2)))
+                t0 = time.perf_counter()
+                cpu3 = O.model_align_blobs(sb[: so[k3]], so[: k3 + 1], rb[: ro[k3]], ro[: k3 + 1], threads=cores)
+                dt3 = time.perf_counter() - t0
+                line["cpu_baseline_o3"] = {"value": k3 / dt3, "unit": "alignments/s", "cores": cores, "kind": "port",
+                                           "sample": f"first {k3} pairs of the same shard, {cores} host threads, oracle/ssw_model.c (scalar restatement) gcc -O3",
+                                           "gcups": k3 * Q_LEN * W_LEN / dt3 / 1e9,
+                                           "gpu_results_identical_on_sample": bool(np.array_equal(pair_digests(cpu3.res, cpu3.cig, first_ordinal=first), dig_resident[:k3]))}
             if hom_line is not None:
                 # the same breakpoints the way the reference does them: host strings, two libsswjni calls each
                 from oracle import callers_restatement as R

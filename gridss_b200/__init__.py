@@ -20,6 +20,8 @@ from .aligner import (  # noqa: F401
     WINDOW_REVCOMP,
     cigar_string,
     load_library,
+    pack_bases,
+    packed_words,
 )
 from .callers import (  # noqa: F401
     BreakendSummary,
@@ -52,4 +54,6 @@ __all__ = [
     "WINDOW_REVCOMP",
     "cigar_string",
     "load_library",
+    "pack_bases",
+    "packed_words",
 ]

@@ -89,6 +89,9 @@ ABI = [
     ("cudasw_create", ctypes.c_int, [ctypes.POINTER(_Scoring), ctypes.c_int, ctypes.POINTER(_vp)]),
     ("cudasw_destroy", None, [_vp]),
     ("cudasw_align_batch", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_align_batch_packed", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
+    ("cudasw_pack_bases", _i64, [_vp, _i64, _i64, _vp, _vp]),
+    ("cudasw_multi_align_batch_packed", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
     ("cudasw_align_batch_device", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
     ("cudasw_reference_load", ctypes.c_int, [_vp, _i32, _vp, _vp]),
     ("cudasw_reference_fetch", ctypes.c_int, [_vp, _vp, _i32, _vp, _i64]),
@@ -155,6 +158,40 @@ def pack(seqs: Sequence[bytes]):
     if blob.size == 0:
         blob = np.zeros(1, dtype=np.uint8)
     return np.ascontiguousarray(blob), off
+
+
+def packed_words(n_bases: int) -> tuple[int, int]:
+    """(two_bit words, nmask words) a packed blob of n_bases needs: whole 32-base groups."""
+    g = (int(n_bases) + 31) // 32
+    return 2 * max(g, 1), max(g, 1)
+
+
+def pack_bases(blob: np.ndarray, two_bit: np.ndarray | None = None, nmask: np.ndarray | None = None, base0: int = 0,
+               n: int | None = None, threads: int = 1):
+    """ASCII bases -> the packed layout of cudasw_align_batch_packed (2 bits per base + N mask), through the library's
+    own host packer cudasw_pack_bases. Returns (two_bit, nmask, n_ambiguous). `threads` > 1 packs disjoint 32-base
+    aligned ranges in parallel (the C call releases the GIL)."""
+    lib = load_library()
+    n = int(len(blob) if n is None else n)
+    w2, wn = packed_words(base0 + n)
+    if two_bit is None:
+        two_bit = np.zeros(w2, dtype=np.uint32)
+    if nmask is None:
+        nmask = np.zeros(wn, dtype=np.uint32)
+    assert two_bit.dtype == np.uint32 and nmask.dtype == np.uint32 and len(two_bit) >= w2 and len(nmask) >= wn
+    if threads <= 1 or n < (1 << 20) or base0 & 31:
+        amb = lib.cudasw_pack_bases(blob.ctypes.data, n, base0, two_bit.ctypes.data, nmask.ctypes.data)
+    else:
+        from concurrent.futures import ThreadPoolExecutor
+        step = ((n + threads - 1) // threads + 31) & ~31
+        cuts = list(range(0, n, step))
+        with ThreadPoolExecutor(max_workers=threads) as ex:
+            parts = list(ex.map(lambda a: lib.cudasw_pack_bases(blob.ctypes.data + a, min(step, n - a), base0 + a,
+                                                                two_bit.ctypes.data, nmask.ctypes.data), cuts))
+        amb = -1 if any(x < 0 for x in parts) else sum(parts)
+    if amb < 0:
+        raise ValueError("cudasw_pack_bases: bad argument")
+    return two_bit, nmask, int(amb)
 
 
 class Alignment:
@@ -278,6 +315,29 @@ class CudaAligner(Aligner):
             if rc != 0:
                 raise CudaSwError(f"cudasw_align_batch failed ({rc}): {self._err()}")
             return res, cig[: used.value]
+
+    _packed_fn = "cudasw_align_batch_packed"
+
+    def align_blobs_packed(self, seq2, seqN, seq_off, ref2, refN, ref_off, res=None, cig=None):
+        """Host blobs packed by pack_bases (2 bits per base; seqN / refN may be None = no ambiguous base in that blob).
+        Same outputs as align_blobs on the ASCII bytes; 3/8 of the bytes cross PCIe."""
+        n = len(seq_off) - 1
+        res = np.zeros(n, dtype=RESULT_DTYPE) if res is None else res
+        cap = max(64, 24 * n) if cig is None else len(cig)
+        while True:
+            if cig is None or len(cig) < cap:
+                cig = np.zeros(cap, dtype=np.uint32)
+            used = ctypes.c_int64(0)
+            rc = getattr(self._lib, self._packed_fn)(
+                self._h, n, seq2.ctypes.data, None if seqN is None else seqN.ctypes.data, seq_off.ctypes.data,
+                ref2.ctypes.data, None if refN is None else refN.ctypes.data, ref_off.ctypes.data,
+                res.ctypes.data, cig.ctypes.data, cap, ctypes.byref(used))
+            if rc == CUDASW_ENOMEM and used.value > cap:
+                cap = int(used.value) + 16
+                continue
+            if rc != 0:
+                raise CudaSwError(f"{self._packed_fn} failed ({rc}): {self._err()}")
+            return res, (cig[: used.value] if self._packed_fn == "cudasw_align_batch_packed" else cig)
 
     def align_blobs_device(self, d_seq, d_seq_off, d_ref, d_ref_off, h_seq_off, h_ref_off, res=None, cig=None):
         """Inputs already resident in device memory (raw device pointers as ints)."""
@@ -530,6 +590,9 @@ class MultiGpuAligner(Aligner):
         assert win.dtype == WINDOW_DTYPE
         return self._call(self._lib.cudasw_multi_align_batch_windows, "cudasw_multi_align_batch_windows", len(seq_off) - 1,
                           (seq_blob.ctypes.data, seq_off.ctypes.data, win.ctypes.data, win_off.ctypes.data), res, cig)
+
+    _packed_fn = "cudasw_multi_align_batch_packed"
+    align_blobs_packed = CudaAligner.align_blobs_packed  # same marshalling; the CIGAR blob is not compact here
 
     _homology_fn = "cudasw_multi_breakpoint_homology"
     breakpoint_homology = CudaAligner.breakpoint_homology   # same marshalling, the multi-GPU entry point

@@ -16,6 +16,7 @@
 #include <condition_variable>
 #include <atomic>
 #include <mutex>
+#include <shared_mutex>
 #include <thread>
 #include <unordered_set>
 #include <string>
@@ -79,6 +80,11 @@ struct QuerySegs {
     int w_stride;
 };
 
+// Host inputs packed as 2 bits per base + an optional N mask (cudasw_align_batch_packed); NULL masks = no N anywhere.
+struct PackedIn {
+    const uint32_t *seq2, *seqN, *ref2, *refN;
+};
+
 // pinned host staging that grows on demand (cudasw_breakpoint_homology)
 template <typename T>
 struct PinBuf {
@@ -128,6 +134,9 @@ struct cudasw {
 
     // staged raw inputs (host API) and encoded copies
     DevBuf<uint8_t> raw_seq, raw_ref, enc_seq, enc_ref;
+    DevBuf<uint32_t> pk_seq2, pk_seqN, pk_ref2, pk_refN;  // packed host inputs as copied (cudasw_align_batch_packed)
+    int64_t pk_word0_q = 0, pk_word0_w = 0;               // first 16-base word of the batch held in pk_* (even)
+    bool pk_has_qn = false, pk_has_wn = false;
     DevBuf<int64_t> seq_off, ref_off;
     DevBuf<uint32_t> keys, keys_alt;
     DevBuf<int> vals, vals_alt, retry_a, retry_b;
@@ -179,21 +188,24 @@ struct cudasw {
     int64_t disp_max_pairs = 0, disp_delay_us = 0;
     std::chrono::steady_clock::time_point first_pending;
 
-    void set_error(const std::string& s) { error = s; }
+    std::mutex err_mu;           // guards `error` (written by whichever thread fails, read by cudasw_last_error)
+    std::shared_mutex ref_mu;    // the loaded reference (contig_off, ref2bit, refN): shared by batches, exclusive for a (re)load
+    void set_error(const std::string& s) { std::lock_guard<std::mutex> l(err_mu); error = s; }
+    void set_error_locked(const std::string& s) { set_error(s); }
     int pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so, const uint8_t* d_ref,
                    const int64_t* d_ro, int64_t q_lo, int64_t q_hi, int64_t w_lo, int64_t w_hi, bool gather,
-                   uint64_t* launches_out, bool qgather = false, int q_stride = 0, int w_stride = 0);
+                   uint64_t* launches_out, bool qgather = false, int q_stride = 0, int w_stride = 0, bool packed = false);
     int forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* d_so, const int64_t* d_ro, uint64_t* launches_out);
     int post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out,
                    bool ends_only = false);
-    int size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off);
+    int size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off, int64_t rev_first, int64_t rev_cnt);
     float last_post_ms = 0.f;
     int run(int64_t n, const uint8_t* d_seq, const int64_t* d_seq_off, const uint8_t* d_ref,
             const int64_t* d_ref_off, int64_t total_q, int64_t total_w, cudasw_result* out,
             uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used, bool inputs_on_host,
             const uint8_t* h_seq, const int64_t* h_seq_off, const uint8_t* h_ref,
             const int64_t* h_ref_off, const WindowSeg* h_segs = nullptr, const int64_t* h_seg_off = nullptr,
-            const QuerySegs* qsegs = nullptr, bool ends_only = false);
+            const QuerySegs* qsegs = nullptr, bool ends_only = false, const PackedIn* packed = nullptr);
 };
 
 static uint32_t pack2(int v) { return ((uint32_t)v & 0xFFFFu) | (((uint32_t)v & 0xFFFFu) << 16); }
@@ -207,7 +219,11 @@ extern "C" int cudasw_device_count(void) {
 extern "C" const char* cudasw_version(void) { return "cudasw 0.1 (sm_100a)"; }
 
 extern "C" const char* cudasw_last_error(cudasw_t* h) {
-    return h ? h->error.c_str() : g_create_error.c_str();
+    if (!h) return g_create_error.c_str();
+    // a copy per calling thread: the handle's string may be rewritten by another thread's batch at any time
+    thread_local std::string copy;
+    { std::lock_guard<std::mutex> l(h->err_mu); copy = h->error; }
+    return copy.c_str();
 }
 
 extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out) {
@@ -330,7 +346,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
         int64_t used = 0;
         int rc = cudasw_align_batch(h, 1, a, off, a, off, &r, cg, 4, &used);
         if (rc != CUDASW_OK || r.status != 0 || r.score != sc.match || r.cigar_len != 1 || cg[0] != (1u << 4)) {
-            std::string m = "self-test failed: " + h->error;
+            std::string m = std::string("self-test failed: ") + cudasw_last_error(h);
             cudasw_destroy(h);
             g_create_error = m;
             return CUDASW_ECUDA;
@@ -348,6 +364,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     h->raw_seq.release(); h->raw_ref.release(); h->enc_seq.release(); h->enc_ref.release();
+    h->pk_seq2.release(); h->pk_seqN.release(); h->pk_ref2.release(); h->pk_refN.release();
     h->seq_off.release(); h->ref_off.release(); h->keys.release(); h->keys_alt.release();
     h->vals.release(); h->vals_alt.release(); h->retry_a.release(); h->retry_b.release();
     h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
@@ -431,7 +448,8 @@ int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairI
 // never overlap each other (both are host-synchronised), so they share d_hist, h_hist and the sort workspace.
 int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so,
                        const uint8_t* d_ref, const int64_t* d_ro, int64_t q_lo, int64_t q_hi,
-                       int64_t w_lo, int64_t w_hi, bool gather, uint64_t* launches_out, bool qgather, int q_stride, int w_stride) {
+                       int64_t w_lo, int64_t w_hi, bool gather, uint64_t* launches_out, bool qgather, int q_stride, int w_stride,
+                       bool packed) {
     cudaStream_t st = pack_stream;
     uint64_t launches = 0;
     const int64_t n = cnt;
@@ -439,12 +457,22 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     CK(cudaEventRecord(chunk_ev[ci].pack0, st));
     {
         const int64_t tq = q_hi - q_lo, tw = w_hi - w_lo;
+        if (packed) {
+            // 2 bit + N mask words -> the encoded byte layout, 16 bases per thread
+            int64_t thr = (tq + 15) / 16 + 1;
+            int blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
+            if (tq > 0) { unpack_kernel<<<std::max(blocks, 1), 256, 0, st>>>(pk_seq2.p, pk_has_qn ? pk_seqN.p : nullptr, pk_word0_q, q_lo, q_hi, enc_seq.p, 0u, nullptr); launches++; }
+            thr = (tw + 15) / 16 + 1;
+            blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
+            if (tw > 0) { unpack_kernel<<<std::max(blocks, 1), 256, 0, st>>>(pk_ref2.p, pk_has_wn ? pk_refN.p : nullptr, pk_word0_w, w_lo, w_hi, enc_ref.p, 0x80u, any_n); launches++; }
+        }
         int64_t thr = (tq + 31) / 32;
         int blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
-        if (tq > 0 && !qgather) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u, nullptr); launches++; }
+        if (packed) {}
+        else if (tq > 0 && !qgather) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_seq + q_lo, enc_seq.p + q_lo, tq, 0u, nullptr); launches++; }
         thr = (tw + 31) / 32;
         blocks = (int)std::min<int64_t>((thr + 255) / 256, 148 * 16);
-        if (tw > 0 && !gather) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u, any_n); launches++; }
+        if (tw > 0 && !gather && !packed) { encode_kernel<<<std::max(blocks, 1), 256, 0, st>>>(d_ref + w_lo, enc_ref.p + w_lo, tw, 0x80u, any_n); launches++; }
     }
     PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
     if (qgather) {
@@ -467,7 +495,8 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     }
     if (gather) CK(cudaEventRecord(chunk_ev[ci].enc1, st));
     // 1 byte read + 1 written per base; a gathered window reads 3 bits and writes 1 byte per base
-    stats.encode_bytes += 2ull * (uint64_t)(q_hi - q_lo) + (gather ? (uint64_t)(w_hi - w_lo) * 11ull / 8ull : 2ull * (uint64_t)(w_hi - w_lo));
+    if (packed) stats.encode_bytes += ((uint64_t)(q_hi - q_lo) + (uint64_t)(w_hi - w_lo)) * 5ull / 4ull + (pk_has_qn ? (uint64_t)(q_hi - q_lo) / 8 : 0) + (pk_has_wn ? (uint64_t)(w_hi - w_lo) / 8 : 0);
+    else stats.encode_bytes += 2ull * (uint64_t)(q_hi - q_lo) + (gather ? (uint64_t)(w_hi - w_lo) * 11ull / 8ull : 2ull * (uint64_t)(w_hi - w_lo));
     launches++;
     seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
         (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first);
@@ -708,24 +737,29 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
 }
 
 // Boundary rows of the strip-mined score variants (queries above the tallest single-strip variant): two rows of one
-// 32-bit word per window column and pair. Sized exactly for the chunk, so the kernels' bump allocation cannot fail.
-int cudasw::size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off) {
-    bool any = false;
-    for (int v = 0; v < g_nvar; v++)
-        if (g_var[v].multi && (h_hist[v] > 0 || h_hist[g_nvar + v] > 0)) any = true;
-    if (!any) return CUDASW_OK;
+// 32-bit word per window column and pair. The forward buffer is sized for the chunk [first, first + cnt) whose forward
+// pass is about to be queued; the reverse buffer for `rev_first`/`rev_cnt`, the range ONE post_chunk call walks (the whole
+// batch unless CUDASW_POST_PER_CHUNK is set), so the kernels' bump allocation cannot run out.
+int cudasw::size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off,
+                               int64_t rev_first, int64_t rev_cnt) {
+    if (!g_var[g_nvar - 1].multi) return CUDASW_OK;
     const int64_t single_rows = vt.n_single > 0 ? vt.rows[vt.n_single - 1] : 0;
-    unsigned long long need = 0;
-    for (int64_t i = first; i < first + cnt; i++) {
-        const int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
-        if (q > single_rows && w > 0) need += ((((unsigned long long)w * 4ull + 15ull) & ~15ull) * 2ull);
-    }
-    if (need > strip_fwd.cap || need > strip_rev.cap) {
+    auto need_of = [&](int64_t a, int64_t c) {
+        unsigned long long need = 0;
+        for (int64_t i = a; i < a + c; i++) {
+            const int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
+            if (q > single_rows && w > 0) need += ((((unsigned long long)w * 4ull + 15ull) & ~15ull) * 2ull);
+        }
+        return need;
+    };
+    const unsigned long long need_f = need_of(first, cnt);
+    const unsigned long long need_r = rev_cnt > 0 ? need_of(rev_first, rev_cnt) : 0;
+    if (need_f > strip_fwd.cap || need_r > strip_rev.cap) {
         // the buffers may still be in use by the chunk before: let it finish before they are replaced
         CK(cudaStreamSynchronize(stream));
         CK(cudaStreamSynchronize(post_set.main));
-        CK(strip_fwd.ensure((size_t)need + 256));
-        CK(strip_rev.ensure((size_t)need + 256));
+        if (need_f > strip_fwd.cap) CK(strip_fwd.ensure((size_t)need_f + 256));
+        if (need_r > strip_rev.cap) CK(strip_rev.ensure((size_t)need_r + 256));
     }
     return CUDASW_OK;
 }
@@ -735,12 +769,13 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
                 int64_t total_w, cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap,
                 int64_t* cigar_used, bool inputs_on_host, const uint8_t* h_seq,
                 const int64_t* h_seq_off, const uint8_t* h_ref, const int64_t* h_ref_off,
-                const WindowSeg* h_segs, const int64_t* h_seg_off, const QuerySegs* qsegs, bool ends_only) {
+                const WindowSeg* h_segs, const int64_t* h_seg_off, const QuerySegs* qsegs, bool ends_only,
+                const PackedIn* packed) {
     std::lock_guard<std::mutex> lock(mu);
     const bool gather = h_segs != nullptr;
     const bool qgather = qsegs != nullptr;
     const int q_stride = qsegs ? qsegs->stride : 0, w_stride = qsegs ? qsegs->w_stride : 0;
-    error.clear();
+    set_error("");
     stats = cudasw_stats{};
     if (cigar_used) *cigar_used = 0;
     if (n < 0 || n > 0x7fffff00ll) { set_error("n_pairs out of range"); return CUDASW_EINVAL; }
@@ -863,9 +898,20 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     const uint8_t* d_ref = d_ref_in;
     const int64_t* d_so = d_seq_off_in;
     const int64_t* d_ro = d_ref_off_in;
+    if (packed) {
+        // packed host inputs: words [word0, ...) of each blob; word0 = the batch's first base rounded down to 32 bases
+        pk_word0_q = (h_seq_off[0] >> 5) << 1;
+        pk_word0_w = (h_ref_off[0] >> 5) << 1;
+        pk_has_qn = packed->seqN != nullptr;
+        pk_has_wn = packed->refN != nullptr;
+        CK(pk_seq2.ensure((size_t)(((total_q + 31) >> 5) * 2 - pk_word0_q) + 4));
+        CK(pk_ref2.ensure((size_t)(((total_w + 31) >> 5) * 2 - pk_word0_w) + 4));
+        if (pk_has_qn) CK(pk_seqN.ensure((size_t)(((total_q + 31) >> 5) - (pk_word0_q >> 1)) + 4));
+        if (pk_has_wn) CK(pk_refN.ensure((size_t)(((total_w + 31) >> 5) - (pk_word0_w >> 1)) + 4));
+    }
     if (inputs_on_host) {
-        if (!qgather) CK(raw_seq.ensure((size_t)total_q + 16));
-        if (!gather) CK(raw_ref.ensure((size_t)total_w + 16));
+        if (!qgather && !packed) CK(raw_seq.ensure((size_t)total_q + 16));
+        if (!gather && !packed) CK(raw_ref.ensure((size_t)total_w + 16));
         CK(seq_off.ensure(n + 1));
         CK(ref_off.ensure(n + 1));
         CK(cudaEventRecord(ev[7], st));
@@ -892,7 +938,27 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
             if (nsegs > 0) CK(cudaMemcpyAsync(d_qsegs.p, qsegs->segs, (size_t)nsegs * sizeof(WindowSeg), cudaMemcpyHostToDevice, copy_stream));
             if (qsegs->lit_bytes > 0) CK(cudaMemcpyAsync(d_lit.p, qsegs->lit, (size_t)qsegs->lit_bytes, cudaMemcpyHostToDevice, copy_stream));
         }
-        for (size_t i = 0; i < chunks.size(); i++) {
+        uint64_t packed_bytes = 0;
+        for (size_t i = 0; packed && i < chunks.size(); i++) {
+            const Chunk& c = chunks[i];
+            // whole 32-base groups (two 2-bit words + one mask word) covering the chunk's bases; neighbouring chunks may
+            // copy the same boundary group twice
+            auto up = [&](DevBuf<uint32_t>& d2, DevBuf<uint32_t>& dN, const uint32_t* h2, const uint32_t* hN, int64_t word0, int64_t lo, int64_t hi) -> cudaError_t {
+                if (hi <= lo) return cudaSuccess;
+                const int64_t g0 = lo >> 5, g1 = (hi + 31) >> 5;  // groups of 32 bases
+                cudaError_t e = cudaMemcpyAsync(d2.p + (2 * g0 - word0), h2 + 2 * g0, (size_t)(g1 - g0) * 8, cudaMemcpyHostToDevice, copy_stream);
+                packed_bytes += (uint64_t)(g1 - g0) * 8;
+                if (e == cudaSuccess && hN) {
+                    e = cudaMemcpyAsync(dN.p + (g0 - (word0 >> 1)), hN + g0, (size_t)(g1 - g0) * 4, cudaMemcpyHostToDevice, copy_stream);
+                    packed_bytes += (uint64_t)(g1 - g0) * 4;
+                }
+                return e;
+            };
+            CK(up(pk_seq2, pk_seqN, packed->seq2, packed->seqN, pk_word0_q, c.q_lo, c.q_hi));
+            CK(up(pk_ref2, pk_refN, packed->ref2, packed->refN, pk_word0_w, c.w_lo, c.w_hi));
+            CK(cudaEventRecord(h2d_done[i], copy_stream));
+        }
+        for (size_t i = 0; !packed && i < chunks.size(); i++) {
             const Chunk& c = chunks[i];
             if (c.q_hi > c.q_lo && !qgather) CK(cudaMemcpyAsync(raw_seq.p + c.q_lo, h_seq + c.q_lo, (size_t)(c.q_hi - c.q_lo), cudaMemcpyHostToDevice, copy_stream));
             if (c.w_hi > c.w_lo && !gather) CK(cudaMemcpyAsync(raw_ref.p + c.w_lo, h_ref + c.w_lo, (size_t)(c.w_hi - c.w_lo), cudaMemcpyHostToDevice, copy_stream));
@@ -902,6 +968,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         stats.h2d_bytes = (qgather ? (q_stride ? 0 : (uint64_t)(n + 1) * 8) + (uint64_t)n_qsegs * sizeof(WindowSeg) + (uint64_t)qsegs->lit_bytes
                                    : (uint64_t)total_q) + (uint64_t)(n + 1) * 16 +
                           (gather ? (w_stride ? 0 : (uint64_t)(n + 1) * 8) + (uint64_t)n_wsegs * sizeof(WindowSeg) : (uint64_t)total_w);
+        if (packed) stats.h2d_bytes = packed_bytes + (uint64_t)(n + 1) * 16;
     }
 
     // ---- the chunk pipeline: pack(i) | forward(i) | post(i-1), see pack_chunk
@@ -914,8 +981,9 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     for (size_t i = 0; i < chunks.size(); i++) {
         const Chunk& c = chunks[i];
         if (inputs_on_host) CK(cudaStreamWaitEvent(pack_stream, h2d_done[i], 0));
-        int rc = pack_chunk(i, c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, gather, &launches, qgather, q_stride, w_stride);
-        if (rc == CUDASW_OK) rc = size_strip_buffers(c.first, c.cnt, h_seq_off, h_ref_off);
+        int rc = pack_chunk(i, c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, gather, &launches, qgather, q_stride, w_stride, packed != nullptr);
+        // reverse-pass strips: per chunk when post runs per chunk, else once for the whole batch (sized with the first chunk)
+        if (rc == CUDASW_OK) rc = size_strip_buffers(c.first, c.cnt, h_seq_off, h_ref_off, post_per_chunk ? c.first : 0, post_per_chunk ? c.cnt : (i == 0 ? n : 0));
         if (rc == CUDASW_OK) rc = forward_chunk(i, c.first, c.cnt, d_so, d_ro, &launches);
         if (rc == CUDASW_OK && serial) rc = cudaStreamSynchronize(st) == cudaSuccess ? CUDASW_OK : CUDASW_ECUDA;
         if (rc == CUDASW_OK && post_per_chunk && i > 0) rc = post_chunk(i - 1, chunks[i - 1].first, chunks[i - 1].cnt, d_so, d_ro, cigar_cap, &launches, ends_only);
@@ -983,8 +1051,8 @@ extern "C" int cudasw_align_batch(cudasw_t* h, int64_t n, const uint8_t* seq_blo
                                   const int64_t* ref_off, cudasw_result* out, uint32_t* cigar_blob,
                                   int64_t cigar_cap, int64_t* cigar_used) {
     if (!h) return CUDASW_EINVAL;
-    if (n > 0 && (!seq_blob || !seq_off || !ref_blob || !ref_off)) { h->error = "null input"; return CUDASW_EINVAL; }
-    if (n > 0 && (seq_off[0] != 0 || ref_off[0] != 0)) { h->error = "offsets must start at 0"; return CUDASW_EINVAL; }
+    if (n > 0 && (!seq_blob || !seq_off || !ref_blob || !ref_off)) { h->set_error("null input"); return CUDASW_EINVAL; }
+    if (n > 0 && (seq_off[0] != 0 || ref_off[0] != 0)) { h->set_error("offsets must start at 0"); return CUDASW_EINVAL; }
     int64_t tq = n > 0 ? seq_off[n] : 0, tw = n > 0 ? ref_off[n] : 0;
     return h->run(n, nullptr, nullptr, nullptr, nullptr, tq, tw, out, cigar_blob, cigar_cap, cigar_used, true,
                   seq_blob, seq_off, ref_blob, ref_off);
@@ -997,7 +1065,7 @@ extern "C" int cudasw_align_batch_device(cudasw_t* h, int64_t n, const uint8_t* 
                                          uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used) {
     if (!h) return CUDASW_EINVAL;
     if (n > 0 && (!d_seq_blob || !d_seq_off || !d_ref_blob || !d_ref_off || !h_seq_off || !h_ref_off)) {
-        h->error = "null input";
+        h->set_error("null input");
         return CUDASW_EINVAL;
     }
     int64_t tq = n > 0 ? h_seq_off[n] : 0, tw = n > 0 ? h_ref_off[n] : 0;
@@ -1005,14 +1073,81 @@ extern "C" int cudasw_align_batch_device(cudasw_t* h, int64_t n, const uint8_t* 
                   false, nullptr, h_seq_off, nullptr, h_ref_off);
 }
 
+// ---- packed host inputs (north_star (1): "packs 2-bit or byte sequences ... into pinned host buffers")
+// Host-side packer for the shim: bases [base0, base0 + n) of a blob from ASCII. A/C/G/T in either case -> 0..3; every
+// other byte is what clean() (SswJniAligner.java:71-79) turns into N: stored as 0 with its mask bit set. The words that
+// hold the range keep their bits below base0 and lose everything from base0 + n up, so a blob can be appended to pair
+// by pair without clearing it first. Returns the number of ambiguous bases, or CUDASW_EINVAL.
+extern "C" int64_t cudasw_pack_bases(const uint8_t* ascii, int64_t n, int64_t base0, uint32_t* two_bit, uint32_t* nmask) {
+    if (n < 0 || base0 < 0 || (n > 0 && (!ascii || !two_bit))) return CUDASW_EINVAL;
+    static const struct Lut {
+        uint8_t c[256];
+        Lut() {
+            for (int i = 0; i < 256; i++) c[i] = 4;
+            c['A'] = c['a'] = 0; c['C'] = c['c'] = 1; c['G'] = c['g'] = 2; c['T'] = c['t'] = 3;
+        }
+    } lut;
+    int64_t amb = 0;
+    int64_t b = base0;
+    const int64_t end = base0 + n;
+    const uint8_t* src = ascii;
+    // head: up to the next 32-base boundary, bit by bit into the partly filled words
+    if (b < end && (b & 31)) {
+        const int64_t stop = std::min(end, (b | 31) + 1);
+        uint32_t w0 = two_bit[(b >> 5) * 2], w1 = two_bit[(b >> 5) * 2 + 1], nm = nmask ? nmask[b >> 5] : 0u;
+        const int k0 = (int)(b & 31);
+        // keep the bits below base0, clear the rest
+        if (k0 < 16) { w0 &= (1u << (2 * k0)) - 1u; w1 = 0u; } else w1 &= k0 == 16 ? 0u : (1u << (2 * (k0 - 16))) - 1u;
+        nm &= (1u << k0) - 1u;
+        for (; b < stop; b++) {
+            const uint32_t c = lut.c[*src++];
+            const int k = (int)(b & 31);
+            if (k < 16) w0 |= (c & 3u) << (2 * k); else w1 |= (c & 3u) << (2 * (k - 16));
+            nm |= (c >> 2) << k;
+            amb += c >> 2;
+        }
+        two_bit[((b - 1) >> 5) * 2] = w0; two_bit[((b - 1) >> 5) * 2 + 1] = w1;
+        if (nmask) nmask[(b - 1) >> 5] = nm;
+    }
+    // body + tail: whole groups of 32 bases (the last one zero-padded)
+    while (b < end) {
+        const int cnt = (int)std::min<int64_t>(32, end - b);
+        uint32_t w0 = 0, w1 = 0, nm = 0;
+        for (int k = 0; k < cnt; k++) {
+            const uint32_t c = lut.c[src[k]];
+            if (k < 16) w0 |= (c & 3u) << (2 * k); else w1 |= (c & 3u) << (2 * (k - 16));
+            nm |= (c >> 2) << k;
+        }
+        amb += __builtin_popcount(nm);
+        two_bit[(b >> 5) * 2] = w0; two_bit[(b >> 5) * 2 + 1] = w1;
+        if (nmask) nmask[b >> 5] = nm;
+        src += cnt; b += cnt;
+    }
+    return amb;
+}
+
+extern "C" int cudasw_align_batch_packed(cudasw_t* h, int64_t n, const uint32_t* seq_two_bit, const uint32_t* seq_nmask,
+                                         const int64_t* seq_off, const uint32_t* ref_two_bit, const uint32_t* ref_nmask,
+                                         const int64_t* ref_off, cudasw_result* out, uint32_t* cigar_blob,
+                                         int64_t cigar_cap, int64_t* cigar_used) {
+    if (!h) return CUDASW_EINVAL;
+    if (n > 0 && (!seq_two_bit || !seq_off || !ref_two_bit || !ref_off)) { h->set_error_locked("null input"); return CUDASW_EINVAL; }
+    if (n > 0 && (seq_off[0] < 0 || ref_off[0] < 0)) { h->set_error_locked("offsets must be non-negative"); return CUDASW_EINVAL; }
+    const int64_t tq = n > 0 ? seq_off[n] : 0, tw = n > 0 ? ref_off[n] : 0;
+    const PackedIn pk{seq_two_bit, seq_nmask, ref_two_bit, ref_nmask};
+    return h->run(n, nullptr, nullptr, nullptr, nullptr, tq, tw, out, cigar_blob, cigar_cap, cigar_used, true,
+                  nullptr, seq_off, nullptr, ref_off, nullptr, nullptr, nullptr, false, &pk);
+}
+
 // ---- device-resident reference + window descriptors
 static_assert(sizeof(cudasw_window) == sizeof(WindowSeg), "cudasw_window and the device descriptor share one layout");
 
 extern "C" int cudasw_reference_load(cudasw_t* h, int32_t n_contigs, const uint8_t* bases, const int64_t* contig_off) {
     if (!h) return CUDASW_EINVAL;
+    std::unique_lock<std::shared_mutex> ref_lock(h->ref_mu);  // no batch may be reading the reference being replaced
     std::lock_guard<std::mutex> lock(h->mu);
-    h->error.clear();
-    auto set_error = [&](const std::string& m) { h->error = m; };
+    h->set_error("");
+    auto set_error = [&](const std::string& m) { h->set_error(m); };
     if (n_contigs < 0 || (n_contigs > 0 && (!bases || !contig_off))) { h->set_error("null reference"); return CUDASW_EINVAL; }
     if (n_contigs > 0 && contig_off[0] != 0) { h->set_error("contig offsets must start at 0"); return CUDASW_EINVAL; }
     for (int32_t c = 0; c < n_contigs; c++)
@@ -1069,9 +1204,10 @@ extern "C" int cudasw_align_batch_windows(cudasw_t* h, int64_t n, const uint8_t*
                                           const cudasw_window* win, const int64_t* win_off, cudasw_result* out,
                                           uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used) {
     if (!h) return CUDASW_EINVAL;
-    if (n > 0 && (!seq_blob || !seq_off || !win || !win_off)) { h->error = "null input"; return CUDASW_EINVAL; }
-    if (n > 0 && (seq_off[0] != 0 || win_off[0] != 0)) { h->error = "offsets must start at 0"; return CUDASW_EINVAL; }
-    if (h->contig_off.empty()) { h->error = "no reference loaded (cudasw_reference_load)"; return CUDASW_EINVAL; }
+    if (n > 0 && (!seq_blob || !seq_off || !win || !win_off)) { h->set_error("null input"); return CUDASW_EINVAL; }
+    if (n > 0 && (seq_off[0] != 0 || win_off[0] != 0)) { h->set_error("offsets must start at 0"); return CUDASW_EINVAL; }
+    std::shared_lock<std::shared_mutex> ref_lock(h->ref_mu);
+    if (h->contig_off.empty()) { h->set_error("no reference loaded (cudasw_reference_load)"); return CUDASW_EINVAL; }
     std::vector<int64_t> ref_off;
     window_offsets(h, std::max<int64_t>(n, 0), win, win_off, ref_off);
     // a pair with a rejected descriptor has window length 0: the gather skips it and the pair reports EINVAL
@@ -1115,13 +1251,14 @@ extern "C" int cudasw_breakpoint_homology(cudasw_t* h, int64_t n, const cudasw_b
                                           int32_t* local_hom, int32_t* remote_hom) {
     if (!h) return CUDASW_EINVAL;
     if (n < 0 || n > 0x3fffff00ll || (n > 0 && (!bp || !local_hom || !remote_hom)) || max_breakend_length < 0 || margin < 0) {
-        h->error = "bad argument";
+        h->set_error("bad argument");
         return CUDASW_EINVAL;
     }
     if (n == 0) return CUDASW_OK;
-    if (ins_off && (ins_off[0] != 0 || (!ins_blob && ins_off[n] > 0))) { h->error = "bad inserted-sequence blob"; return CUDASW_EINVAL; }
-    if (h->contig_off.empty()) { h->error = "no reference loaded (cudasw_reference_load)"; return CUDASW_EINVAL; }
+    if (ins_off && (ins_off[0] != 0 || (!ins_blob && ins_off[n] > 0))) { h->set_error("bad inserted-sequence blob"); return CUDASW_EINVAL; }
     std::lock_guard<std::mutex> hom_lock(h->hom_mu);
+    std::shared_lock<std::shared_mutex> ref_lock(h->ref_mu);
+    if (h->contig_off.empty()) { h->set_error("no reference loaded (cudasw_reference_load)"); return CUDASW_EINVAL; }
     const std::vector<int64_t>& coff = h->contig_off;
     const int32_t ncontig = (int32_t)coff.size() - 1;
     // Fixed layout, so breakpoints can be planned independently (and in parallel): breakpoint k owns pairs 2k (local
@@ -1130,7 +1267,7 @@ extern "C" int cudasw_breakpoint_homology(cudasw_t* h, int64_t n, const cudasw_b
     // reference skips (empty breakend or window) is a pair of length 0, which the engine rejects without work.
     const int64_t np = 2 * n;
     const int64_t lit_bytes = ins_off ? 2 * ins_off[n] : 0;
-    auto alloc_fail = [&](cudaError_t e) { h->error = std::string("pinned staging: ") + cudaGetErrorString(e); return CUDASW_ENOMEM; };
+    auto alloc_fail = [&](cudaError_t e) { h->set_error(std::string("pinned staging: ") + cudaGetErrorString(e)); return CUDASW_ENOMEM; };
     cudaError_t ce;
     if ((ce = h->hom_qs.ensure((size_t)np * 3)) != cudaSuccess || (ce = h->hom_ws.ensure((size_t)np * 2)) != cudaSuccess ||
         (ce = h->hom_seq_off.ensure((size_t)np + 1)) != cudaSuccess || (ce = h->hom_ref_off.ensure((size_t)np + 1)) != cudaSuccess ||
@@ -1214,7 +1351,7 @@ extern "C" int cudasw_breakpoint_homology(cudasw_t* h, int64_t n, const cudasw_b
         }
     }
     if (bad.load() >= 0) {
-        h->error = "breakpoint " + std::to_string(bad.load()) + ": contig, direction or inserted-sequence offsets out of range";
+        h->set_error("breakpoint " + std::to_string(bad.load()) + ": contig, direction or inserted-sequence offsets out of range");
         return CUDASW_EINVAL;
     }
     seq_off[0] = ref_off[0] = 0;
@@ -1230,7 +1367,7 @@ extern "C" int cudasw_breakpoint_homology(cudasw_t* h, int64_t n, const cudasw_b
         const int64_t q = seq_off[p + 1] - seq_off[p];
         if (q == 0 || ref_off[p + 1] == ref_off[p]) continue;  // a call the reference skips (:75-76, :86)
         const cudasw_result& r = res[p];
-        if (r.status != CUDASW_OK) { h->error = "pair failed with status " + std::to_string(r.status); return r.status; }
+        if (r.status != CUDASW_OK) { h->set_error("pair failed with status " + std::to_string(r.status)); return r.status; }
         const int64_t lead = r.read_begin, tail = q - r.read_end - 1;   // the clips of SswJniAligner.java:52-59
         // homology = bases of the OTHER side's breakend sequence that aligned; nothing if the anchor is clipped
         const int64_t other = n_bs[(size_t)(p ^ 1)];
@@ -1242,9 +1379,10 @@ extern "C" int cudasw_breakpoint_homology(cudasw_t* h, int64_t n, const cudasw_b
 
 extern "C" int cudasw_reference_fetch(cudasw_t* h, const cudasw_window* win, int32_t n_win, uint8_t* out, int64_t out_cap) {
     if (!h || !out || (n_win > 0 && !win) || n_win < 0) return CUDASW_EINVAL;
+    std::shared_lock<std::shared_mutex> ref_lock(h->ref_mu);
     std::lock_guard<std::mutex> lock(h->mu);
-    h->error.clear();
-    auto set_error = [&](const std::string& m) { h->error = m; };
+    h->set_error("");
+    auto set_error = [&](const std::string& m) { h->set_error(m); };
     if (h->contig_off.empty()) { h->set_error("no reference loaded (cudasw_reference_load)"); return CUDASW_EINVAL; }
     const int64_t woff[2] = {0, n_win};
     std::vector<int64_t> ref_off;
@@ -1282,7 +1420,7 @@ extern "C" int cudasw_device_alloc(cudasw_t* h, size_t bytes, void** dptr) {
     if (!h || !dptr) return CUDASW_EINVAL;
     if (cudaSetDevice(h->device) != cudaSuccess) return CUDASW_ECUDA;
     cudaError_t e = cudaMalloc(dptr, bytes ? bytes : 1);
-    if (e != cudaSuccess) { h->error = cudaGetErrorString(e); return CUDASW_ENOMEM; }
+    if (e != cudaSuccess) { h->set_error(cudaGetErrorString(e)); return CUDASW_ENOMEM; }
     return CUDASW_OK;
 }
 extern "C" int cudasw_device_free(cudasw_t* h, void* dptr) {
@@ -1295,7 +1433,7 @@ extern "C" int cudasw_upload(cudasw_t* h, void* dptr, const void* src, size_t by
     cudaSetDevice(h->device);
     cudaError_t e = cudaMemcpyAsync(dptr, src, bytes, cudaMemcpyHostToDevice, h->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-    if (e != cudaSuccess) { h->error = cudaGetErrorString(e); return CUDASW_ECUDA; }
+    if (e != cudaSuccess) { h->set_error(cudaGetErrorString(e)); return CUDASW_ECUDA; }
     return CUDASW_OK;
 }
 extern "C" int cudasw_host_alloc(size_t bytes, void** hptr) {
@@ -1306,6 +1444,7 @@ extern "C" int cudasw_host_free(void* hptr) { return cudaFreeHost(hptr) == cudaS
 
 extern "C" int cudasw_get_stats(cudasw_t* h, cudasw_stats* out) {
     if (!h || !out) return CUDASW_EINVAL;
+    std::lock_guard<std::mutex> lock(h->mu);  // the counters of the last COMPLETED batch (waits for a running one)
     *out = h->stats;
     return CUDASW_OK;
 }
@@ -1374,6 +1513,11 @@ extern "C" int cudasw_flush(cudasw_t* h) {
     if (seq.empty()) seq.push_back(0);
     if (ref.empty()) ref.push_back(0);
     int rc = cudasw_align_batch(h, n, seq.data(), so.data(), ref.data(), ro.data(), res.data(), cig.data(), cap, &used);
+    if (rc == CUDASW_ENOMEM && used > cap) {  // the estimate was short (a pair may need up to ~2q + 2 words): once more with the size asked for
+        cap = used + 16;
+        cig.assign((size_t)cap, 0u);
+        rc = cudasw_align_batch(h, n, seq.data(), so.data(), ref.data(), ro.data(), res.data(), cig.data(), cap, &used);
+    }
     {
         std::lock_guard<std::mutex> lock(h->qmu);
         for (int64_t i = 0; i < n; i++) {

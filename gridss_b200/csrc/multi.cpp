@@ -199,6 +199,32 @@ extern "C" int cudasw_multi_align_batch(cudasw_multi_t* m, int64_t n, const uint
                       });
 }
 
+// Packed host inputs (cudasw_align_batch_packed) over all GPUs: a slice is a view of the same word arrays. Its offsets
+// are rebased to the 32-base group its first base lives in, so each engine copies and expands only its own groups.
+extern "C" int cudasw_multi_align_batch_packed(cudasw_multi_t* m, int64_t n, const uint32_t* seq_two_bit, const uint32_t* seq_nmask,
+                                               const int64_t* seq_off, const uint32_t* ref_two_bit, const uint32_t* ref_nmask,
+                                               const int64_t* ref_off, cudasw_result* out, uint32_t* cigar_blob,
+                                               int64_t cigar_cap, int64_t* cigar_used) {
+    if (!m) return CUDASW_EINVAL;
+    std::lock_guard<std::mutex> lock(m->mu);
+    m->error.clear();
+    if (cigar_used) *cigar_used = 0;
+    if (n < 0) { m->error = "n_pairs out of range"; return CUDASW_EINVAL; }
+    if (n == 0) return CUDASW_OK;
+    if (!seq_two_bit || !seq_off || !ref_two_bit || !ref_off || !out) { m->error = "null input"; return CUDASW_EINVAL; }
+    if (seq_off[0] < 0 || ref_off[0] < 0) { m->error = "offsets must be non-negative"; return CUDASW_EINVAL; }
+    const std::vector<int64_t> cut = balance(n, (int)m->eng.size(), seq_off, ref_off);
+    m->last_first = cut;
+    return run_slices(m, n, seq_off, cut, out, cigar_blob, cigar_cap, cigar_used,
+                      [&](int d, int64_t first, int64_t cnt, cudasw_result* o, uint32_t* cg, int64_t cap, int64_t* used) {
+                          std::vector<int64_t> so((size_t)cnt + 1), ro((size_t)cnt + 1);
+                          const int64_t sg = seq_off[first] >> 5, rg = ref_off[first] >> 5;  // 32-base groups to skip
+                          for (int64_t i = 0; i <= cnt; i++) { so[(size_t)i] = seq_off[first + i] - 32 * sg; ro[(size_t)i] = ref_off[first + i] - 32 * rg; }
+                          return cudasw_align_batch_packed(m->eng[(size_t)d], cnt, seq_two_bit + 2 * sg, seq_nmask ? seq_nmask + sg : nullptr, so.data(),
+                                                           ref_two_bit + 2 * rg, ref_nmask ? ref_nmask + rg : nullptr, ro.data(), o, cg, cap, used);
+                      });
+}
+
 extern "C" int cudasw_multi_reference_load(cudasw_multi_t* m, int32_t n_contigs, const uint8_t* bases, const int64_t* contig_off) {
     if (!m) return CUDASW_EINVAL;
     std::lock_guard<std::mutex> lock(m->mu);

@@ -144,6 +144,48 @@ __global__ void __launch_bounds__(256) ref_pack_kernel(const uint8_t* __restrict
     }
 }
 
+// Packed host inputs (cudasw_align_batch_packed): the same 2 bit + N mask layout as the resident reference, over
+// the linear base coordinate of a whole blob. Expands bases [lo, hi) into the ENCODED byte layout the score
+// kernels read (byte b of `out` = base b), i.e. what encode_kernel makes of the ASCII blob. HBM-bound: 3/8 byte
+// in, 1 byte out per base. `two_bit` / `nmask` are indexed from word `word0` (in 16-base words; even), so a
+// batch that starts deep inside a blob does not need the words before it. One thread per 16 bases.
+__device__ __forceinline__ uint32_t spread4(uint32_t x) {  // 4 two-bit codes in bits 0..7 -> one code per byte
+    uint32_t t = (x | (x << 12)) & 0x000F000Fu;
+    return (t | (t << 6)) & 0x03030303u;
+}
+__global__ void __launch_bounds__(256) unpack_kernel(const uint32_t* __restrict__ two_bit,
+                                                     const uint32_t* __restrict__ nmask, int64_t word0,
+                                                     int64_t lo, int64_t hi, uint8_t* __restrict__ out,
+                                                     uint32_t xor_mask, int* __restrict__ any_n) {
+    const uint32_t xw = xor_mask * 0x01010101u;
+    const int64_t g_lo = lo >> 4, g_hi = (hi + 15) >> 4;
+    bool seen_n = false;
+    for (int64_t g = g_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < g_hi; g += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t w = two_bit[g - word0];
+        uint32_t nm = nmask ? (nmask[(g - word0) >> 1] >> (16 * (int)(g & 1))) & 0xFFFFu : 0u;
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t nb = (((nm >> (4 * k)) & 0xFu) * 0x00204081u) & 0x01010101u;  // N flag of base k in byte k
+            const uint32_t cw = (spread4((w >> (8 * k)) & 0xFFu) & ~(nb * 3u)) | (nb << 2);
+            o[k] = (cw | (cw << 4)) ^ xw;
+        }
+        const int64_t b = g << 4;
+        if (b >= lo && b + 16 <= hi) {
+            *reinterpret_cast<uint4*>(out + b) = make_uint4(o[0], o[1], o[2], o[3]);
+            seen_n |= nm != 0u;
+        } else {  // first / last word of the range: only the bases inside [lo, hi) belong to this batch
+#pragma unroll
+            for (int k = 0; k < 16; k++)
+                if (b + k >= lo && b + k < hi) {
+                    out[b + k] = (uint8_t)(o[k >> 2] >> (8 * (k & 3)));
+                    seen_n |= ((nm >> k) & 1u) != 0u;
+                }
+        }
+    }
+    if (any_n && seen_n) *any_n = 1;
+}
+
 // One window segment: bases [start, end) of contig `contig` (0-based, end exclusive), reverse-complemented when
 // bit 0 of flags is set (BreakpointHomology.java:66-68 builds its windows from such pieces).
 struct WindowSeg {

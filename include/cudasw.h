@@ -95,6 +95,25 @@ int cudasw_align_batch(cudasw_t* h, int64_t n_pairs,
                        cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap,
                        int64_t* cigar_used);
 
+/* ---- Packed host inputs (BASELINE.json north_star (1): the shim "packs 2-bit or byte sequences and reference windows
+ * into pinned host buffers"; SURVEY.md 7 "Feeding the GPU"). Same result as cudasw_align_batch on the ASCII bytes, with
+ * 3 bits instead of 8 per base crossing PCIe. Layout = the reference's own packed genome
+ * (picard/TwoBitBufferedReferenceSequenceFile.java:97-125: 2 bits per base + an "ambiguous" bit set): all bases of a blob
+ * share one linear coordinate b (pair i = bases [off[i], off[i+1])), base b sits in bits 2*(b&15) of two_bit[b>>4]
+ * (A0 C1 G2 T3; an ambiguous base stores 0) and its N flag in bit b&31 of nmask[b>>5]. A NULL nmask says that no base of
+ * that blob is ambiguous. off[0] may be > 0 (a slice of a larger blob; the pointers still name the blob's word 0).
+ * Both word arrays must be readable up to the end of the last 32-base group they touch. */
+int cudasw_align_batch_packed(cudasw_t* h, int64_t n_pairs,
+                              const uint32_t* seq_two_bit, const uint32_t* seq_nmask, const int64_t* seq_off,
+                              const uint32_t* ref_two_bit, const uint32_t* ref_nmask, const int64_t* ref_off,
+                              cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used);
+/* Host-side packer for that layout (what the JNI shim calls while it collects a batch; replaces the two array copies +
+ * clean() of SswJniAligner.java:42-44,71-79): packs ascii[0..n) as bases [base0, base0+n) of the blob. Upper/lower case
+ * A,C,G,T -> 0..3, everything else -> N (mask bit; nmask may be NULL if the caller does not keep one). Words that also
+ * hold earlier bases keep them, later bits of the last word are cleared, so a blob is appended to pair by pair.
+ * Returns the number of ambiguous bases packed (>= 0) or CUDASW_EINVAL. Pure host code; needs no GPU. */
+int64_t cudasw_pack_bases(const uint8_t* ascii, int64_t n, int64_t base0, uint32_t* two_bit, uint32_t* nmask);
+
 /* Same hot path with inputs already resident in device memory (what bench.py's `value` times).
  * d_* are device pointers on the handle's device; out/cigar are HOST buffers. */
 int cudasw_align_batch_device(cudasw_t* h, int64_t n_pairs,
@@ -188,6 +207,10 @@ int cudasw_multi_align_batch(cudasw_multi_t* m, int64_t n_pairs,
                              const uint8_t* seq_blob, const int64_t* seq_off,
                              const uint8_t* ref_blob, const int64_t* ref_off,
                              cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used);
+int cudasw_multi_align_batch_packed(cudasw_multi_t* m, int64_t n_pairs,
+                                    const uint32_t* seq_two_bit, const uint32_t* seq_nmask, const int64_t* seq_off,
+                                    const uint32_t* ref_two_bit, const uint32_t* ref_nmask, const int64_t* ref_off,
+                                    cudasw_result* out, uint32_t* cigar_blob, int64_t cigar_cap, int64_t* cigar_used);
 /* The reference is replicated on every GPU of the handle (one-time, outside any timed path). */
 int cudasw_multi_reference_load(cudasw_multi_t* m, int32_t n_contigs, const uint8_t* bases, const int64_t* contig_off);
 int cudasw_multi_align_batch_windows(cudasw_multi_t* m, int64_t n_pairs, const uint8_t* seq_blob, const int64_t* seq_off,

@@ -95,3 +95,55 @@ def test_jni_glue_type_checks_against_the_header():
     glue = open(src).read()
     for name in re.findall(r"private static native [\w.]+(?:\[\])? (\w+)\(", java):
         assert f"Java_au_edu_wehi_idsv_alignment_CudaAligner_{name}(" in glue, name
+
+
+def _np_pack(blob):
+    """numpy statement of the packed layout of include/cudasw.h (2 bits per base + N mask)."""
+    import numpy as np
+
+    lut = np.full(256, 4, dtype=np.uint32)
+    for k, c in enumerate(b"ACGT"):
+        lut[c] = k
+        lut[c + 32] = k
+    code = lut[blob]
+    n = len(code)
+    pad = (-n) % 32
+    c2 = np.concatenate([code & 3, np.zeros(pad, dtype=np.uint32)]).reshape(-1, 16)
+    nm = np.concatenate([code >> 2, np.zeros(pad, dtype=np.uint32)]).reshape(-1, 32)
+    two = (c2 << (2 * np.arange(16, dtype=np.uint32))).sum(axis=1, dtype=np.uint64).astype(np.uint32)
+    msk = (nm.astype(np.uint64) << np.arange(32, dtype=np.uint64)).sum(axis=1, dtype=np.uint64).astype(np.uint32)
+    return two, msk, int((code >> 2).sum())
+
+
+def test_host_packer_matches_the_declared_layout():
+    """cudasw_pack_bases is pure host code (what the JNI shim calls while collecting a batch): whole blobs, appends at
+    unaligned base offsets, lower case, IUPAC codes and N runs, threads."""
+    import numpy as np
+
+    import gridss_b200 as g
+
+    rng = np.random.default_rng(11)
+    alphabet = np.frombuffer(b"ACGTacgtNnRYKM-*", dtype=np.uint8)
+    for n in (1, 15, 16, 17, 31, 32, 33, 1000, 4099):
+        blob = alphabet[rng.integers(0, len(alphabet), size=n)].copy()
+        two, msk, amb = g.pack_bases(blob)
+        w2, wm, a2 = _np_pack(blob)
+        assert np.array_equal(two[: len(w2)], w2) and np.array_equal(msk[: len(wm)], wm) and amb == a2, n
+    # pair-by-pair appends into dirty buffers == one shot
+    lens = [int(x) for x in rng.integers(1, 90, size=200)]
+    blob = alphabet[rng.integers(0, len(alphabet), size=sum(lens))].copy()
+    w2, wm = g.packed_words(len(blob))
+    two = np.full(w2, 0xFFFFFFFF, dtype=np.uint32)
+    msk = np.full(wm, 0xFFFFFFFF, dtype=np.uint32)
+    at, amb = 0, 0
+    for ln in lens:
+        _, _, a = g.pack_bases(blob[at: at + ln], two, msk, base0=at)
+        amb += a
+        at += ln
+    e2, em, ea = _np_pack(blob)
+    assert np.array_equal(two[: len(e2)], e2) and np.array_equal(msk[: len(em)], em) and amb == ea
+    # threaded == serial
+    big = alphabet[rng.integers(0, 8, size=(1 << 21) + 77)].copy()
+    a = g.pack_bases(big, threads=1)
+    b = g.pack_bases(big, threads=4)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2] == b[2]

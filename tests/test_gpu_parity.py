@@ -533,3 +533,69 @@ def test_quiet_chain_edges_vs_oracle(aligner, oracle, q):
     bad, undef = _compare(aligner, oracle, seqs, refs)
     assert bad == [], bad[:5]
     assert undef == 0
+
+
+# ---- packed host inputs (cudasw_align_batch_packed: 2 bits per base + N mask, north_star (1))
+def _same(res1, cig1, res2, cig2):
+    for f in FIELDS:
+        assert np.array_equal(res1[f], res2[f]), f
+    assert all(_cig(res1, cig1, i) == _cig(res2, cig2, i) for i in range(len(res1)))
+
+
+@pytest.mark.parametrize("cfg,n", [(1, 6000), (2, 3000), (3, 800), (4, 5000)])
+def test_packed_inputs_match_ascii_and_oracle(aligner, oracle, synth, cfg, n):
+    import gridss_b200 as gb
+
+    sb, so, rb, ro = synth.generate(cfg, n)
+    if cfg == 1:  # lower case and IUPAC codes must pack to what clean() makes of them
+        rb = rb.copy()
+        rb[::97] = ord("n")
+        rb[5::211] = ord("R")
+        sb = sb.copy()
+        sb[3::301] = ord("y")
+    bad, undef = _compare_blobs(aligner, oracle, sb, so, rb, ro)
+    assert bad == [] and undef == 0, bad[:5]
+    res1, cig1 = aligner.align_blobs(sb, so, rb, ro)
+    s2, sn, samb = gb.pack_bases(sb, n=int(so[-1]))
+    r2, rn, ramb = gb.pack_bases(rb, n=int(ro[-1]))
+    res2, cig2 = aligner.align_blobs_packed(s2, sn, so, r2, rn, ro)
+    _same(res1, cig1, res2, cig2)
+    st = aligner.stats()
+    assert st["h2d_bytes"] < 0.4 * (int(so[-1]) + int(ro[-1])) + 16 * (n + 1) + 64
+    if samb == 0 and ramb == 0:  # a NULL mask = "no ambiguous base in this blob"
+        res3, cig3 = aligner.align_blobs_packed(s2, None, so, r2, None, ro)
+        _same(res1, cig1, res3, cig3)
+
+
+def test_packed_inputs_chunked_and_sliced(aligner, synth, monkeypatch):
+    """many small chunks (chunk borders inside a 2-bit word) and a batch that starts deep inside a packed blob"""
+    import gridss_b200 as gb
+
+    sb, so, rb, ro = synth.generate(4, 5000)
+    rb = rb.copy()
+    rb[7::1013] = ord("N")
+    s2, sn, _ = gb.pack_bases(sb, n=int(so[-1]))
+    r2, rn, _ = gb.pack_bases(rb, n=int(ro[-1]))
+    res1, cig1 = aligner.align_blobs(sb, so, rb, ro)
+    monkeypatch.setenv("CUDASW_CHUNK_MB", "1")
+    res2, cig2 = aligner.align_blobs_packed(s2, sn, so, r2, rn, ro)
+    monkeypatch.delenv("CUDASW_CHUNK_MB")
+    _same(res1, cig1, res2, cig2)
+    for first, cnt in ((1, 1), (1237, 2000), (4999, 1), (3, 4997)):
+        so_v = np.ascontiguousarray(so[first: first + cnt + 1])
+        ro_v = np.ascontiguousarray(ro[first: first + cnt + 1])
+        res3, cig3 = aligner.align_blobs_packed(s2, sn, so_v, r2, rn, ro_v)
+        _same(res1[first: first + cnt], cig1, res3, cig3)
+
+
+def test_packed_inputs_multi_handle(aligner, synth):
+    import gridss_b200 as gb
+
+    ma = gb.MultiGpuAligner(devices=_visible_devices())
+    sb, so, rb, ro = synth.generate(4, 6000)
+    s2, sn, _ = gb.pack_bases(sb, n=int(so[-1]))
+    r2, rn, _ = gb.pack_bases(rb, n=int(ro[-1]))
+    res1, cig1 = aligner.align_blobs(sb, so, rb, ro)
+    resm, cigm = ma.align_blobs_packed(s2, sn, so, r2, rn, ro)
+    _same(res1, cig1, resm, cigm)
+    ma.close()

@@ -16,12 +16,15 @@ __global__ void __launch_bounds__(256) bench(uint32_t* out, int iters, uint32_t 
         for (int r = 0; r < 8; r++) {
 #pragma unroll
             for (int k = 0; k < 8; k++) {
-                if (OP == 0) x[k] = x[k] + b;                                   // IADD3 / IMAD
-                if (OP == 1) x[k] = (x[k] ^ b) & c;                            // LOP3
+                // asm volatile: the compiler can neither fold the 64 x iters repetitions into one multiply-add (which is what
+                // happened to the plain C++ forms of round 1: 1787 and 9291 "T lane-op/s") nor drop them
+                if (OP == 0) asm volatile("{.reg .u32 t; add.u32 t, %1, %2; add.u32 %0, t, %3;}" : "=r"(x[k]) : "r"(x[k]), "r"(b), "r"(c));  // one IADD3
+                if (OP == 1) asm volatile("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(x[k]) : "r"(x[k]), "r"(b), "r"(c));  // LOP3 (xor3)
                 if (OP == 2) asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(x[k]) : "r"(x[k]), "r"(b), "r"(c));
                 if (OP == 3) x[k] = __vimax3_s16x2(x[k], b, c);
                 if (OP == 4) x[k] = __viaddmax_s16x2(x[k], b, c);
                 if (OP == 5) x[k] = __vmaxs2(x[k], b);
+                if (OP == 6) asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(x[k]) : "r"(x[k]), "r"(b), "r"(c));  // IMAD (FMA pipe)
             }
         }
     }
@@ -67,7 +70,7 @@ int main() {
     cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
     int sms = p.multiProcessorCount;
     uint32_t* out; cudaMalloc(&out, sms * 16 * 256 * 4);
-    const char* names[] = {"IADD", "LOP3", "PRMT", "VIMNMX3.S16x2", "VIADDMNMX.S16x2", "VIMNMX.S16x2"};
+    const char* names[] = {"IADD3", "LOP3", "PRMT", "VIMNMX3.S16x2", "VIADDMNMX.S16x2", "VIMNMX.S16x2", "IMAD"};
     int iters = 4000;
     printf("{\"gpu\": \"%s\", \"sms\": %d, \"clock_khz\": %d", p.name, sms, p.clockRate);
     double ops = (double)sms * 8 * 256 * (double)iters * 64;
@@ -78,6 +81,7 @@ int main() {
     ms = time_ms([&] { bench<3><<<sms * 8, 256>>>(out, iters, 1, 2); }); printf(", \"%s_Tlaneops\": %.2f", names[3], ops / ms / 1e9);
     ms = time_ms([&] { bench<4><<<sms * 8, 256>>>(out, iters, 1, 2); }); printf(", \"%s_Tlaneops\": %.2f", names[4], ops / ms / 1e9);
     ms = time_ms([&] { bench<5><<<sms * 8, 256>>>(out, iters, 1, 2); }); printf(", \"%s_Tlaneops\": %.2f", names[5], ops / ms / 1e9);
+    ms = time_ms([&] { bench<6><<<sms * 8, 256>>>(out, iters, 1, 2); }); printf(", \"%s_Tlaneops\": %.2f", names[6], ops / ms / 1e9);
     // cell mix: 8 packed cells (=16 DP cells) per inner iteration per thread
     int it2 = 20000;
     double cells = (double)sms * 16 * 128 * (double)it2 * 16;
