@@ -589,6 +589,9 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
         // CUDASW_TB_WIDE_CELLS additionally sends every pair above that many banded cells to the warp kernel (0 = all)
         long long wide_cells = -1;
         if (const char* e = getenv("CUDASW_TB_WIDE_CELLS")) wide_cells = atoll(e);
+        // widest starting band the one-thread kernels take (experiment hook; they hold up to kTbThreadBand in registers)
+        int thread_band = kTbThreadBand;
+        if (const char* e = getenv("CUDASW_TB_THREAD_BAND")) thread_band = std::min(std::max(atoi(e), 0), kTbThreadBand);
         CK(cudaMemsetAsync(tb_band.p, 0, (size_t)n * sizeof(int), st));
         TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
         int* retry_count = reinterpret_cast<int*>(d_counters + 2);
@@ -606,7 +609,7 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
             // (and run all their band passes in one kernel: a kernel boundary between passes costs the sum of the slowest
             // pairs of each stage instead of the slowest pair overall)
             const long long wc = wide_cells >= 0 ? wide_cells : (c < 8192 ? 2048 : -1);
-            tb_keys_kernel<<<(c + 255) / 256, 256, 0, st>>>(list, c, fwd_c, rev_c, res_c, wc, c < 8192 ? 1 : 0, tb_band.p, keys.p, vals.p, wide_count,
+            tb_keys_kernel<<<(c + 255) / 256, 256, 0, st>>>(list, c, fwd_c, rev_c, res_c, wc, c < 8192 ? 1 : 0, thread_band, tb_band.p, keys.p, vals.p, wide_count,
                                                             d_hist, d_counters + 7);
             launches++;
             CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, c, 0, 23, st));
@@ -644,7 +647,14 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
                 CK(cudaEventRecord(fork_ev, st));
                 if (nbig > 0) {
                     CK(cudaStreamWaitEvent(aux[0], fork_ev, 0));
-                    sw_traceback_warp_kernel<64><<<(nbig + 3) / 4, 128, 0, aux[0]>>>(vals_alt.p, nbig, nullptr, nullptr, nullptr, io, fwd_c, rev_c, tc,
+                    if (nbig <= 148 * 8 && !getenv("CUDASW_TB_NO_BLOCK")) {  // one wave of the CTA-per-pair kernel
+                        // few pairs: a CTA per pair (a quarter of the per-pair latency of a lone warp); anything wider than
+                        // its register frames is handed to the one-warp kernel's list
+                        sw_traceback_block_kernel<<<std::min(nbig, 148 * 8), 128, 0, aux[0]>>>(vals_alt.p, nbig, esc_big, esc_big_count, io, fwd_c, rev_c,
+                                                                                              tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,
+                                                                                              d_counters + 1, retry_out, retry_count, tb_band.p);
+                    } else
+                    sw_traceback_warp_kernel<32><<<(nbig + 3) / 4, 128, 0, aux[0]>>>(vals_alt.p, nbig, nullptr, nullptr, nullptr, io, fwd_c, rev_c, tc,
                                                                                      pool, res_c, cig.p, (unsigned long long)cigar_cap,
                                                                                      d_counters + 1, retry_out, retry_count, tb_band.p);
                     launches++;
@@ -652,7 +662,7 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
                 }
                 if (nwide > nbig) {
                     CK(cudaStreamWaitEvent(aux[1], fork_ev, 0));
-                    sw_traceback_warp_kernel<16><<<(nwide - nbig + 3) / 4, 128, 0, aux[1]>>>(vals_alt.p + nbig, nwide - nbig, nullptr, esc_big,
+                    sw_traceback_warp_kernel<8><<<(nwide - nbig + 3) / 4, 128, 0, aux[1]>>>(vals_alt.p + nbig, nwide - nbig, nullptr, esc_big,
                                                                                              esc_big_count, io, fwd_c, rev_c, tc, pool, res_c, cig.p,
                                                                                              (unsigned long long)cigar_cap, d_counters + 1, retry_out,
                                                                                              retry_count, tb_band.p);
@@ -701,12 +711,13 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
                 }
 #undef CUSW_TB_LAUNCH
                 // pairs that outgrew the widest frame, then those that outgrew the small warp kernel (from either launch)
-                sw_traceback_warp_kernel<16><<<148 * 4, 128, 0, st>>>(esc_small, 0, esc_small_count, esc_big, esc_big_count, io, fwd_c,
+                sw_traceback_warp_kernel<8><<<148 * 4, 128, 0, st>>>(esc_small, 0, esc_small_count, esc_big, esc_big_count, io, fwd_c,
                                                                       rev_c, tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,
                                                                       d_counters + 1, retry_out, retry_count, tb_band.p);
                 launches++;
                 if (nwide > nbig) CK(cudaStreamWaitEvent(st, join_ev[1], 0));
-                sw_traceback_warp_kernel<64><<<148 * 3, 128, 0, st>>>(esc_big, 0, esc_big_count, nullptr, nullptr, io, fwd_c,
+                if (nbig > 0) CK(cudaStreamWaitEvent(st, join_ev[0], 0));  // the CTA-per-pair kernel may append to esc_big too
+                sw_traceback_warp_kernel<32><<<148 * 3, 128, 0, st>>>(esc_big, 0, esc_big_count, nullptr, nullptr, io, fwd_c,
                                                                       rev_c, tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,
                                                                       d_counters + 1, retry_out, retry_count, tb_band.p);
                 launches++;

@@ -983,7 +983,7 @@ __device__ __forceinline__ int tb_sub(const TbConst& tc, uint32_t qb, uint32_t r
 // Ops come out last-to-first. With `outp` they are written to their final place (needs the total, i.e. a second walk);
 // with `buf` the first kTbOpsBuf of them are kept in walk order, so that the usual short CIGAR needs one walk only.
 constexpr int kTbOpsBuf = 12;
-__device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, int readLen,
+__device__ int tb_walk(const uint8_t* dir, int width_d, int band, int readLen,
                        int refLen, uint32_t* outp, int total_ops, int center = -1, uint32_t* buf = nullptr) {
     int i = readLen - 1, j = refLen - 1;
     int e = 0, l = 0, state = 2;
@@ -1032,7 +1032,7 @@ __device__ int tb_walk(const uint8_t* __restrict__ dir, int width_d, int band, i
 constexpr uint32_t kTbKeyMax = (1u << 22) - 1u;
 constexpr int kTbThreadBand = 16;  // widest band sw_traceback_kernel keeps in registers (33 diagonals)
 constexpr int kTbClasses = 5;      // register frames of half-width 1, 2, 4, 8, 16
-constexpr int kTbWarpSmallD = 16;  // sw_traceback_warp_kernel<16>: bands of up to 32*16 diagonals; <64>: everything else
+constexpr int kTbWarpSmallD = 8;   // sw_traceback_warp_kernel<8>: bands of up to 64*8 diagonals; <32>: everything else
 __host__ __device__ __forceinline__ int tb_class_of(int band) { return band <= 1 ? 0 : band <= 2 ? 1 : band <= 4 ? 2 : band <= 8 ? 3 : 4; }
 __host__ __device__ __forceinline__ int tb_frame_bytes(int cls) { return ((2 << cls) + 1 + 3) & ~3; }  // direction bytes per row
 // Keys: warp-kernel pairs first (by descending cost), then the one-thread pairs grouped by frame class and, inside a
@@ -1040,7 +1040,7 @@ __host__ __device__ __forceinline__ int tb_frame_bytes(int cls) { return ((2 << 
 // cls_count[c] = pairs of class c; est_bytes = scratch the first band pass of every pair will ask for.
 __global__ void tb_keys_kernel(const int* __restrict__ list, int n, const int4* __restrict__ fwd,
                                const int4* __restrict__ rev, const cudasw_result* __restrict__ res,
-                               long long wide_cells, int all_big, const int* __restrict__ tb_band, uint32_t* __restrict__ keys,
+                               long long wide_cells, int all_big, int thread_band, const int* __restrict__ tb_band, uint32_t* __restrict__ keys,
                                int* __restrict__ vals, int* __restrict__ wide_count, int* __restrict__ cls_count,
                                unsigned long long* __restrict__ est_bytes) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1054,17 +1054,17 @@ __global__ void tb_keys_kernel(const int* __restrict__ list, int n, const int4* 
         const int band = max(abs(refLen - readLen) + 1, tb_band[pair]);
         long long cost = (long long)readLen * (2 * band + 1);
         // wide_cells < 0: the default rule; >= 0: additionally every pair above that many cells (0 = all of them)
-        const bool wide = band > kTbThreadBand || (wide_cells >= 0 && cost > wide_cells);
+        const bool wide = band > thread_band || (wide_cells >= 0 && cost > wide_cells);
         if (wide) {
             // warp-kernel pairs: those that start beyond 16 diagonals per lane first (their kernel holds more state
             // per thread), each group by descending cost; wide_count = {all, big}
-            const bool big = all_big || 2 * band + 1 > 32 * kTbWarpSmallD;
+            const bool big = all_big || 2 * band + 1 > 64 * kTbWarpSmallD;
             atomicAdd(wide_count, 1);
             if (big) atomicAdd(wide_count + 1, 1);
             if (cost > (long long)(kTbKeyMax >> 1) - 1) cost = (kTbKeyMax >> 1) - 1;
             key = (big ? 0u : (1u << 21)) | ((kTbKeyMax >> 1) - (uint32_t)cost);
             cls = -1;
-            atomicAdd(est_bytes, (unsigned long long)readLen * (unsigned long long)(2 * band + 1) + 16ull);
+            atomicAdd(est_bytes, (unsigned long long)readLen * (unsigned long long)((2 * band + 1 + 3) & ~3) + 16ull);
         } else {
             cls = tb_class_of(band);
             key = (1u << 22) | ((uint32_t)cls << 19) | (0x7FFFu - (uint32_t)min(readLen, 0x7FFF));
@@ -1283,11 +1283,12 @@ sw_traceback_kernel(const int* __restrict__ list, int n_own, const int* __restri
 #ifdef CUSW_MAIN_TU
 namespace cusw {
 
-// One warp per pair of `list` (the pairs sw_traceback_kernel handed over): banded DP by tb_dp_warp, then lane 0
-// walks the direction matrix and emits the CIGAR exactly like the one-thread kernel.
-// DMAX = 16: passes of up to 16 diagonals per lane (bands up to 255) with a small register footprint; a pair that
-// outgrows it is appended to esc_out, the input of the DMAX = 64 instantiation launched behind it (which also has
-// the memory-backed path for even wider bands).
+// One warp per pair of `list` (the pairs sw_traceback_kernel handed over): banded DP by tb_dp_warp2 (every lane busy in
+// every half-step, tb_warp.cuh), then the warp walks the direction matrix together (tb_walk_warp) and lane 0 emits the
+// CIGAR exactly like the one-thread kernel.
+// DMAX = 8: chunks of up to 8 diagonals (bands up to 255) with a small register footprint; a pair that outgrows it is
+// appended to esc_out, the input of the DMAX = 32 instantiation launched behind it (bands up to 1023 in registers, and
+// the memory-backed path for even wider ones).
 template <int DMAX>
 __global__ void __launch_bounds__(128)
 sw_traceback_warp_kernel(const int* __restrict__ list, int n, const int* __restrict__ n_dev, int* __restrict__ esc_out,
@@ -1300,7 +1301,7 @@ sw_traceback_warp_kernel(const int* __restrict__ list, int n, const int* __restr
     if (n_dev) n = *n_dev;  // the list was filled on the device (pairs escalated by sw_traceback_kernel<16>)
     for (int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; wid < n; wid += (gridDim.x * blockDim.x) >> 5) {
     const int pair = list[wid];
-    const cudasw_result r = res[pair];
+    cudasw_result r = res[pair];
     if (r.status != CUDASW_OK) continue;
     const int q = (int)(io.seq_off[pair + 1] - io.seq_off[pair]);
     const int4 f = fwd[pair];
@@ -1316,19 +1317,21 @@ sw_traceback_warp_kernel(const int* __restrict__ list, int n, const int* __restr
     const uint8_t* dirp = nullptr;
     bool ok = true;
     for (;;) {
-        width_d = 2 * band + 1;
+        const int W = 2 * band + 1;
+        width_d = tb_frame_width(band);
         const long long ndir = (long long)width_d * readLen;
         int status = CUDASW_OK;
-        const int nd = (width_d + 31) / 32;
-        if (DMAX < 64 && nd > DMAX) {  // the wide-state instantiation takes over at this band
+        const int dper = (W + 63) / 64;  // diagonals per chunk
+        if (DMAX < 32 && dper > DMAX) {  // the wide-state instantiation takes over at this band
             if (lane == 0) { tb_band[pair] = band; esc_out[atomicAdd(esc_out_count, 1)] = pair; }
             ok = false;
             break;
         }
-        const unsigned long long row_bytes = nd > 64 ? (((unsigned long long)width_d * 8ull + 15ull) & ~15ull) : 0ull;
+        const unsigned long long row_bytes = dper > 32 ? (((unsigned long long)W * 8ull + 15ull) & ~15ull) : 0ull;
         const unsigned long long need = row_bytes + (((unsigned long long)ndir + 15ull) & ~15ull);
         unsigned long long off = 0;
-        if (ndir * 3 >= (1ll << 31) || need > pool.cap) status = CUDASW_ETOOLARGE;
+        // the reference gives up (exit(1)) when its own direction matrix would not fit an int (ssw.c:580-585)
+        if ((long long)W * readLen * 3 >= (1ll << 31) || need > pool.cap) status = CUDASW_ETOOLARGE;
         else {
             if (lane == 0) off = atomicAdd(pool.used, need);
             off = __shfl_sync(0xffffffffu, off, 0);
@@ -1346,28 +1349,149 @@ sw_traceback_warp_kernel(const int* __restrict__ list, int n, const int* __restr
         uint8_t* dir = pool.base + off + row_bytes;
         dirp = dir;
         int m;
-        if (nd <= 1) m = tb_dp_warp<1>(tc, ref, read, refLen, readLen, band, dir, row, nd);
-        else if (nd <= 2) m = tb_dp_warp<2>(tc, ref, read, refLen, readLen, band, dir, row, nd);
-        else if (nd <= 4) m = tb_dp_warp<4>(tc, ref, read, refLen, readLen, band, dir, row, nd);
-        else if (nd <= 8) m = tb_dp_warp<8>(tc, ref, read, refLen, readLen, band, dir, row, nd);
-        else if (nd <= 16) m = tb_dp_warp<16>(tc, ref, read, refLen, readLen, band, dir, row, nd);
-        else if (DMAX >= 64 && nd <= 32) m = tb_dp_warp<DMAX >= 64 ? 32 : 1>(tc, ref, read, refLen, readLen, band, dir, row, nd);
-        else if (DMAX >= 64 && nd <= 64) m = tb_dp_warp<DMAX >= 64 ? 64 : 1>(tc, ref, read, refLen, readLen, band, dir, row, nd);
-        else m = tb_dp_warp<0>(tc, ref, read, refLen, readLen, band, dir, row, nd);
+        if (dper <= 1) m = tb_dp_warp2<1>(tc, ref, read, refLen, readLen, band, dir);
+        else if (dper <= 2) m = tb_dp_warp2<2>(tc, ref, read, refLen, readLen, band, dir);
+        else if (dper <= 4) m = tb_dp_warp2<4>(tc, ref, read, refLen, readLen, band, dir);
+        else if (dper <= 8) m = tb_dp_warp2<8>(tc, ref, read, refLen, readLen, band, dir);
+        else if (DMAX >= 32 && dper <= 16) m = tb_dp_warp2<DMAX >= 32 ? 16 : 1>(tc, ref, read, refLen, readLen, band, dir);
+        else if (DMAX >= 32 && dper <= 32) m = tb_dp_warp2<DMAX >= 32 ? 32 : 1>(tc, ref, read, refLen, readLen, band, dir);
+        else m = tb_dp_warp_mem(tc, ref, read, refLen, readLen, band, dir, row, (W + 31) / 32);
         mx = max(mx, m);  // the reference never resets its running maximum between band widths
         if (mx >= score) break;
         band *= 2;
     }
-    __syncwarp();  // every lane's direction bytes are visible to lane 0
-    if (ok && lane == 0) {
-        uint32_t opsbuf[kTbOpsBuf];
-        const int nbody = tb_walk(dirp, width_d, band, readLen, refLen, nullptr, 0, -1, opsbuf);
-        if (nbody < 0) res[pair].status = nbody;
-        else tb_emit(pair, q, score, ref_begin, ref_end, read_begin, read_end, nbody, dirp, width_d, band, readLen, refLen,
-                     r, res, cig, cig_cap, cig_used, -1, opsbuf);
+    __syncwarp();  // every lane's direction bytes are visible to the whole warp
+    if (ok) {
+        __shared__ uint32_t ops_sh[4][kTbOpsBuf];
+        uint32_t* opsbuf = ops_sh[threadIdx.x >> 5];
+        const int nbody = tb_walk_warp(dirp, width_d, band, readLen, refLen, nullptr, 0, opsbuf);
+        if (nbody < 0) { if (lane == 0) res[pair].status = nbody; }
+        else {
+            // tb_emit, with the second walk (CIGARs longer than the ops buffer) done by the whole warp
+            const int lead = read_begin != 0, tail = (q - read_end - 1) != 0;
+            const int nops = nbody + lead + tail;
+            unsigned long long coff = 0;
+            if (lane == 0) coff = atomicAdd(cig_used, (unsigned long long)nops);
+            coff = __shfl_sync(0xffffffffu, coff, 0);
+            const bool fits = coff + (unsigned long long)nops <= cig_cap && coff < 0x7fffffffull;
+            uint32_t* o = cig + coff + lead;
+            if (fits && nbody > kTbOpsBuf) tb_walk_warp(dirp, width_d, band, readLen, refLen, o, nbody, nullptr);
+            if (lane == 0) {
+                r.score = score; r.ref_begin = ref_begin; r.ref_end = ref_end; r.read_begin = read_begin; r.read_end = read_end;
+                r.cigar_len = nops; r.cigar_off = (int32_t)coff;
+                if (fits) {
+                    if (lead) cig[coff] = ((uint32_t)read_begin << 4) | CUDASW_CIGAR_S;
+                    if (nbody <= kTbOpsBuf)
+                        for (int k = 0; k < nbody; k++) o[k] = opsbuf[nbody - 1 - k];  // kept by the counting walk, last op first
+                    if (tail) o[nbody] = ((uint32_t)(q - read_end - 1) << 4) | CUDASW_CIGAR_S;
+                } else r.status = CUDASW_ENOMEM;
+                res[pair] = r;
+            }
+        }
     }
     __syncwarp();
     }  // pairs of this warp
+}
+
+// One CTA (4 warps) per pair: the latency-oriented flavour of the kernel above for batches with too few wide pairs to
+// fill the machine with one warp each (BASELINE.json C5: 1000 contigs of 10 kb, where a lone warp needs tens of
+// milliseconds per pair). 256 chunks instead of 64, so a chunk is a quarter as wide and an iteration a quarter as long;
+// the warps hand over through shared memory (tb_dp_warp2<D, 4>). Bands beyond 256*4 diagonals go to esc_out (the
+// one-warp kernel); keeping D <= 4 holds the kernel at 8 CTAs per SM.
+__global__ void __launch_bounds__(128, 8)
+sw_traceback_block_kernel(const int* __restrict__ list, int n, int* __restrict__ esc_out, int* __restrict__ esc_out_count,
+                          PairIO io, const int4* __restrict__ fwd, const int4* __restrict__ rev, TbConst tc, TbPool pool,
+                          cudasw_result* __restrict__ res, uint32_t* __restrict__ cig, unsigned long long cig_cap,
+                          unsigned long long* __restrict__ cig_used, int* __restrict__ retry_list,
+                          int* __restrict__ retry_count, int* __restrict__ tb_band) {
+    __shared__ TbXchg xc;
+    __shared__ unsigned long long off_sh;
+    __shared__ uint32_t ops_sh[kTbOpsBuf];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    for (int wid = blockIdx.x; wid < n; wid += gridDim.x) {
+    const int pair = list[wid];
+    cudasw_result r = res[pair];
+    if (r.status != CUDASW_OK) continue;  // (uniform: every thread reads the same record)
+    const int q = (int)(io.seq_off[pair + 1] - io.seq_off[pair]);
+    const int4 f = fwd[pair];
+    const int4 rv = rev[pair];
+    const int score = f.x;
+    const int ref_end = f.y, read_end = f.z;
+    const int ref_begin = ref_end - rv.y, read_begin = read_end - rv.z;
+    const int refLen = ref_end - ref_begin + 1, readLen = read_end - read_begin + 1;
+    const uint8_t* ref = io.enc_ref + io.ref_off[pair] + ref_begin;
+    const uint8_t* read = io.enc_seq + io.seq_off[pair] + read_begin;
+    int band = max(abs(refLen - readLen) + 1, tb_band[pair]);
+    __syncthreads();  // tb_band[pair] is rewritten below by thread 0
+    int mx = 0, width_d = 0;
+    const uint8_t* dirp = nullptr;
+    bool ok = true;
+    for (;;) {
+        const int W = 2 * band + 1;
+        width_d = tb_frame_width(band);
+        const long long ndir = (long long)width_d * readLen;
+        int status = CUDASW_OK;
+        const int dper = (W + 255) / 256;  // diagonals per chunk
+        if (dper > 4) {  // wider than this kernel keeps in registers (bands above 511)
+            if (threadIdx.x == 0) { tb_band[pair] = band; esc_out[atomicAdd(esc_out_count, 1)] = pair; }
+            ok = false;
+            break;
+        }
+        const unsigned long long need = ((unsigned long long)ndir + 15ull) & ~15ull;
+        if ((long long)W * readLen * 3 >= (1ll << 31) || need > pool.cap) status = CUDASW_ETOOLARGE;  // ssw.c:580-585
+        else {
+            __syncthreads();
+            if (threadIdx.x == 0) off_sh = atomicAdd(pool.used, need);
+            __syncthreads();
+            if (off_sh + need > pool.cap) status = 1;  // scratch exhausted: try again in the next round
+        }
+        if (status != CUDASW_OK) {
+            if (threadIdx.x == 0) {
+                if (status == 1) { tb_band[pair] = band; retry_list[atomicAdd(retry_count, 1)] = pair; }
+                else res[pair].status = status;
+            }
+            ok = false;
+            break;
+        }
+        uint8_t* dir = pool.base + off_sh;
+        dirp = dir;
+        int m;
+        if (dper <= 1) m = tb_dp_warp2<1, 4>(tc, ref, read, refLen, readLen, band, dir, &xc);
+        else if (dper <= 2) m = tb_dp_warp2<2, 4>(tc, ref, read, refLen, readLen, band, dir, &xc);
+        else m = tb_dp_warp2<4, 4>(tc, ref, read, refLen, readLen, band, dir, &xc);
+        mx = max(mx, m);  // the reference never resets its running maximum between band widths
+        if (mx >= score) break;
+        band *= 2;
+    }
+    __syncthreads();  // every warp's direction bytes are visible to warp 0
+    if (ok && wib == 0) {
+        const int nbody = tb_walk_warp(dirp, width_d, band, readLen, refLen, nullptr, 0, ops_sh);
+        if (nbody < 0) { if (lane == 0) res[pair].status = nbody; }
+        else {
+            const int lead = read_begin != 0, tail = (q - read_end - 1) != 0;
+            const int nops = nbody + lead + tail;
+            unsigned long long coff = 0;
+            if (lane == 0) coff = atomicAdd(cig_used, (unsigned long long)nops);
+            coff = __shfl_sync(0xffffffffu, coff, 0);
+            const bool fits = coff + (unsigned long long)nops <= cig_cap && coff < 0x7fffffffull;
+            uint32_t* o = cig + coff + lead;
+            if (fits && nbody > kTbOpsBuf) tb_walk_warp(dirp, width_d, band, readLen, refLen, o, nbody, nullptr);
+            __syncwarp();
+            if (lane == 0) {
+                r.score = score; r.ref_begin = ref_begin; r.ref_end = ref_end; r.read_begin = read_begin; r.read_end = read_end;
+                r.cigar_len = nops; r.cigar_off = (int32_t)coff;
+                if (fits) {
+                    if (lead) cig[coff] = ((uint32_t)read_begin << 4) | CUDASW_CIGAR_S;
+                    if (nbody <= kTbOpsBuf)
+                        for (int k = 0; k < nbody; k++) o[k] = ops_sh[nbody - 1 - k];
+                    if (tail) o[nbody] = ((uint32_t)(q - read_end - 1) << 4) | CUDASW_CIGAR_S;
+                } else r.status = CUDASW_ENOMEM;
+                res[pair] = r;
+            }
+        }
+    }
+    __syncthreads();
+    }  // pairs of this CTA
 }
 
 }  // namespace cusw

@@ -202,8 +202,12 @@ def test_long_queries_strip_mined(aligner, oracle, synth):
     assert bad == [] and undef == 0, bad[:3]
 
 
-def test_c5_long_contigs_vs_oracle(aligner, oracle, synth):
-    sb, so, rb, ro = synth.generate(5, 6)
+@pytest.mark.parametrize("flavour", ["cta_per_pair", "warp_per_pair"])
+def test_c5_long_contigs_vs_oracle(aligner, oracle, synth, flavour, monkeypatch):
+    """BASELINE.json C5 (10 kb contigs vs 20 kb windows: strip-mined score passes, band doubling, long CIGARs), 64 pairs"""
+    if flavour == "warp_per_pair":
+        monkeypatch.setenv("CUDASW_TB_NO_BLOCK", "1")
+    sb, so, rb, ro = synth.generate(5, 64)
     bad, undef = _compare_blobs(aligner, oracle, sb, so, rb, ro)
     assert bad == [] and undef == 0, bad[:3]
 
@@ -224,9 +228,13 @@ def test_chunked_pipeline_matches_oracle(aligner, oracle, synth, monkeypatch):
 
 @pytest.mark.parametrize("kind", ["random", "mutated", "two_letter", "homopolymer", "dinuc", "tandem", "subst_block",
                                   "with_n", "zero", "tiny", "q_gt_w", "indel_heavy"])
-def test_warp_traceback_forced(aligner, oracle, synth, kind, monkeypatch):
-    """every pair through the warp-cooperative traceback kernel (normally only long / wide-band pairs take it)"""
+@pytest.mark.parametrize("flavour", ["cta_per_pair", "warp_per_pair"])
+def test_warp_traceback_forced(aligner, oracle, synth, kind, flavour, monkeypatch):
+    """every pair through the cooperative traceback kernels (normally only long / wide-band pairs take them): the
+    CTA-per-pair kernel small batches get, and the one-warp-per-pair kernels of large batches"""
     monkeypatch.setenv("CUDASW_TB_WIDE_CELLS", "0")
+    if flavour == "warp_per_pair":
+        monkeypatch.setenv("CUDASW_TB_NO_BLOCK", "1")
     for seed, qmax, wmax in ((5, 120, 300), (6, 700, 1500)):
         seqs, refs = synth.adversarial(kind, 800, seed=seed, qmax=qmax, wmax=wmax)
         bad, undef = _compare(aligner, oracle, seqs, refs)
@@ -234,12 +242,16 @@ def test_warp_traceback_forced(aligner, oracle, synth, kind, monkeypatch):
         assert undef == 0
 
 
-def test_warp_traceback_wide_bands(aligner, oracle, monkeypatch):
-    """long indels force band doubling up to the memory-backed state (more than 16 diagonals per lane)"""
+@pytest.mark.parametrize("flavour", ["cta_per_pair", "warp_per_pair"])
+def test_warp_traceback_wide_bands(aligner, oracle, flavour, monkeypatch):
+    """long indels force band doubling through every register frame width, the hand-over from the CTA-per-pair kernel
+    to the one-warp kernel (bands above 511) and the memory-backed state (bands above 1023)"""
     monkeypatch.setenv("CUDASW_TB_WIDE_CELLS", "0")
+    if flavour == "warp_per_pair":
+        monkeypatch.setenv("CUDASW_TB_NO_BLOCK", "1")
     rng = np.random.default_rng(21)
     seqs, refs = [], []
-    for gap in (40, 90, 200, 300, 450, 700):
+    for gap in (40, 90, 200, 300, 450, 700, 1100, 1500):
         for kind in ("del", "ins"):
             a = rng.choice(list(b"ACGT"), size=400).astype(np.uint8).tobytes()
             b = rng.choice(list(b"ACGT"), size=400).astype(np.uint8).tobytes()
