@@ -25,6 +25,7 @@
 
 #define CUSW_MAIN_TU 1  // non-template kernels are emitted in this translation unit only
 #include "sw_kernels.cuh"
+#include "rev_band.cuh"
 #include "variants.h"
 
 using namespace cusw;
@@ -125,6 +126,9 @@ struct cudasw {
     unsigned long long* d_strip = nullptr;  // [0], [1]: bump counters of the strip-mining boundary buffers (forward, reverse); [2], [3]: cells, padded cells
     unsigned long long* h_cells = nullptr;  // pinned copy of d_strip[2..3]
     DevBuf<uint8_t> strip_fwd, strip_rev;
+    DevBuf<uint32_t> rev_ring[2 * kRevVariants];  // banded reverse pass: per-group boundary rings of every (variant, flavour) launch
+    int* d_rev_slots = nullptr;                    // (start, count) per slot of that pass, filled on the device
+    int64_t batch_max_q = 0, batch_max_w = 0;      // longest query / window of the batch being run (host offsets)
     int launch_variants(StreamSet& ss, bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool, uint64_t* launches);
     std::vector<int16_t> var_by_q;  // host copy of variant_of() for the stats
     cudaEvent_t ev[8]{};
@@ -292,6 +296,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     }
     if ((e = cudaMalloc(&h->d_strip, 4 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_rev_slots, 64 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
     if ((e = cudaMallocHost(&h->h_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
@@ -373,6 +378,8 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->d_qsegs.release(); h->d_qseg_off.release(); h->d_lit.release();
     h->hom_qs.release(); h->hom_ws.release(); h->hom_seq_off.release(); h->hom_ref_off.release(); h->hom_lit.release(); h->hom_res.release();
     if (h->d_hist) cudaFree(h->d_hist);
+    if (h->d_rev_slots) cudaFree(h->d_rev_slots);
+    for (auto& r : h->rev_ring) r.release();
     if (h->d_pool) cudaFree(h->d_pool);
     if (h->d_counters) cudaFree(h->d_counters);
     if (h->h_hist) cudaFreeHost(h->h_hist);
@@ -561,6 +568,41 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
     CK(cudaEventRecord(ev[3], st));
 
     // ---- reverse score pass
+    static const bool rev_full = getenv("CUDASW_REV_FULL") != nullptr;  // experiment hook: round 1's full-rectangle kernels
+    if (!rev_full) {
+        // Banded, strip-mined, persistent kernels (rev_band.cuh): binned on the device, job list bounds read from device
+        // memory, so nothing here waits for the host.
+        CK(cudaMemsetAsync(d_hist, 0, 64 * sizeof(int), st));
+        const int few_pairs = n < 4096 ? 1 : 0;
+        rev_band_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, sc.match, sc.B, sc.ge, few_pairs, keys.p, vals.p, d_hist,
+                                                                    reinterpret_cast<int*>(d_counters + 5), wflags_c);
+        launches++;
+        CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 24, st));
+        launches += 3;
+        slot_scan_kernel<<<1, 32, 0, st>>>(d_hist, 2 * kRevVariants + 1, d_rev_slots);
+        launches++;
+        CK(cudaEventRecord(fork_ev, st));
+        for (int s = 0; s < 2 * kRevVariants; s++) {
+            const int v = s % kRevVariants;
+            const bool prof = s < kRevVariants;
+            const int gpb = 128 / rev_variant_lanes(v);
+            // persistent grid: what fits the machine (4 CTAs per SM), fewer for the rare N flavour, never more than the
+            // batch could fill; and no more ring memory than 1 GB per launch
+            const long long half = rev_ring_half(v, batch_max_q, batch_max_w, sc.match, sc.B, sc.ge);
+            long long blocks = std::min<long long>((n + gpb - 1) / gpb, prof ? 148 * 4 : 148);
+            const long long per_block = (long long)gpb * 2 * half * 4;
+            blocks = std::max<long long>(1, std::min<long long>(blocks, ((long long)1 << 30) / std::max<long long>(per_block, 1)));
+            CK(rev_ring[s].ensure((size_t)(blocks * gpb * 2 * half)));
+            cudaStream_t sx = aux[s % kAux];
+            if (s < kAux) CK(cudaStreamWaitEvent(sx, fork_ev, 0));
+            cusw::launch_rev_band(v, prof, (int)blocks, vals_alt.p, d_rev_slots + 2 * s, io, fwd_c, rev_c, sc, rev_ring[s].p, (int)half, sx);
+            launches++;
+        }
+        for (int a = 0; a < kAux; a++) {
+            CK(cudaEventRecord(join_ev[a], aux[a]));
+            CK(cudaStreamWaitEvent(st, join_ev[a], 0));
+        }
+    } else {
     CK(cudaMemsetAsync(d_strip + 1, 0, sizeof(unsigned long long), st));
     CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
     rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, vt, keys.p, vals.p, d_hist,
@@ -571,6 +613,7 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
     CK(cudaMemcpyAsync(h_hist, d_hist, 256 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     { int rc = launch_variants(post_set, true, vals_alt.p, io, fwd_c, rev_c, spool, &launches); if (rc != CUDASW_OK) return rc; }
+    }
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[4], st));
 
@@ -865,6 +908,16 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     }
     int64_t max_cnt = 0;
     for (auto& c : chunks) max_cnt = std::max(max_cnt, c.cnt);
+    {
+        // longest query / window of the batch (sizes the boundary rings of the banded reverse pass)
+        int64_t mq = 0, mw = 0;
+        for (int64_t i = 0; i < n; i++) {
+            mq = std::max(mq, h_seq_off[i + 1] - h_seq_off[i]);
+            mw = std::max(mw, h_ref_off[i + 1] - h_ref_off[i]);
+        }
+        batch_max_q = std::min<int64_t>(std::max<int64_t>(mq, 1), 32767);
+        batch_max_w = std::min<int64_t>(std::max<int64_t>(mw, 1), (1 << 24));
+    }
 
     // ---- capacity
     CK(enc_seq.ensure((size_t)total_q + 16));

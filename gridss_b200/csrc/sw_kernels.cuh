@@ -487,6 +487,21 @@ struct StripPool {
     unsigned long long* used;
 };
 
+// Most gap bases (insertions + deletions, over all gaps) an alignment over `rows` query rows can contain and still
+// score `target`: its matches give at most rows * match, k gaps of L bases in total cost k*go + (L-k)*ge.
+// -1 = unbounded (a gap can grow for free).
+__host__ __device__ __forceinline__ long long max_gap_bases(long long rows, int match, int target, int go, int ge) {
+    const long long budget = rows * match - target;
+    if (budget < 0) return 0;
+    if (go >= ge) {  // cheapest: one gap
+        if (budget < go) return 0;
+        if (ge == 0) return -1;
+        return (budget - go) / ge + 1;
+    }
+    if (go == 0) return -1;  // cheapest: L gaps of one base
+    return budget / go;
+}
+
 // Row (per half) of the first H equal to `target` = number of rows whose running prefix maximum is still below
 // it. A half whose column is out of range may hold values above its target (they are never used): the prefix
 // maximum is clamped so that the packed subtract cannot borrow across halves.
@@ -540,10 +555,9 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             rptr += ro + f.y;
             // An alignment of `target` inside q rows spans at most q + D columns, D = the deletions its
             // score budget can pay for; columns beyond cannot hold the first cell reaching `target`.
-            if (sc.ge > 0) {
-                long long budget = (long long)q * sc.match - target - sc.B;
-                long long dmax = budget >= 0 ? budget / sc.ge + 1 : 0;
-                long long lim = (long long)q + dmax + 1;
+            const long long dmax = max_gap_bases(q, sc.match, target, sc.B, sc.ge);
+            if (dmax >= 0) {
+                const long long lim = (long long)q + dmax + 1;
                 if (lim < w) w = (int)lim;
             }
         } else {

@@ -30,4 +30,8 @@ void variants_g32(std::vector<Variant>&);
 // single-strip variants ascending by rows, then the strip-mined ones; for equal rows the larger R (fewer lanes) wins; CUDASW_VARIANTS="8x19,4x38" restricts
 std::vector<Variant> collect_variants();
 
+// rev_variants.cu: the banded reverse pass (rev_band.cuh), variant v in [0, kRevVariants), persistent grid of `blocks`
+void launch_rev_band(int v, bool prof, int blocks, const int* order, const int* slot, PairIO io, const int4* fwd, int4* out,
+                     ScoreConst sc, uint32_t* ring, int ring_half, cudaStream_t st);
+
 }  // namespace cusw
