@@ -129,7 +129,12 @@ struct cudasw {
     DevBuf<uint32_t> rev_ring[2 * kRevVariants];  // banded reverse pass: per-group boundary rings of every (variant, flavour) launch
     int* d_rev_slots = nullptr;                    // (start, count) per slot of that pass, filled on the device
     int64_t batch_max_q = 0, batch_max_w = 0;      // longest query / window of the batch being run (host offsets)
-    int launch_variants(StreamSet& ss, bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool, uint64_t* launches);
+    int launch_variants(StreamSet& ss, bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c, StripPool spool, uint64_t* launches,
+                        const int* counts, const int* dev_slots, bool maybe_x);
+    std::vector<std::vector<int>> fwd_counts;  // per chunk: pairs per query-length class (variant), counted on the host
+    DevBuf<int> fwd_slots;                     // per chunk: (start, count) of every forward slot, filled on the device
+    DevBuf<uint8_t> cub_tmp_post;              // sort workspace of the post stream (it may run beside a later chunk's pack)
+    bool batch_maybe_n = true;                 // false when the caller's packed inputs carry no N mask for the windows
     std::vector<int16_t> var_by_q;  // host copy of variant_of() for the stats
     cudaEvent_t ev[8]{};
     std::mutex mu;
@@ -198,7 +203,8 @@ struct cudasw {
     void set_error_locked(const std::string& s) { set_error(s); }
     int pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so, const uint8_t* d_ref,
                    const int64_t* d_ro, int64_t q_lo, int64_t q_hi, int64_t w_lo, int64_t w_hi, bool gather,
-                   uint64_t* launches_out, bool qgather = false, int q_stride = 0, int w_stride = 0, bool packed = false);
+                   uint64_t* launches_out, bool qgather, int q_stride, int w_stride, bool packed, const int64_t* h_seq_off,
+                   const int64_t* h_ref_off);
     int forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* d_so, const int64_t* d_ro, uint64_t* launches_out);
     int post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out,
                    bool ends_only = false);
@@ -341,6 +347,9 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
         if (!g_var[i].multi) h->vt.n_single = i + 1;
     }
 
+    h->var_by_q.assign(32768, 0);
+    for (int q = 1; q < 32768; q++) h->var_by_q[(size_t)q] = (int16_t)variant_of(h->vt, q);
+
     // self-test, like AlignerFactory's "A" vs "A" probe (AlignerFactory.java:74-84)
 #ifndef CUSW_EXPERIMENT_NO_SELFTEST
     {
@@ -373,7 +382,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->seq_off.release(); h->ref_off.release(); h->keys.release(); h->keys_alt.release();
     h->vals.release(); h->vals_alt.release(); h->retry_a.release(); h->retry_b.release();
     h->fwd.release(); h->rev.release(); h->res.release(); h->cig.release();
-    h->cub_tmp.release(); h->tb_pool.release(); h->tb_band.release(); h->tb_esc.release(); h->wflags.release(); h->anchor.release();
+    h->cub_tmp.release(); h->cub_tmp_post.release(); h->fwd_slots.release(); h->tb_pool.release(); h->tb_band.release(); h->tb_esc.release(); h->wflags.release(); h->anchor.release();
     h->ref2bit.release(); h->refN.release(); h->d_contig_off.release(); h->d_seg_off.release(); h->d_segs.release();
     h->d_qsegs.release(); h->d_qseg_off.release(); h->d_lit.release();
     h->hom_qs.release(); h->hom_ws.release(); h->hom_seq_off.release(); h->hom_ref_off.release(); h->hom_lit.release(); h->hom_res.release();
@@ -403,13 +412,17 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     delete h;
 }
 
-// Launches the score kernel of every variant that has pairs in h_hist (sorted order in `order`). With several
-// variants the launches are spread over auxiliary streams so that small launches overlap (fork/join by events).
+// Launches the score kernel of every variant that has pairs (sorted order in `order`). With several variants the
+// launches are spread over auxiliary streams so that small launches overlap (fork/join by events).
+// dev_slots != nullptr (forward pass): `counts[v]` = pairs whose query length falls into variant v, counted by the host
+// from the offsets it already holds; it sizes the grids of both flavours of the variant, while the kernels read the true
+// (start, count) of their list from dev_slots (filled by slot_scan_kernel), so the host never waits for the device bins.
+// dev_slots == nullptr (CUDASW_REV_FULL reverse pass): counts[slot] are the exact per-slot counts read back from the device.
 int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairIO io, const int4* fwd_c, int4* out_c,
-                            StripPool spool, uint64_t* launches) {
+                            StripPool spool, uint64_t* launches, const int* counts, const int* dev_slots, bool maybe_x) {
     cudaStream_t st = ss.main;
     int nonempty = 0;
-    for (int v = 0; v < 2 * g_nvar; v++) nonempty += h_hist[v] > 0;
+    for (int v = 0; v < (dev_slots ? g_nvar : 2 * g_nvar); v++) nonempty += counts[v] > 0;
     static const bool no_spread = getenv("CUDASW_NO_SPREAD") != nullptr;  // experiment hook: variant launches one after the other
     const bool spread = nonempty > 1 && !no_spread;
     // Quiet-chain flavour of the forward kernels: faster launch by launch (C2 -11 %, C3's variants -2.5 % serialised),
@@ -422,20 +435,21 @@ int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairI
     int64_t start = 0;
     int k = 0;
     for (int slot = 0; slot < 2 * g_nvar; slot++) {  // [0, nvar): query-profile flavour, [nvar, 2 nvar): xor-selector flavour
-        const int c = h_hist[slot];
+        const bool xr = slot >= g_nvar;
+        const int c = dev_slots ? ((xr && !maybe_x) ? 0 : counts[slot % g_nvar]) : counts[slot];
         if (c > 0) {
             const cusw::Variant& V = g_var[slot % g_nvar];
-            const bool xr = slot >= g_nvar;
             cudaStream_t s = st;
             if (spread) {
                 const int a = k++ % kAux;
                 s = ss.aux[a];
                 if (!used[a]) { CK(cudaStreamWaitEvent(s, ss.fork_ev, 0)); used[a] = true; }
             }
-            (reverse ? (xr ? V.revx : V.rev) : (xr ? V.fwdx : chained ? V.fwdc : V.fwd))(order + start, c, io, fwd_c, out_c, sc, spool, s);
+            (reverse ? (xr ? V.revx : V.rev) : (xr ? V.fwdx : chained ? V.fwdc : V.fwd))(dev_slots ? order : order + start, c, io, fwd_c, out_c, sc, spool, s,
+                                                                                      dev_slots ? dev_slots + 2 * slot : nullptr);
             (*launches)++;
         }
-        start += c;
+        if (!dev_slots) start += c;
     }
     for (int a = 0; a < kAux; a++)
         if (used[a]) {
@@ -456,7 +470,7 @@ int cudasw::launch_variants(StreamSet& ss, bool reverse, const int* order, PairI
 int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_seq, const int64_t* d_so,
                        const uint8_t* d_ref, const int64_t* d_ro, int64_t q_lo, int64_t q_hi,
                        int64_t w_lo, int64_t w_hi, bool gather, uint64_t* launches_out, bool qgather, int q_stride, int w_stride,
-                       bool packed) {
+                       bool packed, const int64_t* h_seq_off, const int64_t* h_ref_off) {
     cudaStream_t st = pack_stream;
     uint64_t launches = 0;
     const int64_t n = cnt;
@@ -521,15 +535,25 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p + first, keys_alt.p + first, vals.p + first,
                                        vals_alt.p + first, (int)n, 0, 32, st));
     launches += 3;
-    CK(cudaMemcpyAsync(h_hist, d_hist, 256 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    // where every (flavour, variant) slot starts in the sorted order: stays on the device (the forward kernels read it)
+    slot_scan_kernel<<<1, 32, 0, st>>>(d_hist, 2 * g_nvar + 1, fwd_slots.p + ci * (size_t)(2 * (2 * g_nvar + 1)));
+    launches++;
     CK(cudaEventRecord(chunk_ev[ci].pack1, st));
-    CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
+    {
+        // grid sizes for the forward launches: pairs per query-length class, from the host's own copy of the offsets
+        std::vector<int>& hc = fwd_counts[ci];
+        hc.assign((size_t)g_nvar, 0);
+        for (int64_t i = first; i < first + cnt; i++) {
+            const int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
+            if (q > 0 && w > 0 && q <= max_rows && w <= max_cols) hc[(size_t)var_by_q[(size_t)q]]++;
+        }
+    }
     *launches_out += launches;
     return CUDASW_OK;
 }
 
-// Forward score pass of one packed chunk (h_hist holds its pairs per variant). Waits for the pack by event.
+// Forward score pass of one packed chunk (fwd_counts / fwd_slots hold its bins). Waits for the pack by event.
 int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* d_so, const int64_t* d_ro, uint64_t* launches_out) {
     (void)cnt;
     cudaStream_t st = stream;
@@ -539,7 +563,8 @@ int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* 
     CK(cudaEventRecord(chunk_ev[ci].fwd0, st));
     CK(cudaMemsetAsync(d_strip, 0, sizeof(unsigned long long), st));
     StripPool spool{strip_fwd.p, (unsigned long long)strip_fwd.cap, d_strip};
-    { int rc = launch_variants(fwd_set, false, vals_alt.p + first, io, nullptr, fwd.p + first, spool, &launches); if (rc != CUDASW_OK) return rc; }
+    { int rc = launch_variants(fwd_set, false, vals_alt.p + first, io, nullptr, fwd.p + first, spool, &launches, fwd_counts[ci].data(),
+                               fwd_slots.p + ci * (size_t)(2 * (2 * g_nvar + 1)), batch_maybe_n); if (rc != CUDASW_OK) return rc; }
     CK(cudaEventRecord(chunk_ev[ci].fwd1, st));
     CK(cudaGetLastError());
     *launches_out += launches;
@@ -563,23 +588,24 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
     DevBuf<int> vals = this->vals, vals_alt = this->vals_alt, retry_a = this->retry_a, retry_b = this->retry_b, tb_band = this->tb_band;
     keys.p += first; keys_alt.p += first; vals.p += first; vals_alt.p += first; retry_a.p += first; retry_b.p += first; tb_band.p += first;
     const uint8_t* wflags_c = wflags.p + first;
-    size_t cub_bytes = cub_tmp.cap;
+    size_t cub_bytes = cub_tmp_post.cap;
     StripPool spool{strip_rev.p, (unsigned long long)strip_rev.cap, d_strip + 1};
     CK(cudaEventRecord(ev[3], st));
 
     // ---- reverse score pass
-    static const bool rev_full = getenv("CUDASW_REV_FULL") != nullptr;  // experiment hook: round 1's full-rectangle kernels
+    const bool rev_full = getenv("CUDASW_REV_FULL") != nullptr;  // experiment hook: round 1's full-rectangle kernels
     if (!rev_full) {
         // Banded, strip-mined, persistent kernels (rev_band.cuh): binned on the device, job list bounds read from device
         // memory, so nothing here waits for the host.
-        CK(cudaMemsetAsync(d_hist, 0, 64 * sizeof(int), st));
+        int* dhr = d_hist + 160;  // this pass's own histogram (the pack of a later chunk may be using d_hist[0 ..))
+        CK(cudaMemsetAsync(dhr, 0, 32 * sizeof(int), st));
         const int few_pairs = n < 4096 ? 1 : 0;
-        rev_band_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, sc.match, sc.B, sc.ge, few_pairs, keys.p, vals.p, d_hist,
+        rev_band_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, sc.match, sc.B, sc.ge, few_pairs, keys.p, vals.p, dhr,
                                                                     reinterpret_cast<int*>(d_counters + 5), wflags_c);
         launches++;
-        CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 24, st));
+        CK(cub::DeviceRadixSort::SortPairs(cub_tmp_post.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 24, st));
         launches += 3;
-        slot_scan_kernel<<<1, 32, 0, st>>>(d_hist, 2 * kRevVariants + 1, d_rev_slots);
+        slot_scan_kernel<<<1, 32, 0, st>>>(dhr, 2 * kRevVariants + 1, d_rev_slots);
         launches++;
         CK(cudaEventRecord(fork_ev, st));
         for (int s = 0; s < 2 * kRevVariants; s++) {
@@ -608,11 +634,11 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
     rev_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, vt, keys.p, vals.p, d_hist,
                                                            reinterpret_cast<int*>(d_counters + 5), wflags_c);
     launches++;
-    CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
+    CK(cub::DeviceRadixSort::SortPairs(cub_tmp_post.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
     launches += 3;
     CK(cudaMemcpyAsync(h_hist, d_hist, 256 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    { int rc = launch_variants(post_set, true, vals_alt.p, io, fwd_c, rev_c, spool, &launches); if (rc != CUDASW_OK) return rc; }
+    { int rc = launch_variants(post_set, true, vals_alt.p, io, fwd_c, rev_c, spool, &launches, h_hist, nullptr, true); if (rc != CUDASW_OK) return rc; }
     }
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[4], st));
@@ -625,8 +651,10 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
         CK(cudaStreamSynchronize(st));
     }
     // ---- traceback (+ retry rounds when the scratch pool runs out); the CIGAR counter [1] runs on across rounds.
-    // Pairs are sorted by estimated banded cells: the widest go to the warp-cooperative kernel (one warp each, on
-    // an auxiliary stream), the rest to the one-thread-per-pair kernel in descending cost order.
+    // Pairs are sorted by estimated banded cells: the widest go to the cooperative kernels (a CTA or a warp each, on
+    // auxiliary streams), the rest to the one-thread-per-pair kernels in descending cost order. A round is queued
+    // without the host knowing how the pairs fall into these lists: every kernel is launched over an upper-bound grid
+    // and reads its list bounds from device memory (tb_slots_kernel); the one synchronisation is at the end of the round.
     if (!ends_only) {
         // default: the one-thread kernel keeps bands up to kTbThreadBand in registers, wider pairs take a warp each;
         // CUDASW_TB_WIDE_CELLS additionally sends every pair above that many banded cells to the warp kernel (0 = all)
@@ -635,10 +663,13 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
         // widest starting band the one-thread kernels take (experiment hook; they hold up to kTbThreadBand in registers)
         int thread_band = kTbThreadBand;
         if (const char* e = getenv("CUDASW_TB_THREAD_BAND")) thread_band = std::min(std::max(atoi(e), 0), kTbThreadBand);
+        const int cta_wave = getenv("CUDASW_TB_NO_BLOCK") ? -1 : 148 * 8;  // big pairs take a CTA each while they fit one wave
         CK(cudaMemsetAsync(tb_band.p, 0, (size_t)n * sizeof(int), st));
         TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
         int* retry_count = reinterpret_cast<int*>(d_counters + 2);
         int* wide_count = reinterpret_cast<int*>(d_counters + 3);
+        int* dh = d_hist + 128;            // [0, 8): pairs per frame class, [8, 16): escalation list counters
+        int* tb_slots = d_rev_slots + 32;  // (start, count) of the kTbSlots lists of this round
         const int* list = nullptr;  // first round: every pair
         int c = (int)n;
         int* retry_out = retry_a.p;
@@ -646,23 +677,92 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
         for (int round = 0; round < 64 && c > 0; round++) {
             CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));      // pool
             CK(cudaMemsetAsync(d_counters + 2, 0, 2 * sizeof(unsigned long long), st));  // retry + wide counters
-            CK(cudaMemsetAsync(d_hist, 0, 8 * sizeof(int), st));                         // pairs per frame class
+            CK(cudaMemsetAsync(dh, 0, 16 * sizeof(int), st));                            // class and escalation counters
             CK(cudaMemsetAsync(d_counters + 7, 0, sizeof(unsigned long long), st));      // scratch estimate
-            // few pairs cannot fill the machine with one thread each: long ones then take a warp each
+            // few pairs cannot fill the machine with one thread each: long ones then take a warp / CTA each
             // (and run all their band passes in one kernel: a kernel boundary between passes costs the sum of the slowest
             // pairs of each stage instead of the slowest pair overall)
-            const long long wc = wide_cells >= 0 ? wide_cells : (c < 8192 ? 2048 : -1);
+            // (measured on C1: 10 k pairs 1.31 -> 0.76 ms with the 1024-cell rule, neutral at 50 k, slower from 400 k up)
+            const long long wc = wide_cells >= 0 ? wide_cells : (c < 8192 ? 2048 : c < 32768 ? 1024 : -1);
             tb_keys_kernel<<<(c + 255) / 256, 256, 0, st>>>(list, c, fwd_c, rev_c, res_c, wc, c < 8192 ? 1 : 0, thread_band, tb_band.p, keys.p, vals.p, wide_count,
-                                                            d_hist, d_counters + 7);
+                                                            dh, d_counters + 7);
             launches++;
-            CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, c, 0, 23, st));
+            CK(cub::DeviceRadixSort::SortPairs(cub_tmp_post.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, c, 0, 23, st));
             launches += 3;
-            CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-            CK(cudaMemcpyAsync(h_hist, d_hist, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
-            CK(cudaStreamSynchronize(st));
-            const int nwide = *reinterpret_cast<int*>(h_counters + 3);
+            tb_slots_kernel<<<1, 32, 0, st>>>(wide_count, dh, cta_wave, tb_slots);
+            launches++;
+            // escalation lists: kTbClasses + 2 arrays of c ints (list k = input of thread class k, list kTbClasses = input
+            // of the small warp kernel, list kTbClasses + 1 = input of the big one); their counters live in dh[8 ..]
+            CK(tb_esc.ensure((size_t)(kTbClasses + 2) * (size_t)c));
+            int* esc_small = tb_esc.p + (size_t)kTbClasses * c;
+            int* esc_big = tb_esc.p + (size_t)(kTbClasses + 1) * c;
+            int* esc_small_count = dh + 8 + kTbClasses;
+            int* esc_big_count = dh + 8 + kTbClasses + 1;
+            const unsigned long long ccap = (unsigned long long)cigar_cap;
             {
-                // the scratch pool follows the demand of the batch (first band passes + a margin for doublings)
+                CK(cudaEventRecord(fork_ev, st));
+                // big pairs: a CTA each while they fit one wave (a quarter of the per-pair latency of a lone warp; anything
+                // wider than its register frames is handed to the one-warp kernel's list), else a warp each
+                CK(cudaStreamWaitEvent(aux[0], fork_ev, 0));
+                sw_traceback_block_kernel<<<std::min(c, 148 * 8), 128, 0, aux[0]>>>(vals_alt.p, 0, esc_big, esc_big_count, io, fwd_c, rev_c, tc, pool, res_c,
+                                                                                   cig.p, ccap, d_counters + 1, retry_out, retry_count, tb_band.p, tb_slots + 0);
+                sw_traceback_warp_kernel<32><<<std::min((c + 3) / 4, 148 * 8), 128, 0, aux[0]>>>(vals_alt.p, 0, nullptr, nullptr, nullptr, io, fwd_c, rev_c, tc,
+                                                                                                pool, res_c, cig.p, ccap, d_counters + 1, retry_out,
+                                                                                                retry_count, tb_band.p, tb_slots + 2);
+                launches += 2;
+                CK(cudaEventRecord(join_ev[0], aux[0]));
+                CK(cudaStreamWaitEvent(aux[1], fork_ev, 0));
+                sw_traceback_warp_kernel<8><<<std::min((c + 3) / 4, 148 * 16), 128, 0, aux[1]>>>(vals_alt.p, 0, nullptr, esc_big, esc_big_count, io, fwd_c, rev_c,
+                                                                                                tc, pool, res_c, cig.p, ccap, d_counters + 1, retry_out,
+                                                                                                retry_count, tb_band.p, tb_slots + 4);
+                launches++;
+                CK(cudaEventRecord(join_ev[1], aux[1]));
+            }
+            {
+                // One launch per frame class, narrowest first: class k appends the pairs that outgrow its frame to the
+                // escalation list that class k+1 reads behind its own (sorted) list, and the widest class hands over to
+                // a second warp-kernel launch, all stream-ordered. Class slot 5 = pairs with nothing to trace.
+                const int grid = std::min((c + 127) / 128, 148 * 8);
+                for (int k = 0; k <= kTbClasses; k++) {
+                    const bool none = k == kTbClasses;  // score 0 / failed pairs: "1M(q-1)S" or nothing; any class will do
+                    const int* esc_in = (k == 0 || none) ? nullptr : tb_esc.p + (size_t)k * c;
+                    const int* esc_in_count = (k == 0 || none) ? nullptr : dh + 8 + k;
+                    int* esc_out = none ? tb_esc.p : tb_esc.p + (size_t)(k + 1) * c;
+                    int* esc_out_count = none ? dh + 8 : dh + 8 + k + 1;
+#define CUSW_TB_LAUNCH(B)                                                                                                           \
+    sw_traceback_kernel<B><<<grid, 128, 0, st>>>(vals_alt.p, 0, esc_in, esc_in_count, esc_out, esc_out_count, io, fwd_c, rev_c, tc, pool, res_c, \
+                                                 cig.p, ccap, d_counters + 1, retry_out, retry_count, tb_band.p, tb_slots + 6 + 2 * k)
+                    switch (k) {
+                        case 1: CUSW_TB_LAUNCH(2); break;
+                        case 2: CUSW_TB_LAUNCH(4); break;
+                        case 3: CUSW_TB_LAUNCH(8); break;
+                        case 4: CUSW_TB_LAUNCH(16); break;
+                        default: CUSW_TB_LAUNCH(1); break;
+                    }
+#undef CUSW_TB_LAUNCH
+                    launches++;
+                }
+                // pairs that outgrew the widest frame, then those that outgrew the small warp kernel (from either launch)
+                sw_traceback_warp_kernel<8><<<148 * 4, 128, 0, st>>>(esc_small, 0, esc_small_count, esc_big, esc_big_count, io, fwd_c,
+                                                                      rev_c, tc, pool, res_c, cig.p, ccap, d_counters + 1, retry_out, retry_count, tb_band.p);
+                launches++;
+                CK(cudaStreamWaitEvent(st, join_ev[1], 0));
+                CK(cudaStreamWaitEvent(st, join_ev[0], 0));  // the CTA-per-pair kernel may append to esc_big too
+                sw_traceback_warp_kernel<32><<<148 * 3, 128, 0, st>>>(esc_big, 0, esc_big_count, nullptr, nullptr, io, fwd_c,
+                                                                      rev_c, tc, pool, res_c, cig.p, ccap, d_counters + 1, retry_out, retry_count, tb_band.p);
+                launches++;
+            }
+            CK(cudaEventRecord(ev[5], st));
+            CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));  // the one host round trip of the round
+            int nretry = *reinterpret_cast<int*>(h_counters + 2);
+            if (nretry == 0) { c = 0; break; }
+            // a whole round may legitimately come back once (every pair handed from the thread kernel to the warp
+            // kernel); twice in a row means no pair fits the scratch pool
+            if (nretry == c && stuck) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
+            stuck = nretry == c;
+            {
+                // the scratch pool ran out: let it follow the demand (first band passes of the round + a margin for doublings)
                 const unsigned long long est = 3ull * h_counters[7] + ((unsigned long long)256 << 20);
                 if (est > tb_pool_bytes && !getenv("CUDASW_TB_POOL_MB")) {
                     size_t free_b = 0, total_b = 0;
@@ -674,107 +774,10 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
                         CK(tb_pool.ensure(want));
                         tb_pool_bytes = want;
                         pool = TbPool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+                        stuck = false;
                     }
                 }
             }
-            const int nbig = reinterpret_cast<int*>(h_counters + 3)[1];
-            // escalation lists: kTbClasses + 2 arrays of c ints (list k = input of thread class k, list kTbClasses = input
-            // of the small warp kernel, list kTbClasses + 1 = input of the big one); their counters live in d_hist[8 ..]
-            CK(tb_esc.ensure((size_t)(kTbClasses + 2) * (size_t)c));
-            CK(cudaMemsetAsync(d_hist + 8, 0, 8 * sizeof(int), st));
-            int* esc_small = tb_esc.p + (size_t)kTbClasses * c;
-            int* esc_big = tb_esc.p + (size_t)(kTbClasses + 1) * c;
-            int* esc_small_count = d_hist + 8 + kTbClasses;
-            int* esc_big_count = d_hist + 8 + kTbClasses + 1;
-            if (nwide > 0) {
-                CK(cudaEventRecord(fork_ev, st));
-                if (nbig > 0) {
-                    CK(cudaStreamWaitEvent(aux[0], fork_ev, 0));
-                    if (nbig <= 148 * 8 && !getenv("CUDASW_TB_NO_BLOCK")) {  // one wave of the CTA-per-pair kernel
-                        // few pairs: a CTA per pair (a quarter of the per-pair latency of a lone warp); anything wider than
-                        // its register frames is handed to the one-warp kernel's list
-                        sw_traceback_block_kernel<<<std::min(nbig, 148 * 8), 128, 0, aux[0]>>>(vals_alt.p, nbig, esc_big, esc_big_count, io, fwd_c, rev_c,
-                                                                                              tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,
-                                                                                              d_counters + 1, retry_out, retry_count, tb_band.p);
-                    } else
-                    sw_traceback_warp_kernel<32><<<(nbig + 3) / 4, 128, 0, aux[0]>>>(vals_alt.p, nbig, nullptr, nullptr, nullptr, io, fwd_c, rev_c, tc,
-                                                                                     pool, res_c, cig.p, (unsigned long long)cigar_cap,
-                                                                                     d_counters + 1, retry_out, retry_count, tb_band.p);
-                    launches++;
-                    CK(cudaEventRecord(join_ev[0], aux[0]));
-                }
-                if (nwide > nbig) {
-                    CK(cudaStreamWaitEvent(aux[1], fork_ev, 0));
-                    sw_traceback_warp_kernel<8><<<(nwide - nbig + 3) / 4, 128, 0, aux[1]>>>(vals_alt.p + nbig, nwide - nbig, nullptr, esc_big,
-                                                                                             esc_big_count, io, fwd_c, rev_c, tc, pool, res_c, cig.p,
-                                                                                             (unsigned long long)cigar_cap, d_counters + 1, retry_out,
-                                                                                             retry_count, tb_band.p);
-                    launches++;
-                    CK(cudaEventRecord(join_ev[1], aux[1]));
-                }
-            }
-            {
-                // One launch per frame class, narrowest first: class k appends the pairs that outgrow its frame to the
-                // escalation list that class k+1 reads behind its own (sorted) list, and the widest class hands over to
-                // a second warp-kernel launch, all stream-ordered. Class slot 5 = pairs with nothing to trace.
-                int start = nwide;
-                int cstart[kTbClasses + 1];
-                for (int k = 0; k <= kTbClasses; k++) { cstart[k] = start; start += h_hist[k]; }
-                for (int k = 0; k < kTbClasses; k++) {
-                    const int own = h_hist[k];
-                    const int* esc_in = k == 0 ? nullptr : tb_esc.p + (size_t)k * c;
-                    const int* esc_in_count = k == 0 ? nullptr : d_hist + 8 + k;
-                    int* esc_out = tb_esc.p + (size_t)(k + 1) * c;
-                    int* esc_out_count = d_hist + 8 + k + 1;
-                    // the escalated pairs are not known to the host: the grid covers the own list plus a few CTAs per SM
-                    // and strides over whatever else there is
-                    const int grid = (own + 127) / 128 + (k == 0 ? 0 : 148 * 2);
-                    if (grid == 0) continue;
-#define CUSW_TB_LAUNCH(B)                                                                                              \
-    sw_traceback_kernel<B><<<grid, 128, 0, st>>>(vals_alt.p + cstart[k], own, esc_in, esc_in_count, esc_out, esc_out_count, io, \
-                                                 fwd_c, rev_c, tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,     \
-                                                 d_counters + 1, retry_out, retry_count, tb_band.p)
-                    switch (k) {
-                        case 0: CUSW_TB_LAUNCH(1); break;
-                        case 1: CUSW_TB_LAUNCH(2); break;
-                        case 2: CUSW_TB_LAUNCH(4); break;
-                        case 3: CUSW_TB_LAUNCH(8); break;
-                        default: CUSW_TB_LAUNCH(16); break;
-                    }
-                    launches++;
-                }
-                if (h_hist[kTbClasses] > 0) {  // score 0 / failed pairs: "1M(q-1)S" or nothing; any class will do
-                    const int k = kTbClasses, own = h_hist[kTbClasses];
-                    const int grid = (own + 127) / 128;
-                    const int *esc_in = nullptr, *esc_in_count = nullptr;
-                    int* esc_out = tb_esc.p;
-                    int* esc_out_count = d_hist + 8;
-                    CUSW_TB_LAUNCH(1);
-                    launches++;
-                }
-#undef CUSW_TB_LAUNCH
-                // pairs that outgrew the widest frame, then those that outgrew the small warp kernel (from either launch)
-                sw_traceback_warp_kernel<8><<<148 * 4, 128, 0, st>>>(esc_small, 0, esc_small_count, esc_big, esc_big_count, io, fwd_c,
-                                                                      rev_c, tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,
-                                                                      d_counters + 1, retry_out, retry_count, tb_band.p);
-                launches++;
-                if (nwide > nbig) CK(cudaStreamWaitEvent(st, join_ev[1], 0));
-                if (nbig > 0) CK(cudaStreamWaitEvent(st, join_ev[0], 0));  // the CTA-per-pair kernel may append to esc_big too
-                sw_traceback_warp_kernel<32><<<148 * 3, 128, 0, st>>>(esc_big, 0, esc_big_count, nullptr, nullptr, io, fwd_c,
-                                                                      rev_c, tc, pool, res_c, cig.p, (unsigned long long)cigar_cap,
-                                                                      d_counters + 1, retry_out, retry_count, tb_band.p);
-                launches++;
-            }
-            if (nbig > 0) CK(cudaStreamWaitEvent(st, join_ev[0], 0));
-            CK(cudaEventRecord(ev[5], st));
-            CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-            CK(cudaStreamSynchronize(st));
-            int nretry = *reinterpret_cast<int*>(h_counters + 2);
-            if (nretry == 0) { c = 0; break; }
-            // a whole round may legitimately come back once (every pair handed from the thread kernel to the warp
-            // kernel); twice in a row means no pair fits the scratch pool
-            if (nretry == c && stuck) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
-            stuck = nretry == c;
             list = retry_out;
             retry_out = (retry_out == retry_a.p) ? retry_b.p : retry_a.p;
             c = nretry;
@@ -930,7 +933,11 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         size_t cub_bytes = 0;
         CK(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
         CK(cub_tmp.ensure(cub_bytes + 16));
+        CK(cub_tmp_post.ensure(cub_bytes + 16));
     }
+    fwd_counts.resize(chunks.size());
+    CK(fwd_slots.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1))));
+    batch_maybe_n = !(packed && packed->refN == nullptr);
     if (!tb_pool.p) {
         size_t free_b = 0, total_b = 0;
         CK(cudaMemGetInfo(&free_b, &total_b));
@@ -1045,7 +1052,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     for (size_t i = 0; i < chunks.size(); i++) {
         const Chunk& c = chunks[i];
         if (inputs_on_host) CK(cudaStreamWaitEvent(pack_stream, h2d_done[i], 0));
-        int rc = pack_chunk(i, c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, gather, &launches, qgather, q_stride, w_stride, packed != nullptr);
+        int rc = pack_chunk(i, c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, gather, &launches, qgather, q_stride, w_stride, packed != nullptr, h_seq_off, h_ref_off);
         // reverse-pass strips: per chunk when post runs per chunk, else once for the whole batch (sized with the first chunk)
         if (rc == CUDASW_OK) rc = size_strip_buffers(c.first, c.cnt, h_seq_off, h_ref_off, post_per_chunk ? c.first : 0, post_per_chunk ? c.cnt : (i == 0 ? n : 0));
         if (rc == CUDASW_OK) rc = forward_chunk(i, c.first, c.cnt, d_so, d_ro, &launches);

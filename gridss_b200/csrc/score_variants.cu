@@ -9,10 +9,11 @@ namespace cusw {
 
 template <int G, int R, bool REV, bool MULTI, bool PROF, bool CHN = false>
 static void launch_score(const int* order, int njobs, PairIO io, const int4* fwd, int4* out, ScoreConst sc,
-                         StripPool sp, cudaStream_t st) {
+                         StripPool sp, cudaStream_t st, const int* slot) {
+    // njobs sizes the grid (with `slot` it is an upper bound; the kernel reads the true list bounds from device memory)
     constexpr int GPB = 128 / G;
     int blocks = (njobs + GPB - 1) / GPB;
-    sw_score_kernel<G, R, REV, MULTI, PROF, CHN><<<blocks, 128, 0, st>>>(order, njobs, io, fwd, out, sc, sp);
+    sw_score_kernel<G, R, REV, MULTI, PROF, CHN><<<blocks, 128, 0, st>>>(order, njobs, io, fwd, out, sc, sp, slot);
 }
 
 #define V(R) v.push_back(Variant{SCORE_G, R, 2 * SCORE_G * R, false, launch_score<SCORE_G, R, false, false, true>, launch_score<SCORE_G, R, true, false, true>, launch_score<SCORE_G, R, false, false, false>, launch_score<SCORE_G, R, true, false, false>, launch_score<SCORE_G, R, false, false, true, true>})

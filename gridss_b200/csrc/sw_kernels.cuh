@@ -532,13 +532,17 @@ constexpr int score_min_blocks() { return (PROF ? 5 : 4) * R + 32 <= 128 ? 4 : (
 template <int G, int R, bool REV, bool MULTI, bool PROF, bool CHN = false>
 __global__ void __launch_bounds__(128, score_min_blocks<R, PROF>())
 sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4* __restrict__ fwd,
-                int4* __restrict__ out, ScoreConst sc, StripPool sp) {
+                int4* __restrict__ out, ScoreConst sc, StripPool sp, const int* __restrict__ slot) {
     static_assert(!MULTI || G == 32, "strip mining uses one warp per pair");
     constexpr int GPB = 128 / G;
     constexpr int S = 2 * G * R;  // rows per strip
     const int lig = threadIdx.x % G;
     const int gidx = blockIdx.x * GPB + threadIdx.x / G;
+    // slot != nullptr: the job list is order[slot[0] .. slot[0] + slot[1]), binned on the device; the grid was sized from
+    // an upper bound the host knows (pairs per query-length class), so trailing warps may have nothing to do
+    if (slot) { njobs = slot[1]; order += slot[0]; }
     const bool active = gidx < njobs;
+    if (!__any_sync(0xffffffffu, active)) return;  // (warps never synchronise with each other in this kernel)
 
     int q = 0, w = 0, target = -1, pair = -1;
     const uint8_t* qptr = io.enc_seq;
@@ -1090,6 +1094,26 @@ __global__ void tb_keys_kernel(const int* __restrict__ list, int n, const int4* 
     vals[tid] = pair;
 }
 
+// (start, count) of the traceback lists inside the sorted order, from the counters tb_keys_kernel left behind, so that
+// the kernels can be launched without the host knowing the counts. Slots: 0 = big pairs for the CTA-per-pair kernel,
+// 1 = big pairs for the one-warp kernel (one of the two is empty: a CTA per pair pays while they fit one wave),
+// 2 = other wide pairs (small warp kernel), 3 + k = one-thread class k (k = kTbClasses: nothing to trace).
+constexpr int kTbSlots = 3 + kTbClasses + 1;
+__global__ void tb_slots_kernel(const int* __restrict__ wide_count, const int* __restrict__ cls_count, int cta_wave, int* __restrict__ slots) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const int nwide = wide_count[0], nbig = wide_count[1];
+    const bool cta = nbig <= cta_wave;
+    slots[0] = 0; slots[1] = cta ? nbig : 0;
+    slots[2] = 0; slots[3] = cta ? 0 : nbig;
+    slots[4] = nbig; slots[5] = nwide - nbig;
+    int start = nwide;
+    for (int k = 0; k <= kTbClasses; k++) {
+        slots[6 + 2 * k] = start;
+        slots[7 + 2 * k] = cls_count[k];
+        start += cls_count[k];
+    }
+}
+
 // Reserves CIGAR words for one pair and writes soft clips + body (SswJniAligner.java:52-59).
 __device__ __forceinline__ void tb_emit(int pair, int q, int score, int ref_begin, int ref_end, int read_begin,
                                         int read_end, int nbody, const uint8_t* dirp, int width_d, int band,
@@ -1225,7 +1249,9 @@ sw_traceback_kernel(const int* __restrict__ list, int n_own, const int* __restri
                     PairIO io, const int4* __restrict__ fwd, const int4* __restrict__ rev, TbConst tc, TbPool pool,
                     cudasw_result* __restrict__ res, uint32_t* __restrict__ cig,
                     unsigned long long cig_cap, unsigned long long* __restrict__ cig_used,
-                    int* __restrict__ retry_list, int* __restrict__ retry_count, int* __restrict__ tb_band) {
+                    int* __restrict__ retry_list, int* __restrict__ retry_count, int* __restrict__ tb_band,
+                    const int* __restrict__ slot = nullptr) {
+    if (slot) { list += slot[0]; n_own = slot[1]; }  // own list bounds from device memory (tb_slots_kernel)
     const int n_all = n_own + (esc_in_count ? *esc_in_count : 0);
     for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_all; idx += gridDim.x * blockDim.x) {
         const int pair = idx < n_own ? list[idx] : esc_in[idx - n_own];
@@ -1310,9 +1336,10 @@ sw_traceback_warp_kernel(const int* __restrict__ list, int n, const int* __restr
                          const int4* __restrict__ rev, TbConst tc, TbPool pool, cudasw_result* __restrict__ res,
                          uint32_t* __restrict__ cig, unsigned long long cig_cap,
                          unsigned long long* __restrict__ cig_used, int* __restrict__ retry_list,
-                         int* __restrict__ retry_count, int* __restrict__ tb_band) {
+                         int* __restrict__ retry_count, int* __restrict__ tb_band, const int* __restrict__ slot = nullptr) {
     const int lane = threadIdx.x & 31;
     if (n_dev) n = *n_dev;  // the list was filled on the device (pairs escalated by sw_traceback_kernel<16>)
+    if (slot) { list += slot[0]; n = slot[1]; }  // list bounds from device memory (tb_slots_kernel)
     for (int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; wid < n; wid += (gridDim.x * blockDim.x) >> 5) {
     const int pair = list[wid];
     cudasw_result r = res[pair];
@@ -1417,7 +1444,8 @@ sw_traceback_block_kernel(const int* __restrict__ list, int n, int* __restrict__
                           PairIO io, const int4* __restrict__ fwd, const int4* __restrict__ rev, TbConst tc, TbPool pool,
                           cudasw_result* __restrict__ res, uint32_t* __restrict__ cig, unsigned long long cig_cap,
                           unsigned long long* __restrict__ cig_used, int* __restrict__ retry_list,
-                          int* __restrict__ retry_count, int* __restrict__ tb_band) {
+                          int* __restrict__ retry_count, int* __restrict__ tb_band, const int* __restrict__ slot = nullptr) {
+    if (slot) { list += slot[0]; n = slot[1]; }
     __shared__ TbXchg xc;
     __shared__ unsigned long long off_sh;
     __shared__ uint32_t ops_sh[kTbOpsBuf];

@@ -9,7 +9,7 @@
 
 namespace cusw {
 
-typedef void (*score_launch_fn)(const int*, int, PairIO, const int4*, int4*, ScoreConst, StripPool, cudaStream_t);
+typedef void (*score_launch_fn)(const int*, int, PairIO, const int4*, int4*, ScoreConst, StripPool, cudaStream_t, const int* slot);
 
 struct Variant {
     int G, R, rows;  // rows = 2*G*R; for multi (strip-mined) variants rows per strip
