@@ -17,7 +17,7 @@ from typing import Sequence
 
 import numpy as np
 
-from .aligner import BREAKPOINT_DTYPE, WINDOW_DTYPE, WINDOW_REVCOMP, CudaAligner, cigar_string, pack
+from .aligner import BREAKPOINT_DTYPE, CUDASW_EINVAL, WINDOW_DTYPE, WINDOW_REVCOMP, CudaAligner, CudaSwError, cigar_string, pack
 
 FWD, BWD = "f", "b"
 _COMP = bytes.maketrans(b"ACGTNacgtn", b"TGCANtgcan")
@@ -172,8 +172,10 @@ def breakpoint_homology_batch(aligner: CudaAligner, contigs: Sequence[bytes], br
         res, cig = aligner.align_blobs_windows(sb, so, win, np.asarray(win_off, dtype=np.int64))
         for i, (k, side) in enumerate(owner):
             r = res[i]
-            if r["status"] != 0:
-                continue  # an empty window: the reference skips the call (:76, :86)
+            if r["status"] == CUDASW_EINVAL:
+                continue  # a window the reference clipped to nothing / outside the contig: it skips the call (:76, :86)
+            if r["status"] != 0:  # ENOMEM / ETOOLARGE / EUNDEF are not "no alignment": the reference would have thrown or crashed
+                raise CudaSwError(f"breakpoint {k}: alignment failed with status {int(r['status'])}")
             lead, tail = _clips(cig[r["cigar_off"]: r["cigar_off"] + r["cigar_len"]])
             n_local, n_remote = meta[k]
             if side == 0:   # local alignment -> remote homology (:79-85)
@@ -242,12 +244,20 @@ def realign_batch(aligner: CudaAligner, contig_len: Sequence[int], reads, window
         res, cig = aligner.align_blobs_windows(sb, so, np.array(win, dtype=WINDOW_DTYPE), np.arange(len(win) + 1, dtype=np.int64))
     for (ref_idx, pos0, cigar, bases), k in zip(reads, keep):
         if k is None or res[k]["status"] != 0:
-            out.append((pos0, cigar))                        # alignment == null -> return read (:643-645)
+            # alignment == null -> return read (:643-645); the reference swallows EVERY exception of the aligner here
+            # (catch (Exception e), :632-644), so any per-pair failure keeps the original alignment; it is counted so
+            # that a caller can tell "unchanged" from "could not be realigned"
+            if k is not None:
+                realign_batch.failed += 1
+            out.append((pos0, cigar))
             continue
         r = res[k]
         new_cigar = cigar_string(cig[r["cigar_off"]: r["cigar_off"] + r["cigar_len"]])
         out.append((starts[k] + int(r["ref_begin"]), new_cigar))   # :647
     return out
+
+
+realign_batch.failed = 0  # reads whose realignment failed in the engine (kept unchanged, as the reference does)
 
 
 class SmithWatermanStreamingAligner:
@@ -278,6 +288,11 @@ class SmithWatermanStreamingAligner:
         sb, so = pack([b for _, b in self._pending])
         res, cig = self.aligner.align_blobs_windows(sb, so, np.repeat(self._win, n), np.arange(n + 1, dtype=np.int64))
         for (name, _), r in zip(self._pending, res):
+            if r["status"] != 0:
+                # e.g. CUDASW_ETOOLARGE: a contig beyond 2^24 - 2 columns or a read beyond 32 k rows. The reference would
+                # have produced an alignment (or died in native code); silently emitting start 0 / empty CIGAR is neither
+                self._pending.clear()
+                raise CudaSwError(f"read {name}: alignment failed with status {int(r['status'])}")
             words = cig[r["cigar_off"]: r["cigar_off"] + r["cigar_len"]]
             self._done.append((name, self.referenceIndex, int(r["ref_begin"]) + 1, cigar_string(words)))   # :36-38
         self._pending.clear()

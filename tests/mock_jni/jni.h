@@ -32,5 +32,9 @@ struct JNINativeInterface_ {
     void (*SetObjectArrayElement)(JNIEnv*, jobjectArray, jsize, jobject);
     jobject (*NewDirectByteBuffer)(JNIEnv*, void*, jlong);
     void* (*GetDirectBufferAddress)(JNIEnv*, jobject);
+    jlong (*GetDirectBufferCapacity)(JNIEnv*, jobject);
+    void (*GetByteArrayRegion)(JNIEnv*, jbyteArray, jsize, jsize, jbyte*);
+    void (*GetLongArrayRegion)(JNIEnv*, jlongArray, jsize, jsize, jlong*);
+    void (*DeleteLocalRef)(JNIEnv*, jobject);
 };
 #endif

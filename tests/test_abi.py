@@ -147,3 +147,40 @@ def test_host_packer_matches_the_declared_layout():
     a = g.pack_bases(big, threads=1)
     b = g.pack_bases(big, threads=4)
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2] == b[2]
+
+
+def test_reference_side_patches_apply_and_the_contract_test_exists():
+    """N2: the AlignerFactory / Defaults wiring is a real patch against the reference sources, and the
+    reference's aligner contract test has a subclass for the new backend. Needs /root/reference (not on the GPU box)."""
+    import shutil
+    import subprocess
+    import tempfile
+
+    ref = "/root/reference"
+    jdir = os.path.join(ROOT, "java")
+    test_src = open(os.path.join(jdir, "test", "au", "edu", "wehi", "idsv", "alignment", "CudaAlignerTest.java")).read()
+    assert "extends SmithWatermanAlignerTest" in test_src and "new CudaAligner(" in test_src
+    # every class / member the patched factory refers to exists in the shim sources
+    fac = open(os.path.join(jdir, "patches", "AlignerFactory.java.patch")).read()
+    dfl = open(os.path.join(jdir, "patches", "Defaults.java.patch")).read()
+    cuda = open(os.path.join(jdir, "au", "edu", "wehi", "idsv", "alignment", "CudaAligner.java")).read()
+    batching = open(os.path.join(jdir, "au", "edu", "wehi", "idsv", "alignment", "BatchingAligner.java")).read()
+    for name in re.findall(r"Defaults\.(CUDASW_\w+|USE_CUDASW)", fac):
+        assert f" {name};" in dfl and f"{name} = " in dfl, name
+    assert "public CudaAligner(int match, int mismatch, int ambiguous, int gapOpen, int gapExtend, int device)" in cuda
+    assert "public BatchingAligner(CudaAligner aligner, int batchSize, long maxWaitMillis)" in batching
+    assert "implements Aligner, AutoCloseable" in cuda and "isCudaswLoaded" in fac and "isCudaswLoaded" in test_src
+    if not os.path.isdir(ref):
+        pytest.skip("reference tree not present")
+    with tempfile.TemporaryDirectory() as tmp:
+        for rel in ("src/main/java/au/edu/wehi/idsv/alignment/AlignerFactory.java", "src/main/java/au/edu/wehi/idsv/Defaults.java"):
+            os.makedirs(os.path.dirname(os.path.join(tmp, rel)), exist_ok=True)
+            shutil.copy(os.path.join(ref, rel), os.path.join(tmp, rel))
+        for p in ("AlignerFactory.java.patch", "Defaults.java.patch"):
+            subprocess.check_call(["patch", "--dry-run", "-p1", "-s", "-d", tmp, "-i", os.path.join(jdir, "patches", p)])
+            subprocess.check_call(["patch", "-p1", "-s", "-d", tmp, "-i", os.path.join(jdir, "patches", p)])
+        out = open(os.path.join(tmp, "src/main/java/au/edu/wehi/idsv/alignment/AlignerFactory.java")).read()
+        # the new branch sits ahead of GKL / sswjni / JAligner and the fall-through chain is intact
+        body = out[out.index("public static Aligner create(int match"):]
+        assert body.index("cudaswLoaded") < body.index("isw != null") < body.index("sswjniLoaded") < body.index("JAlignerAligner")
+        assert out.count("{") == out.count("}")
