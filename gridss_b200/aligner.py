@@ -19,7 +19,8 @@ from typing import Iterable, Sequence
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libcudasw.so")
+# CUDASW_LIB selects another build of the same library (the -DCUSW_BOUNDS_CHECK flavour, gridss_b200/build.py --check)
+LIB_PATH = os.environ.get("CUDASW_LIB") or os.path.join(HERE, "libcudasw.so")
 
 CUDASW_OK = 0
 CUDASW_EINVAL = -1

@@ -28,11 +28,16 @@ def up_to_date() -> bool:
     return all(os.path.getmtime(d) <= t for d in _deps())
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, check: bool = False) -> str:
+    """check=True: the -DCUSW_BOUNDS_CHECK flavour (every data-dependent global index trapped when out of range) as
+    libcudasw_check.so beside the product library; tests load it with CUDASW_LIB=<path> (gridss_b200/aligner.py)."""
+    global OBJ, OUT
+    if check:
+        OBJ, OUT = os.path.join(HERE, "build_check"), os.path.join(HERE, "libcudasw_check.so")
     if not force and up_to_date():
         return OUT
     os.makedirs(OBJ, exist_ok=True)
-    extra = (["-Xptxas", "-v"] if verbose else []) + os.environ.get("CUDASW_NVCC_EXTRA", "").split()
+    extra = (["-Xptxas", "-v"] if verbose else []) + (["-DCUSW_BOUNDS_CHECK"] if check else []) + os.environ.get("CUDASW_NVCC_EXTRA", "").split()
     jobs = [(os.path.join(OBJ, "cudasw.o"), [os.path.join(CSRC, "cudasw.cu")]),
             (os.path.join(OBJ, "variants.o"), [os.path.join(CSRC, "variants.cu")]),
             (os.path.join(OBJ, "multi.o"), [os.path.join(CSRC, "multi.cpp")]),
@@ -52,5 +57,5 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    build(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    build(force="--force" in sys.argv, verbose="-v" in sys.argv, check="--check" in sys.argv)
     print(OUT)

@@ -117,6 +117,15 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
     long long dmax = 0;
     const uint8_t* qptr = io.enc_seq;
     const uint8_t* rptr = io.enc_ref;
+#ifdef CUSW_BOUNDS_CHECK
+    const uint8_t *ck_q0 = nullptr, *ck_q1 = nullptr, *ck_r0 = nullptr, *ck_r1 = nullptr;  // this pair's own bytes
+    const uint32_t* ck_b1 = ring_a + 2 * (size_t)ring_half;                                // end of this group's ring
+    if (active) {
+        const int pr = order[gidx];
+        ck_q0 = io.enc_seq + io.seq_off[pr]; ck_q1 = io.enc_seq + io.seq_off[pr + 1];
+        ck_r0 = io.enc_ref + io.ref_off[pr]; ck_r1 = io.enc_ref + io.ref_off[pr + 1];
+    }
+#endif
     if (active) {
         pair = order[gidx];
         const int4 f = fwd[pair];
@@ -156,6 +165,8 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
 #pragma unroll
         for (int k = 0; k < R; k++) {
             const int a = r0 + k, b = r0 + R + k;
+            if (has && a < q) CUSW_CHECK_PTR(qptr - (int64_t)a, ck_q0, ck_q1, "query row (reverse)");
+            if (has && b < q) CUSW_CHECK_PTR(qptr - (int64_t)b, ck_q0, ck_q1, "query row (reverse)");
             const uint32_t qa = (has && a < q) ? (uint32_t)qptr[-(int64_t)a] : kQueryPad;
             const uint32_t qb = (has && b < q) ? (uint32_t)qptr[-(int64_t)b] : kQueryPad;
             if (PROF) {
@@ -178,6 +189,7 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
     int t_end = has ? wlen + 2 * G - 1 : 0;
     int t_end_warp = (__reduce_max_sync(0xffffffffu, t_end) + 1) & ~1;
     int c = -2 * lig;  // local column of the low virtual lane
+    if ((unsigned)c < (unsigned)wlen) CUSW_CHECK_PTR(rp - (int64_t)c, ck_r0, ck_r1, "window column (reverse)");
     uint32_t rb_next = ((unsigned)c < (unsigned)wlen) ? (uint32_t)rp[-(int64_t)c] : kOut;
     const bool read_top = has && strip > 0 && lig == 0;
     const bool write_bot = has && lig == G - 1 && row0 + S < q;
@@ -185,8 +197,8 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
     uint32_t top_next = cBB & 0xFFFFu;  // lane 0: (H | F << 16) of the row above the strip at column c
     uint32_t topdiag = cBB & 0xFFFFu;   // lane 0: H of the row above the strip at column c0 - 1 (diagonal of the first cell)
     if (read_top) {
-        if ((unsigned)c < (unsigned)wlen && c + shift < plen) top_next = bnd_in[c + shift];
-        if (shift >= 1 && shift - 1 < plen) topdiag = bnd_in[shift - 1] & 0xFFFFu;
+        if ((unsigned)c < (unsigned)wlen && c + shift < plen) { CUSW_CHECK_PTR(bnd_in + c + shift, ring_a, ck_b1, "ring read"); top_next = bnd_in[c + shift]; }
+        if (shift >= 1 && shift - 1 < plen) { CUSW_CHECK_PTR(bnd_in + shift - 1, ring_a, ck_b1, "ring read (diagonal)"); topdiag = bnd_in[shift - 1] & 0xFFFFu; }
     }
     if (lig == 0) Hdiag_top = (Hdiag_top & 0xFFFF0000u) | topdiag;
 
@@ -202,8 +214,9 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
             rb_next = kOut;
             top_next = cBB & 0xFFFFu;
             if ((unsigned)cn < (unsigned)wlen) {
+                CUSW_CHECK_PTR(rp - (int64_t)cn, ck_r0, ck_r1, "window column (reverse)");
                 rb_next = (uint32_t)rp[-(int64_t)cn];
-                if (read_top && cn + shift < plen) top_next = bnd_in[cn + shift];
+                if (read_top && cn + shift < plen) { CUSW_CHECK_PTR(bnd_in + cn + shift, ring_a, ck_b1, "ring read"); top_next = bnd_in[cn + shift]; }
             }
         }
         Rsel = prmt(Rsel, rb, 0x3204u);  // byte1 <- old byte0, byte0 <- new
@@ -241,7 +254,12 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
         if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
         Hout = Hn[R - 1];
         Fout = F;
-        if (write_bot && (unsigned)(c - 1) < (unsigned)wlen) bnd_out[c - 1] = (Hout >> 16) | (Fout & 0xFFFF0000u);
+        if (write_bot && (unsigned)(c - 1) < (unsigned)wlen) {
+            CUSW_CHECK_PTR(bnd_out + c - 1, ring_a, ck_b1, "ring write");
+            // the two halves of the ring must not run into each other either
+            CUSW_CHECK_PTR(bnd_out + c - 1, bnd_out, bnd_out + ring_half, "ring write (half)");
+            bnd_out[c - 1] = (Hout >> 16) | (Fout & 0xFFFF0000u);
+        }
         {
             // columns outside the strip's range must never raise the maximum
             const bool v_lo = (unsigned)c < (unsigned)wlen, v_hi = (unsigned)(c - 1) < (unsigned)wlen;

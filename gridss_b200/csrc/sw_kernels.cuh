@@ -11,6 +11,24 @@
 
 #include "../../include/cudasw.h"
 
+// -DCUSW_BOUNDS_CHECK (python -m gridss_b200.build --check -> libcudasw_check.so): every data-dependent global-memory
+// index of the score, reverse and traceback kernels is tested against the allocation / the pair's own bytes it must stay
+// inside, and the kernel traps (the CUDA call fails, the test fails) on the first violation. compute-sanitizer is not
+// available on the GPU pool; this is the memcheck the GPU test-suite runs under instead (profiles/bounds_check_r02.log).
+#ifdef CUSW_BOUNDS_CHECK
+#include <cstdio>
+#define CUSW_CHECK_PTR(p, lo, hi, what)                                                                              \
+    do {                                                                                                             \
+        if ((const char*)(p) < (const char*)(lo) || (const char*)(p) >= (const char*)(hi)) {                         \
+            printf("CUSW_BOUNDS_CHECK: %s out of range at %s:%d (off %lld of %lld)\n", what, __FILE__, __LINE__,      \
+                   (long long)((const char*)(p) - (const char*)(lo)), (long long)((const char*)(hi) - (const char*)(lo))); \
+            __trap();                                                                                                \
+        }                                                                                                            \
+    } while (0)
+#else
+#define CUSW_CHECK_PTR(p, lo, hi, what) ((void)0)
+#endif
+
 namespace cusw {
 
 // ------------------------------------------------------------------------------------------
@@ -547,6 +565,15 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     int q = 0, w = 0, target = -1, pair = -1;
     const uint8_t* qptr = io.enc_seq;
     const uint8_t* rptr = io.enc_ref;
+#ifdef CUSW_BOUNDS_CHECK
+    const uint8_t *ck_q0 = nullptr, *ck_q1 = nullptr, *ck_r0 = nullptr, *ck_r1 = nullptr;  // this pair's own bytes
+    const uint32_t *ck_b0 = nullptr, *ck_b1 = nullptr;                                      // its strip boundary rows
+    if (active) {
+        const int pr = order[gidx];
+        ck_q0 = io.enc_seq + io.seq_off[pr]; ck_q1 = io.enc_seq + io.seq_off[pr + 1];
+        ck_r0 = io.enc_ref + io.ref_off[pr]; ck_r1 = io.enc_ref + io.ref_off[pr + 1];
+    }
+#endif
     if (active) {
         pair = order[gidx];
         int64_t qo = io.seq_off[pair], ro = io.ref_off[pair];
@@ -599,6 +626,9 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             else {
                 bnd_in = reinterpret_cast<uint32_t*>(sp.base + off);
                 bnd_out = reinterpret_cast<uint32_t*>(sp.base + off + need / 2);
+#ifdef CUSW_BOUNDS_CHECK
+                ck_b0 = bnd_in; ck_b1 = reinterpret_cast<uint32_t*>(sp.base + off + need);
+#endif
             }
         }
     }
@@ -615,6 +645,8 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 #pragma unroll
         for (int k = 0; k < R; k++) {
             int a = r0 + k, b = r0 + R + k;
+            if (a < q) CUSW_CHECK_PTR(qptr + (int64_t)a * STEP, ck_q0, ck_q1, "query row");
+            if (b < q) CUSW_CHECK_PTR(qptr + (int64_t)b * STEP, ck_q0, ck_q1, "query row");
             uint32_t qa = a < q ? (uint32_t)qptr[(int64_t)a * STEP] : kQueryPad;
             uint32_t qb = b < q ? (uint32_t)qptr[(int64_t)b * STEP] : kQueryPad;
             if (PROF) {
@@ -644,13 +676,14 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 
     // prefetch the window byte (and, when strip-mining, the boundary word) of step 0
     int c = -2 * lig;  // column of the low virtual lane at step t
+    if ((unsigned)c < (unsigned)w) CUSW_CHECK_PTR(rptr + (int64_t)c * STEP, ck_r0, ck_r1, "window column");
     uint32_t rb_next = ((unsigned)c < (unsigned)w) ? (uint32_t)rptr[(int64_t)c * STEP] : kOut;
     uint32_t top_next = 0u;  // lane 0 only: (H | F << 16) of the row above this strip at column c
     const bool read_top = MULTI && strip > 0 && lig == 0;
     const bool write_bot = MULTI && strip + 1 < nstrips && lig == G - 1;
     if (MULTI) {
         top_next = sc.BB & 0xFFFFu;
-        if (read_top && (unsigned)c < (unsigned)w) top_next = bnd_in[c];
+        if (read_top && (unsigned)c < (unsigned)w) { CUSW_CHECK_PTR(bnd_in + c, ck_b0, ck_b1, "strip boundary read"); top_next = bnd_in[c]; }
     }
 
     // ---- quiet chains (CHAIN flavours only; see qstep below)
@@ -688,10 +721,10 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         {
             int cn = c + 1;
             rb_next = kOut;
-            if ((unsigned)cn < (unsigned)w) rb_next = (uint32_t)rptr[(int64_t)cn * STEP];
+            if ((unsigned)cn < (unsigned)w) { CUSW_CHECK_PTR(rptr + (int64_t)cn * STEP, ck_r0, ck_r1, "window column"); rb_next = (uint32_t)rptr[(int64_t)cn * STEP]; }
             if (MULTI) {
                 top_next = cBB & 0xFFFFu;
-                if (read_top && (unsigned)cn < (unsigned)w) top_next = bnd_in[cn];
+                if (read_top && (unsigned)cn < (unsigned)w) { CUSW_CHECK_PTR(bnd_in + cn, ck_b0, ck_b1, "strip boundary read"); top_next = bnd_in[cn]; }
             }
         }
         Rsel = prmt(Rsel, rb, 0x3204u);  // byte1 <- old byte0, byte0 <- new
@@ -771,7 +804,10 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         Fout = F;
         if (MULTI) {
             // bottom row of the strip (hi half = last virtual lane, column c-1) -> boundary buffer
-            if (write_bot && (unsigned)(c - 1) < (unsigned)w) bnd_out[c - 1] = (Hout >> 16) | (Fout & 0xFFFF0000u);
+            if (write_bot && (unsigned)(c - 1) < (unsigned)w) {
+                CUSW_CHECK_PTR(bnd_out + c - 1, ck_b0, ck_b1, "strip boundary write");
+                bnd_out[c - 1] = (Hout >> 16) | (Fout & 0xFFFF0000u);
+            }
         }
 
         if (PROF) {
@@ -840,6 +876,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         if (!__all_sync(0xffffffffu, thr == cGOBB)) return false;
         Hdiag_top = Hin;
         rb_next = rb2;  // loaded a whole step ago
+        CUSW_CHECK_PTR(rptr + c + 2, ck_r0, ck_r1, "chained window column (c + 2)");  // unguarded by design: the chain gate keeps it inside
         rb2 = (uint32_t)rptr[c + 2];
         Rsel = Rnew;
         Hout = Hn[R - 1];
@@ -869,7 +906,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 #ifdef CUSW_STEP_STATS
                 if ((threadIdx.x & 31) == 0 && tt + 2 < t_hi) atomicAdd((unsigned long long*)(sc.pool_dev + 512) + 5, 1ull);
 #endif
-                if (tt + 2 < t_hi) rb2 = (uint32_t)rptr[c + 1];
+                if (tt + 2 < t_hi) { CUSW_CHECK_PTR(rptr + c + 1, ck_r0, ck_r1, "chained window column (c + 1)"); rb2 = (uint32_t)rptr[c + 1]; }
                 while (tt + 2 < t_hi) {  // both steps of the pair are interior
 #ifdef CUSW_NO_SKIPQ
                     if (!qstep(HA, HB)) break;
@@ -1003,11 +1040,14 @@ __device__ __forceinline__ int tb_sub(const TbConst& tc, uint32_t qb, uint32_t r
 constexpr int kTbOpsBuf = 12;
 __device__ int tb_walk(const uint8_t* dir, int width_d, int band, int readLen,
                        int refLen, uint32_t* outp, int total_ops, int center = -1, uint32_t* buf = nullptr) {
+#ifdef CUSW_BOUNDS_CHECK
+    const uint8_t* ck_d1 = dir + (long long)width_d * readLen;
+#endif
     int i = readLen - 1, j = refLen - 1;
     int e = 0, l = 0, state = 2;
     int op = 0, prev_op = 0;  // 0 = M, 1 = I, 2 = D
     auto put = [&](int idx, uint32_t v) {
-        if (outp) outp[total_ops - idx] = v;
+        if (outp) { CUSW_CHECK_PTR(outp + total_ops - idx, outp, outp + total_ops, "CIGAR word"); outp[total_ops - idx] = v; }
         if (buf && idx <= kTbOpsBuf) buf[idx - 1] = v;
     };
     while (i > 0) {
@@ -1015,6 +1055,7 @@ __device__ int tb_walk(const uint8_t* dir, int width_d, int band, int readLen,
         const int jj = j - xi;
         const int lo = max(i - band, 0) - xi, hi = min(i + band, refLen - 1) - xi;
         if (jj < lo || jj > hi) return CUDASW_EUNDEF;
+        CUSW_CHECK_PTR(dir + (int64_t)width_d * i + (center >= 0 ? j - i + center : jj), dir, ck_d1, "direction byte (walk)");
         const uint32_t b = dir[(int64_t)width_d * i + (center >= 0 ? j - i + center : jj)];
         int dv = state == 2 ? (int)(b & 7u) : state == 0 ? (2 + (int)((b >> 3) & 1u)) : (4 + (int)((b >> 4) & 1u));
         switch (dv) {
@@ -1226,7 +1267,10 @@ __device__ int tb_dp_thread(const TbConst& tc, const uint8_t* __restrict__ ref, 
                 dw |= (uint32_t)dv << (8 * (x & 3));
             }
             cur_h = nxt_h;
-            if ((x & 3) == 3 || x == WMAX - 1) { drow[x >> 2] = dw; dw = 0; }
+            if ((x & 3) == 3 || x == WMAX - 1) {
+                CUSW_CHECK_PTR(drow + (x >> 2), dir, dir + (long long)WP * readLen, "direction word (one-thread DP)");
+                drow[x >> 2] = dw; dw = 0;
+            }
         }
         // slide the window bytes: the frame of row i+1 starts one column further right
 #pragma unroll

@@ -138,11 +138,14 @@ __device__ int tb_dp_warp2(const TbConst& tc, const uint8_t* __restrict__ ref, c
                     if (x == 0) { first_h = h; first_e = e; }
                     out_h = h; out_f = fgap;
                     if (D >= 4) { dw |= (uint32_t)dv << (8 * (x & 3)); any = true; }
-                    else drow[kb + X0 + x] = dv;
+                    else { CUSW_CHECK_PTR(drow + kb + X0 + x, dir, dir + (long long)Wp * readLen, "direction byte (cooperative DP)"); drow[kb + X0 + x] = dv; }
                 }
                 cur_h = nh;
                 if (D >= 4 && (x & 3) == 3) {
-                    if (any) *reinterpret_cast<uint32_t*>(drow + kb + X0 + x - 3) = dw;
+                    if (any) {
+                        CUSW_CHECK_PTR(drow + kb + X0 + x, dir, dir + (long long)Wp * readLen, "direction word (cooperative DP)");
+                        *reinterpret_cast<uint32_t*>(drow + kb + X0 + x - 3) = dw;
+                    }
                     dw = 0; any = false;
                 }
             }
@@ -228,6 +231,7 @@ __device__ int tb_dp_warp_mem(const TbConst& tc, const uint8_t* __restrict__ ref
                     int h, e;
                     uint8_t dv;
                     tb_cell(tc, i, up_h, up_e, hdiag, tb_sub(tc, qb, (uint32_t)ref[j]), hleft, fgap, mx, h, e, dv);
+                    CUSW_CHECK_PTR(drow + j, dir, dir + (long long)Wp * readLen, "direction byte (memory-backed DP)");
                     drow[j] = dv;
                     row[kb + x] = make_int2(h, e);
                     if (x == 0) { first_h = h; first_e = e; }
@@ -256,17 +260,23 @@ __device__ int tb_walk_warp(const uint8_t* dir, int width_d, int band, int readL
     int op = 0, prev_op = 0;  // 0 = M, 1 = I, 2 = D
     auto put = [&](int idx, uint32_t v) {
         if (lane == 0) {
-            if (outp) outp[total_ops - idx] = v;
+            if (outp) { CUSW_CHECK_PTR(outp + total_ops - idx, outp, outp + total_ops, "CIGAR word"); outp[total_ops - idx] = v; }
             if (buf && idx <= kTbOpsBuf) buf[idx - 1] = v;
         }
     };
+#ifdef CUSW_BOUNDS_CHECK
+    const uint8_t* ck_d1 = dir + (long long)width_d * readLen;
+#endif
     auto in_band = [&](int ii, int jj) { return jj >= max(ii - band, 0) && jj <= min(ii + band, refLen - 1); };
     while (i > 0) {
         if (state == 2) {
             // lane x looks at cell (i - x, j - x)
             const int ii = i - lane, jj = j - lane;
             bool diag = false;
-            if (ii > 0 && in_band(ii, jj)) diag = (dir[(long long)width_d * ii + (jj - ii + band)] & 7u) == 1u;
+            if (ii > 0 && in_band(ii, jj)) {
+                CUSW_CHECK_PTR(dir + (long long)width_d * ii + (jj - ii + band), dir, ck_d1, "direction byte (cooperative walk)");
+                diag = (dir[(long long)width_d * ii + (jj - ii + band)] & 7u) == 1u;
+            }
             const uint32_t bal = __ballot_sync(0xffffffffu, diag);
             const uint32_t run = bal == 0xffffffffu ? 32u : (uint32_t)(__ffs((int)~bal) - 1);  // leading diagonal cells (0..32)
             if (run > 0) {
@@ -278,6 +288,7 @@ __device__ int tb_walk_warp(const uint8_t* dir, int width_d, int band, int readL
             }
         }
         if (!in_band(i, j)) return CUDASW_EUNDEF;
+        CUSW_CHECK_PTR(dir + (long long)width_d * i + (j - i + band), dir, ck_d1, "direction byte (cooperative walk)");
         const uint32_t b = dir[(long long)width_d * i + (j - i + band)];
         const int dv = state == 2 ? (int)(b & 7u) : state == 0 ? (2 + (int)((b >> 3) & 1u)) : (4 + (int)((b >> 4) & 1u));
         switch (dv) {

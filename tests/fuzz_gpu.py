@@ -59,6 +59,25 @@ def main():
     use_ref = args.checker == "reference" and O.have_reference()
     check = O.ref_align_blobs if use_ref else O.model_align_blobs
     al = g.CudaAligner()
+    calls = {"ascii": 0, "packed": 0}
+
+    class _Alt:
+        """every other batch goes through the packed host entry point (cudasw_align_batch_packed)"""
+
+        def align_blobs(self, sb, so, rb, ro):
+            if (calls["ascii"] + calls["packed"]) % 2 == 0:
+                calls["ascii"] += 1
+                return al_raw.align_blobs(sb, so, rb, ro)
+            calls["packed"] += 1
+            s2, sn, _ = g.pack_bases(sb, n=int(so[-1]), threads=8)
+            r2, rn, _ = g.pack_bases(rb, n=int(ro[-1]), threads=8)
+            return al_raw.align_blobs_packed(s2, sn, so, r2, rn, ro)
+
+        def close(self):
+            al_raw.close()
+
+    al_raw, al = al, None
+    al = _Alt()
     plan = [(1, 200000), (2, 60000), (4, 100000), (3, 30000)]
     kinds = ["random", "mutated", "two_letter", "homopolymer", "dinuc", "tandem", "subst_block", "with_n", "zero", "tiny", "q_gt_w", "indel_heavy"]
     tot = {"pairs": 0, "cells": 0.0, "mismatches": 0, "undefined_in_reference": 0, "by_source": {}}
@@ -150,6 +169,7 @@ def main():
                 examples.append({"source": kind, "seed": 1000 + rnd, "pair": first})
     tot["checker"] = ("libsswjni.so as shipped by the reference" if use_ref else "oracle/ssw_model.c") + f", {cores} host threads"
     tot["rounds"] = rnd
+    tot["entry_points"] = calls
     tot["examples"] = examples
     print(json.dumps(tot), flush=True)
     al.close()
