@@ -28,6 +28,7 @@ CUDASW_ENOMEM = -2
 CUDASW_ECUDA = -3
 CUDASW_ETOOLARGE = -4
 CUDASW_EUNDEF = -5
+TIEBREAK_SSW, TIEBREAK_JALIGNER = 0, 1
 
 RESULT_DTYPE = np.dtype(
     [
@@ -88,6 +89,7 @@ _lib_lock = threading.Lock()
 _vp, _i64, _i32, _sz = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, ctypes.c_size_t
 ABI = [
     ("cudasw_create", ctypes.c_int, [ctypes.POINTER(_Scoring), ctypes.c_int, ctypes.POINTER(_vp)]),
+    ("cudasw_create_ex", ctypes.c_int, [ctypes.POINTER(_Scoring), ctypes.c_int, ctypes.c_int, ctypes.POINTER(_vp)]),
     ("cudasw_destroy", None, [_vp]),
     ("cudasw_align_batch", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
     ("cudasw_align_batch_packed", ctypes.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, ctypes.POINTER(_i64)]),
@@ -253,13 +255,15 @@ class PinnedBuffer:
 class CudaAligner(Aligner):
     """The drop-in for SswJniAligner (alignment/SswJniAligner.java:8-61) on one B200."""
 
-    def __init__(self, match=1, mismatch=-4, ambiguous=-4, gapOpen=6, gapExtend=1, device: int = 0):
+    def __init__(self, match=1, mismatch=-4, ambiguous=-4, gapOpen=6, gapExtend=1, device: int = 0, tie_break: str = "ssw"):
+        """tie_break: "ssw" = bit-compatible with SswJniAligner (the reference's default backend); "jaligner" = with
+        JAlignerAligner, its --nojni fallback (unpinned: no JVM here; see include/cudasw.h)."""
         lib = load_library()
         self._lib = lib
         self.scoring = (match, mismatch, ambiguous, gapOpen, gapExtend)
         sc = _Scoring(match, mismatch, ambiguous, gapOpen, gapExtend)
         h = ctypes.c_void_p()
-        rc = lib.cudasw_create(ctypes.byref(sc), device, ctypes.byref(h))
+        rc = lib.cudasw_create_ex(ctypes.byref(sc), device, {"ssw": TIEBREAK_SSW, "jaligner": TIEBREAK_JALIGNER}[tie_break], ctypes.byref(h))
         if rc != 0:
             msg = (lib.cudasw_last_error(None) or b"").decode()
             if rc == CUDASW_EINVAL:

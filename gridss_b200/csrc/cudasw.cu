@@ -26,6 +26,7 @@
 #define CUSW_MAIN_TU 1  // non-template kernels are emitted in this translation unit only
 #include "sw_kernels.cuh"
 #include "rev_band.cuh"
+#include "ja_mode.cuh"
 #include "variants.h"
 
 using namespace cusw;
@@ -208,6 +209,8 @@ struct cudasw {
     int forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* d_so, const int64_t* d_ro, uint64_t* launches_out);
     int post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out,
                    bool ends_only = false);
+    int post_chunk_ja(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out);
+    int tie_break = CUDASW_TIEBREAK_SSW;
     int size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off, int64_t rev_first, int64_t rev_cnt);
     float last_post_ms = 0.f;
     int run(int64_t n, const uint8_t* d_seq, const int64_t* d_seq_off, const uint8_t* d_ref,
@@ -237,8 +240,16 @@ extern "C" const char* cudasw_last_error(cudasw_t* h) {
 }
 
 extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out) {
+    return cudasw_create_ex(s, device, CUDASW_TIEBREAK_SSW, out);
+}
+
+extern "C" int cudasw_create_ex(const cudasw_scoring* s, int device, int tie_break, cudasw_t** out) {
     if (!out) return CUDASW_EINVAL;
     *out = nullptr;
+    if (tie_break != CUDASW_TIEBREAK_SSW && tie_break != CUDASW_TIEBREAK_JALIGNER) {
+        g_create_error = "unknown tie-break mode";
+        return CUDASW_EINVAL;
+    }
     cudasw_scoring sc = {1, -4, -4, 6, 1};  // AlignerFactory.java:90
     if (s) sc = *s;
     // ssw.Aligner.align argument checks (jar bytecode)
@@ -270,6 +281,7 @@ extern "C" int cudasw_create(const cudasw_scoring* s, int device, cudasw_t** out
     cudasw_t* h = new cudasw();
     h->device = device;
     h->scoring = sc;
+    h->tie_break = tie_break;
     auto fail = [&](const std::string& m) {
         g_create_error = m;
         delete h;
@@ -793,6 +805,80 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
     return CUDASW_OK;
 }
 
+// JAligner-compatible mode (ja_mode.cuh): no reverse pass; a banded pointer DP from row 0 to the end cell and jaligner's
+// walk, one CTA per pair, with the same scratch pool / retry rounds as the SSW traceback.
+int cudasw::post_chunk_ja(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap,
+                          uint64_t* launches_out) {
+    cudaStream_t st = post_set.main;
+    CK(cudaStreamWaitEvent(st, chunk_ev[ci].fwd1, 0));
+    uint64_t launches = 0;
+    PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
+    int4* fwd_c = fwd.p + first;
+    cudasw_result* res_c = res.p + first;
+    uint32_t* keys_c = keys.p + first; uint32_t* keys_alt_c = keys_alt.p + first;
+    int* vals_c = vals.p + first; int* vals_alt_c = vals_alt.p + first;
+    int* retry_a_c = retry_a.p + first; int* retry_b_c = retry_b.p + first;
+    size_t cub_bytes = cub_tmp_post.cap;
+    CK(cudaEventRecord(ev[3], st));
+    CK(cudaEventRecord(ev[4], st));  // (no reverse pass in this mode)
+    TbPool pool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+    int* retry_count = reinterpret_cast<int*>(d_counters + 2);
+    int* dh = d_hist + 128;
+    int* slots = d_rev_slots + 32;
+    const int* list = nullptr;
+    int c = (int)n;
+    int* retry_out = retry_a_c;
+    bool stuck = false;
+    for (int round = 0; round < 256 && c > 0; round++) {
+        CK(cudaMemsetAsync(d_counters, 0, sizeof(unsigned long long), st));          // pool
+        CK(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned long long), st));      // retry counter
+        CK(cudaMemsetAsync(d_counters + 7, 0, sizeof(unsigned long long), st));      // scratch estimate
+        CK(cudaMemsetAsync(dh, 0, 8 * sizeof(int), st));
+        ja_keys_kernel<<<(c + 255) / 256, 256, 0, st>>>(list, c, io, fwd_c, res_c, tc, keys_c, vals_c, dh, d_counters + 7);
+        CK(cub::DeviceRadixSort::SortPairs(cub_tmp_post.p, cub_bytes, keys_c, keys_alt_c, vals_c, vals_alt_c, c, 0, 22, st));
+        slot_scan_kernel<<<1, 32, 0, st>>>(dh, 3, slots);
+        launches += 5;
+        sw_ja_traceback_kernel<kJaSmallD><<<std::min(c, 148 * 8), 128, 0, st>>>(vals_alt_c, slots + 0, io, fwd_c, tc, pool, res_c, cig.p,
+                                                                               (unsigned long long)cigar_cap, d_counters + 1, retry_out, retry_count);
+        sw_ja_traceback_kernel<kJaBigD><<<std::min(c, 148 * 2), 128, 0, st>>>(vals_alt_c, slots + 2, io, fwd_c, tc, pool, res_c, cig.p,
+                                                                             (unsigned long long)cigar_cap, d_counters + 1, retry_out, retry_count);
+        launches += 2;
+        CK(cudaEventRecord(ev[5], st));
+        CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        const int nretry = *reinterpret_cast<int*>(h_counters + 2);
+        if (nretry == 0) { c = 0; break; }
+        if (nretry == c && stuck) { set_error("traceback scratch pool too small"); return CUDASW_ENOMEM; }
+        stuck = nretry == c;
+        {
+            // every pair keeps a pointer byte per band cell: let the pool grow towards what a round asks for
+            const unsigned long long est = h_counters[7] + ((unsigned long long)64 << 20);
+            if (est > tb_pool_bytes && !getenv("CUDASW_TB_POOL_MB")) {
+                size_t free_b = 0, total_b = 0;
+                CK(cudaMemGetInfo(&free_b, &total_b));
+                const size_t want = (size_t)std::min<unsigned long long>(est, (unsigned long long)((free_b + tb_pool_bytes) / 2));
+                if (want > tb_pool_bytes) {
+                    tb_pool.release();
+                    tb_pool_bytes = 0;
+                    CK(tb_pool.ensure(want));
+                    tb_pool_bytes = want;
+                    pool = TbPool{tb_pool.p, (unsigned long long)tb_pool_bytes, d_counters};
+                    stuck = false;
+                }
+            }
+        }
+        list = retry_out;
+        retry_out = (retry_out == retry_a_c) ? retry_b_c : retry_a_c;
+        c = nretry;
+    }
+    if (c > 0) { set_error("traceback did not converge"); return CUDASW_ENOMEM; }
+    CK(cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev[4], ev[5]); stats.ms_traceback += ms; last_post_ms = ms;
+    *launches_out += launches;
+    return CUDASW_OK;
+}
+
 // Boundary rows of the strip-mined score variants (queries above the tallest single-strip variant): two rows of one
 // 32-bit word per window column and pair. The forward buffer is sized for the chunk [first, first + cnt) whose forward
 // pass is about to be queued; the reverse buffer for `rev_first`/`rev_cnt`, the range ONE post_chunk call walks (the whole
@@ -1057,7 +1143,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         if (rc == CUDASW_OK) rc = size_strip_buffers(c.first, c.cnt, h_seq_off, h_ref_off, post_per_chunk ? c.first : 0, post_per_chunk ? c.cnt : (i == 0 ? n : 0));
         if (rc == CUDASW_OK) rc = forward_chunk(i, c.first, c.cnt, d_so, d_ro, &launches);
         if (rc == CUDASW_OK && serial) rc = cudaStreamSynchronize(st) == cudaSuccess ? CUDASW_OK : CUDASW_ECUDA;
-        if (rc == CUDASW_OK && post_per_chunk && i > 0) rc = post_chunk(i - 1, chunks[i - 1].first, chunks[i - 1].cnt, d_so, d_ro, cigar_cap, &launches, ends_only);
+        if (rc == CUDASW_OK && post_per_chunk && tie_break == CUDASW_TIEBREAK_SSW && i > 0) rc = post_chunk(i - 1, chunks[i - 1].first, chunks[i - 1].cnt, d_so, d_ro, cigar_cap, &launches, ends_only);
         if (rc != CUDASW_OK) { drain(); return rc; }
     }
     {
@@ -1065,8 +1151,9 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         // pass was measured slower on B200 (C2: 253 vs 237 ms per 1 M pairs): their latency-bound CTAs displace
         // forward CTAs that fill the register file. CUDASW_POST_PER_CHUNK=1 keeps that experiment available.
         const Chunk& c = chunks.back();
-        int rc = post_per_chunk ? post_chunk(chunks.size() - 1, c.first, c.cnt, d_so, d_ro, cigar_cap, &launches, ends_only)
-                                : post_chunk(chunks.size() - 1, 0, n, d_so, d_ro, cigar_cap, &launches, ends_only);
+        int rc = tie_break == CUDASW_TIEBREAK_JALIGNER ? post_chunk_ja(chunks.size() - 1, 0, n, d_so, d_ro, cigar_cap, &launches)
+                 : post_per_chunk ? post_chunk(chunks.size() - 1, c.first, c.cnt, d_so, d_ro, cigar_cap, &launches, ends_only)
+                                  : post_chunk(chunks.size() - 1, 0, n, d_so, d_ro, cigar_cap, &launches, ends_only);
         if (rc != CUDASW_OK) { drain(); return rc; }
     }
     CK(cudaEventRecord(ev[5], st));
@@ -1326,6 +1413,7 @@ extern "C" int cudasw_breakpoint_homology(cudasw_t* h, int64_t n, const cudasw_b
         return CUDASW_EINVAL;
     }
     if (n == 0) return CUDASW_OK;
+    if (h->tie_break != CUDASW_TIEBREAK_SSW) { h->set_error("cudasw_breakpoint_homology needs the SSW tie-break mode"); return CUDASW_EINVAL; }
     if (ins_off && (ins_off[0] != 0 || (!ins_blob && ins_off[n] > 0))) { h->set_error("bad inserted-sequence blob"); return CUDASW_EINVAL; }
     std::lock_guard<std::mutex> hom_lock(h->hom_mu);
     std::shared_lock<std::shared_mutex> ref_lock(h->ref_mu);

@@ -80,6 +80,19 @@ typedef struct cudasw_stats {
 int cudasw_create(const cudasw_scoring* scoring, int device, cudasw_t** out);
 void cudasw_destroy(cudasw_t* h);
 
+/* Which of the reference's CPU backends the results are bit-compatible with.
+ * CUDASW_TIEBREAK_SSW (what cudasw_create gives): SswJniAligner, the reference's default (AlignerFactory.java:108-117).
+ * CUDASW_TIEBREAK_JALIGNER: JAlignerAligner (alignment/JAlignerAligner.java:30-93), the fallback under --nojni /
+ *   -Dsswjni.disable=true: same score and end cell, but jaligner's pointer walk - DIAGONAL, then the gap in the read
+ *   (`D`), then `I`; a gap is extended only when that is strictly better than opening; the walk runs until H == 0, i.e.
+ *   the longest zero-free start - and its CIGAR assembly ("0M<q>S" for score 0, start 0). UNPINNED: jaligner ships as
+ *   class files only and no JVM is available; tested against the restatement oracle/jaligner_model.py. Sequences are
+ *   clean()ed as in the SSW mode, which equals JAlignerAligner's raw-byte matrix for A/C/G/T/N in either case only.
+ *   Limits: bands above 8192 diagonals -> per-pair CUDASW_ETOOLARGE; cudasw_breakpoint_homology is SSW-mode only. */
+#define CUDASW_TIEBREAK_SSW 0
+#define CUDASW_TIEBREAK_JALIGNER 1
+int cudasw_create_ex(const cudasw_scoring* scoring, int device, int tie_break, cudasw_t** out);
+
 /* Batched Aligner.align_smith_waterman (Aligner.java:10): pair i aligns
  * seq_blob[seq_off[i]..seq_off[i+1]) inside ref_blob[ref_off[i]..ref_off[i+1]).
  * Bytes are raw ASCII in any case; the clean() map of SswJniAligner.java:71-79 (upper-case,

@@ -611,3 +611,95 @@ def test_packed_inputs_multi_handle(aligner, synth):
     resm, cigm = ma.align_blobs_packed(s2, sn, so, r2, rn, ro)
     _same(res1, cig1, resm, cigm)
     ma.close()
+
+
+# ---- JAligner-compatible tie-break mode (cudasw_create_ex(..., CUDASW_TIEBREAK_JALIGNER)). UNPINNED: the
+# checker is oracle/jaligner_model.py, a restatement of jaligner 1.0's published algorithm (class files only, no JVM).
+def _ja_expected(seqs, refs, scoring=(1, -4, -4, 6, 1)):
+    from oracle import jaligner_model as J
+
+    return [J.align(s, r, *scoring) for s, r in zip(seqs, refs)]
+
+
+def _ja_check(al, seqs, refs, scoring=(1, -4, -4, 6, 1)):
+    import gridss_b200 as gb
+    from gridss_b200.aligner import pack
+
+    sb, so = pack(seqs)
+    rb, ro = pack(refs)
+    res, cig = al.align_blobs(sb, so, rb, ro)
+    want = _ja_expected(seqs, refs, scoring)
+    bad = []
+    for i, (sc, st, cg, ref_end, read_end) in enumerate(want):
+        r = res[i]
+        got = (int(r["status"]), int(r["score"]), int(r["ref_begin"]), gb.cigar_string(cig[r["cigar_off"]: r["cigar_off"] + r["cigar_len"]]))
+        exp = (0, sc, st, cg)
+        if got != exp or (sc > 0 and (int(r["ref_end"]), int(r["read_end"])) != (ref_end, read_end)):
+            bad.append((i, got, exp, seqs[i][:40], refs[i][:40]))
+    return bad
+
+
+def test_jaligner_mode_contract_vectors():
+    import gridss_b200 as gb
+
+    al = gb.CudaAligner(tie_break="jaligner")
+    # SmithWatermanAlignerTest.java:13-35, run by the reference against every backend (JAlignerAlignerTest)
+    for seq, ref, start, cigar in ((b"AAACCCCCCCCCCCCCTTAATTAATTAATTTT", b"AAACCCCCCCCCCCCCGTTAATTAATTAATTTT", 0, "16M1D16M"),
+                                   (b"AACCCTTTTTT", b"AAACCCTTTTTT", 1, "11M"), (b"GGGGGGTTTTTT", b"AAACCCTTTTTT", 6, "6S6M")):
+        a = al.align_smith_waterman(seq, ref)
+        assert (a.getStartPosition(), a.getCigar()) == (start, cigar)
+    a = al.align_smith_waterman(b"AAAA", b"CCCCCC")  # no positive cell: alignmentToCigar still appends its (empty) last run
+    assert (a.getStartPosition(), a.getCigar(), a.score) == (0, "0M4S", 0)
+    al.close()
+
+
+@pytest.mark.parametrize("kind", ["random", "mutated", "two_letter", "homopolymer", "dinuc", "tandem", "subst_block", "zero",
+                                  "tiny", "q_gt_w", "indel_heavy"])
+def test_jaligner_mode_vs_restatement(synth, kind):
+    import gridss_b200 as gb
+
+    al = gb.CudaAligner(tie_break="jaligner")
+    for seed, qmax, wmax, n in ((31, 60, 140, 250), (32, 260, 420, 40)):
+        seqs, refs = synth.adversarial(kind, n, seed=seed, qmax=qmax, wmax=wmax)
+        bad = _ja_check(al, seqs, refs)
+        assert bad == [], bad[:3]
+    al.close()
+
+
+def test_jaligner_mode_other_scoring_and_n(synth):
+    """gap extension free / cheaper to open than to extend (the open-beats-extend tie rule), and N in both sequences"""
+    import gridss_b200 as gb
+
+    rng = np.random.default_rng(5)
+    for sc in ((2, -6, -1, 5, 3), (3, -2, -5, 4, 0), (1, -1, -1, 2, 1), (1, -4, -4, 1, 3)):
+        al = gb.CudaAligner(*sc, tie_break="jaligner")
+        seqs, refs = [], []
+        for kind in ("mutated", "indel_heavy", "tandem"):
+            s, r = synth.adversarial(kind, 60, seed=41, qmax=70, wmax=150)
+            seqs += s
+            refs += r
+        for _ in range(60):  # ACGTN only, either case: where clean() and jaligner's raw-byte matrix agree
+            r = rng.choice(list(b"ACGTNacgtn"), size=int(rng.integers(20, 120))).astype(np.uint8).tobytes()
+            st = int(rng.integers(0, len(r) // 2))
+            seqs.append(r[st: st + int(rng.integers(5, 60))].swapcase())
+            refs.append(r)
+        bad = _ja_check(al, seqs, refs, sc)
+        assert bad == [], (sc, bad[:3])
+        al.close()
+
+
+def test_jaligner_mode_shares_score_and_end_with_ssw_mode(aligner, synth):
+    import gridss_b200 as gb
+
+    al = gb.CudaAligner(tie_break="jaligner")
+    sb, so, rb, ro = synth.generate(4, 3000)
+    a, _ = aligner.align_blobs(sb, so, rb, ro)
+    b, _ = al.align_blobs(sb, so, rb, ro)
+    assert (b["status"] == 0).all()
+    for f in ("score", "ref_end", "read_end"):
+        assert np.array_equal(a[f], b[f]), f
+    # SSW reports the start column nearest the end among all full-score alignments; jaligner's walk ends in one of them
+    ok = a["score"] > 0
+    assert (b["ref_begin"][ok] <= a["ref_begin"][ok]).all()
+    assert (b["ref_begin"] == a["ref_begin"]).mean() > 0.9
+    al.close()
