@@ -7,7 +7,7 @@
 // the end along the pointers - whole gaps at a time, a gap being extended only when extending is STRICTLY better than
 // opening - until a STOP pointer. So: same score and end cell as SSW, but the LONGEST zero-free start instead of SSW's
 // nearest one, open-beats-extend on ties, and no band rule. PARITY UNPINNED: the arithmetic ships as class files only
-// (jaligner-1.0.jar) and this image has no JVM; the kernel is tested against oracle/jaligner_model.py, the restatement
+// (jaligner-1.0.jar) and this image has no JVM; the kernel is tested (tests/test_gpu_parity.py) against the CPU restatement
 // of that published algorithm, and the three contract vectors the reference runs against every backend. Symbols go
 // through the same clean() encoding as the SSW mode, which is what JAlignerAligner's raw-byte matrix gives for
 // A, C, G, T, N in either case (other IUPAC letters score differently there; documented limit).
