@@ -69,6 +69,55 @@ def full_capture(rep, name, title, cmd, notes=""):
     return {k: v[h.index(k)] for k in h if k in KEYS}
 
 
+def alu_mix(tag, m, cmd_pairs=50000, q=300, w=4000):
+    """profiles/fwd_alu_mix.json: ALU-pipe lane-ops per DP cell and DRAM bytes per pair of the forward kernel, from the
+    --set full capture (bench.py reads it for roofline.alu_pipe_frac / roofline.traffic)."""
+    import json
+
+    def f(k):
+        return float(str(m[k]).replace(",", ""))
+
+    cyc, alu = f("sm__cycles_elapsed.avg"), f("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active") / 100.0
+    smsps = 148 * 4
+    warp_inst = alu * cyc * smsps * 0.5  # the ALU pipe takes one warp instruction every other clock (16 lanes)
+    cells = float(cmd_pairs) * q * w
+    rd, wr = f("dram__bytes_read.sum"), f("dram__bytes_write.sum")  # Mbyte
+    out = {"alu_lane_ops_per_cell": round(warp_inst * 32 / cells, 3), "dram_bytes_per_pair": round((rd + wr) * 1e6 / cmd_pairs, 1),
+           "source": f"profiles/ncu_fwd_{tag}.md",
+           "how": f"sm__inst_executed_pipe_alu {alu * 100:.3f} % x sm__cycles_elapsed {cyc:.0f} x {smsps} SMSPs x 0.5 warp-inst/clk (16-lane ALU pipe) x 32 lanes / "
+                  f"({cmd_pairs} pairs x {q} x {w} cells); dram__bytes_read+write {rd + wr:.2f} MB / {cmd_pairs} pairs"}
+    json.dump(out, open(os.path.join(P, "fwd_alu_mix.json"), "w"), indent=1)
+    print("fwd_alu_mix", out)
+
+
+if __name__ == "__main__" and len(sys.argv) > 4 and sys.argv[1] == "one":
+    # python tools/profile_summaries.py one <rep in gpurun_out> <md under profiles> <title> [command]
+    m = full_capture(sys.argv[2], sys.argv[3], sys.argv[4], sys.argv[5] if len(sys.argv) > 5 else "")
+    print({k: m[k] for k in list(m)[:10]})
+    sys.exit(0)
+
+if __name__ == "__main__" and len(sys.argv) > 2 and sys.argv[2] == "r02":
+    # round 2 session (tools/gpu_session3.sh)
+    tag = sys.argv[1]
+    cmd = "python bench.py --steps 2 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows --no-homology --no-worst-case"
+    launch_list(tag, cmd)
+    caps = [("fwd", "forward score kernel (C2, chained query-profile flavour)", "sw_score_kernel -s 2", cmd),
+            ("rev", "banded reverse pass (C2)", "sw_rev_band_kernel -s 3", cmd),
+            ("unpack", "unpack kernel (packed host inputs -> encoded bytes; load phase of the packed path)", "unpack_kernel -s 3", cmd),
+            ("tb", "one-thread traceback kernel (C2)", "sw_traceback_kernel -s 12", cmd),
+            ("tbwarp", "one-warp-per-pair cooperative traceback (C3, 200 k pairs)", "sw_traceback_warp_kernel -s 5", "python tools/bench_configs.py 3:200000"),
+            ("tbcta", "CTA-per-pair cooperative traceback (C5, 1000 pairs)", "sw_traceback_block_kernel -s 1", "python tools/bench_configs.py 5:1000"),
+            ("fwdstrip", "strip-mined forward kernel (C5: 10 kb contigs, one warp per pair)", "'sw_score_kernel<32' -s 1", "python tools/bench_configs.py 5:1000"),
+            ("revc5", "banded reverse pass, one warp per pair (C5)", "'sw_rev_band_kernel<32' -s 1", "python tools/bench_configs.py 5:1000")]
+    for name, title, kre, c in caps:
+        rep = f"prof_{name}_{tag}.ncu-rep"
+        if os.path.exists(os.path.join(O, rep)):
+            m = full_capture(rep, f"ncu_{name}_{tag}.md", title, f"ncu --set full --clock-control none --import-source on -k regex:{kre} -c 1 {c}")
+            print(name, {k: m[k] for k in list(m)[:8]})
+            if name == "fwd":
+                alu_mix(tag, m)
+    sys.exit(0)
+
 if __name__ == "__main__":
     tag = sys.argv[1]
     cmd = "python bench.py --steps 2 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows --no-homology"
