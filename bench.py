@@ -162,6 +162,7 @@ def main():
     ap.add_argument("--no-homology", action="store_true", help="skip the caller-level line (cudasw_breakpoint_homology)")
     ap.add_argument("--homology-breakpoints", type=int, default=500000)
     ap.add_argument("--no-worst-case", action="store_true", help="skip the zero-quiet-steps forward line")
+    ap.add_argument("--no-int-peak", action="store_true", help="do not run tools/int_peak (keeps an ncu launch list to the library's own kernels)")
     ap.add_argument("--worst-case-pairs", type=int, default=1_000_000)
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
@@ -424,7 +425,7 @@ def main():
         # the integer pipes measured on THIS box in THIS run (tools/int_peak.cu, dependent-free asm streams, < 1 s)
         measured = {}
         ip = os.path.join(ROOT, "tools", "int_peak")
-        if os.path.exists(ip):
+        if os.path.exists(ip) and not args.no_int_peak:
             try:
                 env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(local) if "CUDA_VISIBLE_DEVICES" not in os.environ else os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local])
                 measured = json.loads(subprocess.run([ip], capture_output=True, text=True, timeout=120, env=env).stdout.strip().splitlines()[-1])

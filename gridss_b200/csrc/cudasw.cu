@@ -121,6 +121,8 @@ struct cudasw {
         cudaEvent_t fork_ev = nullptr, join_ev[kAux]{};
     };
     StreamSet fwd_set, post_set;  // fwd_set.main == stream
+    cudaStream_t tb_streams[5]{};  // the one-thread traceback classes run side by side (post_chunk)
+    cudaEvent_t tb_join[5]{};
     cudaStream_t pack_stream = nullptr;  // encode / bin of chunk i+1 while chunk i is in its forward pass
     struct ChunkEvents { cudaEvent_t pack0, enc1, pack1, fwd0, fwd1; };
     std::vector<ChunkEvents> chunk_ev;
@@ -312,6 +314,14 @@ extern "C" int cudasw_create_ex(const cudasw_scoring* s, int device, int tie_bre
                 if ((e = cudaEventCreateWithFlags(&j, cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
         }
     }
+    {
+        int lo_pri = 0, hi_pri = 0;
+        cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri);
+        for (int k = 0; k < 5; k++) {
+            if ((e = cudaStreamCreateWithPriority(&h->tb_streams[k], cudaStreamNonBlocking, hi_pri)) != cudaSuccess) return fail(cudaGetErrorString(e));
+            if ((e = cudaEventCreateWithFlags(&h->tb_join[k], cudaEventDisableTiming)) != cudaSuccess) return fail(cudaGetErrorString(e));
+        }
+    }
     if ((e = cudaMalloc(&h->d_strip, 4 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_rev_slots, 64 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
@@ -412,6 +422,10 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
         for (auto& a : ss->aux) if (a) { cudaStreamSynchronize(a); cudaStreamDestroy(a); }
         if (ss->fork_ev) cudaEventDestroy(ss->fork_ev);
         for (auto& j : ss->join_ev) if (j) cudaEventDestroy(j);
+    }
+    for (int k = 0; k < 5; k++) {
+        if (h->tb_streams[k]) { cudaStreamSynchronize(h->tb_streams[k]); cudaStreamDestroy(h->tb_streams[k]); }
+        if (h->tb_join[k]) cudaEventDestroy(h->tb_join[k]);
     }
     if (h->post_set.main) { cudaStreamSynchronize(h->post_set.main); cudaStreamDestroy(h->post_set.main); }
     if (h->pack_stream) { cudaStreamSynchronize(h->pack_stream); cudaStreamDestroy(h->pack_stream); }
@@ -731,29 +745,53 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
                 CK(cudaEventRecord(join_ev[1], aux[1]));
             }
             {
-                // One launch per frame class, narrowest first: class k appends the pairs that outgrow its frame to the
-                // escalation list that class k+1 reads behind its own (sorted) list, and the widest class hands over to
-                // a second warp-kernel launch, all stream-ordered. Class slot 5 = pairs with nothing to trace.
+                // One launch per frame class over its own (sorted) list, all classes side by side on their own streams: each is
+                // latency-bound (one thread per pair, a few hundred registers' worth of frame) and leaves most of the machine
+                // idle on its own. A pair that outgrows its frame is appended to the escalation list of the next wider class;
+                // those lists are drained afterwards, narrowest first (each drain may append to the next), and the widest
+                // class hands over to the warp kernels. Class slot 5 = pairs with nothing to trace.
                 const int grid = std::min((c + 127) / 128, 148 * 8);
-                for (int k = 0; k <= kTbClasses; k++) {
+#define CUSW_TB_LAUNCH(B, STREAM, SLOT, ESC_IN, ESC_IN_COUNT)                                                                                    \
+    sw_traceback_kernel<B><<<grid, 128, 0, STREAM>>>(vals_alt.p, 0, ESC_IN, ESC_IN_COUNT, esc_out, esc_out_count, io, fwd_c, rev_c, tc, pool, res_c, \
+                                                     cig.p, ccap, d_counters + 1, retry_out, retry_count, tb_band.p, SLOT)
+                // own lists: classes 1.. on their streams first, class 0 on the main stream
+                for (int kk = 1; kk <= kTbClasses + 1; kk++) {
+                    const int k = kk <= kTbClasses ? kk : 0;
                     const bool none = k == kTbClasses;  // score 0 / failed pairs: "1M(q-1)S" or nothing; any class will do
-                    const int* esc_in = (k == 0 || none) ? nullptr : tb_esc.p + (size_t)k * c;
-                    const int* esc_in_count = (k == 0 || none) ? nullptr : dh + 8 + k;
                     int* esc_out = none ? tb_esc.p : tb_esc.p + (size_t)(k + 1) * c;
                     int* esc_out_count = none ? dh + 8 : dh + 8 + k + 1;
-#define CUSW_TB_LAUNCH(B)                                                                                                           \
-    sw_traceback_kernel<B><<<grid, 128, 0, st>>>(vals_alt.p, 0, esc_in, esc_in_count, esc_out, esc_out_count, io, fwd_c, rev_c, tc, pool, res_c, \
-                                                 cig.p, ccap, d_counters + 1, retry_out, retry_count, tb_band.p, tb_slots + 6 + 2 * k)
+                    cudaStream_t sk = k == 0 ? st : tb_streams[k - 1];
+                    if (k > 0) CK(cudaStreamWaitEvent(sk, fork_ev, 0));
                     switch (k) {
-                        case 1: CUSW_TB_LAUNCH(2); break;
-                        case 2: CUSW_TB_LAUNCH(4); break;
-                        case 3: CUSW_TB_LAUNCH(8); break;
-                        case 4: CUSW_TB_LAUNCH(16); break;
-                        default: CUSW_TB_LAUNCH(1); break;
+                        case 1: CUSW_TB_LAUNCH(2, sk, tb_slots + 6 + 2 * k, nullptr, nullptr); break;
+                        case 2: CUSW_TB_LAUNCH(4, sk, tb_slots + 6 + 2 * k, nullptr, nullptr); break;
+                        case 3: CUSW_TB_LAUNCH(8, sk, tb_slots + 6 + 2 * k, nullptr, nullptr); break;
+                        case 4: CUSW_TB_LAUNCH(16, sk, tb_slots + 6 + 2 * k, nullptr, nullptr); break;
+                        default: CUSW_TB_LAUNCH(1, sk, tb_slots + 6 + 2 * k, nullptr, nullptr); break;
                     }
-#undef CUSW_TB_LAUNCH
+                    launches++;
+                    if (k > 0) CK(cudaEventRecord(tb_join[k - 1], sk));
+                }
+                // drain the escalation lists on the main stream, narrowest first: class k takes what class k-1 (own list and
+                // drain) handed over as soon as its own list is through, while the wider classes' own lists are still running
+                const int egrid = std::min((c + 127) / 128, 148 * 2);
+                for (int k = 1; k < kTbClasses; k++) {
+                    const int* esc_in = tb_esc.p + (size_t)k * c;
+                    const int* esc_in_count = dh + 8 + k;
+                    int* esc_out = tb_esc.p + (size_t)(k + 1) * c;
+                    int* esc_out_count = dh + 8 + k + 1;
+                    const int grid = egrid;
+                    CK(cudaStreamWaitEvent(st, tb_join[k - 1], 0));
+                    switch (k) {
+                        case 1: CUSW_TB_LAUNCH(2, st, tb_slots + 2 * kTbSlots, esc_in, esc_in_count); break;
+                        case 2: CUSW_TB_LAUNCH(4, st, tb_slots + 2 * kTbSlots, esc_in, esc_in_count); break;
+                        case 3: CUSW_TB_LAUNCH(8, st, tb_slots + 2 * kTbSlots, esc_in, esc_in_count); break;
+                        default: CUSW_TB_LAUNCH(16, st, tb_slots + 2 * kTbSlots, esc_in, esc_in_count); break;
+                    }
                     launches++;
                 }
+                CK(cudaStreamWaitEvent(st, tb_join[kTbClasses - 1], 0));  // the "nothing to trace" class
+#undef CUSW_TB_LAUNCH
                 // pairs that outgrew the widest frame, then those that outgrew the small warp kernel (from either launch)
                 sw_traceback_warp_kernel<8><<<148 * 4, 128, 0, st>>>(esc_small, 0, esc_small_count, esc_big, esc_big_count, io, fwd_c,
                                                                       rev_c, tc, pool, res_c, cig.p, ccap, d_counters + 1, retry_out, retry_count, tb_band.p);
@@ -767,6 +805,14 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
             CK(cudaEventRecord(ev[5], st));
             CK(cudaMemcpyAsync(h_counters, d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));  // the one host round trip of the round
+            if (getenv("CUDASW_TB_STATS")) {  // experiment hook: how the pairs fell into the traceback lists
+                int hh[16];
+                CK(cudaMemcpy(hh, dh, sizeof hh, cudaMemcpyDeviceToHost));
+                const int* wc2 = reinterpret_cast<const int*>(h_counters + 3);
+                fprintf(stderr, "[cudasw tb round %d] pairs %d: wide %d (big %d), classes 1/2/4/8/16/none = %d %d %d %d %d %d; escalated into 2/4/8/16/warp8/warp32 = %d %d %d %d %d %d; retry %d\n",
+                        round, c, wc2[0], wc2[1], hh[0], hh[1], hh[2], hh[3], hh[4], hh[5], hh[9], hh[10], hh[11], hh[12], hh[13], hh[14],
+                        *reinterpret_cast<int*>(h_counters + 2));
+            }
             int nretry = *reinterpret_cast<int*>(h_counters + 2);
             if (nretry == 0) { c = 0; break; }
             // a whole round may legitimately come back once (every pair handed from the thread kernel to the warp

@@ -1153,6 +1153,7 @@ __global__ void tb_slots_kernel(const int* __restrict__ wide_count, const int* _
         slots[7 + 2 * k] = cls_count[k];
         start += cls_count[k];
     }
+    slots[2 * kTbSlots] = 0; slots[2 * kTbSlots + 1] = 0;  // an empty list (launches that only drain an escalation list)
 }
 
 // Reserves CIGAR words for one pair and writes soft clips + body (SswJniAligner.java:52-59).

@@ -9,7 +9,7 @@ timeout 600 python bench.py > $O/bench_$TAG.json 2> $O/bench_$TAG.err; echo "ben
 tail -c 400 $O/bench_$TAG.err
 timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$TAG.json 2>> $O/bench_$TAG.err; echo "ref exit $?"
 timeout 600 python tools/bench_configs.py 1:10000 1:400000 2:1000000 3:1000000 4:1000000 5:1000 > $O/configs_$TAG.txt 2>&1; echo "configs exit $?"
-CMD="python bench.py --steps 2 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows --no-homology --no-worst-case"
+CMD="python bench.py --steps 2 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows --no-homology --no-worst-case --no-int-peak"
 timeout 300 $CMD > $O/plain_$TAG.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/launches_$TAG.csv $CMD > $O/ncu_launches_$TAG.log 2>&1
 echo "launch list exit $?"
