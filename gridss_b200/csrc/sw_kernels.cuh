@@ -445,10 +445,12 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
     else if (q > max_rows || w > max_cols) { r.status = CUDASW_ETOOLARGE; v = 2 * vt.n; }
     else v = variant_of(vt, (int)q) + ((*any_n != 0 && wflags[p]) ? vt.n : 0);
     res[p] = r;
-    // key = (slot : 7 | window length / 64 : 13 | seed anchor column / 4 : 12)
+    // key = (slot : 7 | 0x1FFF - window length / 64 : 13 | seed anchor column / 4 : 12): inside a slot the LONGEST windows
+    // come first, so the CTAs that run longest start first and a launch does not end in a tail of its slowest pairs
+    // (mixed-length batches: C3's forward pass took twice as long with its variants launched one after the other)
     uint32_t wq = (uint32_t)(w >> 6);
     if (wq > 0x1FFFu) wq = 0x1FFFu;
-    keys[p] = ((uint32_t)v << 25) | (wq << 12) | (uint32_t)anchor[p];
+    keys[p] = ((uint32_t)v << 25) | ((0x1FFFu - wq) << 12) | (uint32_t)anchor[p];
     vals[p] = p;
     atomicAdd(&hist[v], 1);
 }

@@ -703,3 +703,25 @@ def test_jaligner_mode_shares_score_and_end_with_ssw_mode(aligner, synth):
     assert (b["ref_begin"][ok] <= a["ref_begin"][ok]).all()
     assert (b["ref_begin"] == a["ref_begin"]).mean() > 0.9
     al.close()
+
+
+def test_strip_mined_queries_across_many_chunks(aligner, oracle, monkeypatch):
+    """queries above the tallest single-strip variant (strip-mined forward pass, boundary rows in a bump-allocated
+    pool) spread over MANY host chunks with w ~ q, so that the reverse pass (which runs once over the whole batch) needs more
+    boundary memory than any single chunk's forward pass did; both reverse-pass implementations."""
+    rng = np.random.default_rng(77)
+    seqs, refs = [], []
+    for _ in range(160):
+        w = int(rng.integers(2150, 3100))
+        r = rng.choice(list(b"ACGT"), size=w).astype(np.uint8)
+        s = r[int(rng.integers(0, 40)): w - int(rng.integers(0, 40))].copy()
+        for k in rng.integers(0, len(s), size=len(s) // 40):
+            s[k] = rng.choice(list(b"ACGT"))
+        seqs.append(s.tobytes())
+        refs.append(r.tobytes())
+    monkeypatch.setenv("CUDASW_CHUNK_MB", "1")
+    bad, undef = _compare(aligner, oracle, seqs, refs)
+    assert bad == [] and undef == 0, bad[:3]
+    monkeypatch.setenv("CUDASW_REV_FULL", "1")  # round 1's full-rectangle reverse kernels (strip pool sized for the whole batch)
+    bad, undef = _compare(aligner, oracle, seqs, refs)
+    assert bad == [] and undef == 0, bad[:3]
