@@ -496,6 +496,11 @@ def main():
                                               "achieved": gbs, "peak": hbm_peak or 6650.0, "unit": "GB/s", "frac": gbs / (hbm_peak or 6650.0),
                                               "peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_peak else "B200_PROFILING.md fallback (6.65 TB/s)",
                                               "bytes_per_launch_pair": enc_bytes, "ms": phase["ms_encode"]}
+        if st_h.get("ms_encode"):
+            gbs_u = st_h["encode_bytes"] / (st_h["ms_encode"] / 1e3) / 1e9
+            line["roofline"]["load_phase_packed"] = {"kernel": "unpack_kernel (2 bit + N mask words -> encoded bytes: 3/8 B read + 1 B written per base), e2e path",
+                                                     "bound": "hbm", "achieved": gbs_u, "peak": hbm_peak or 6650.0, "unit": "GB/s", "frac": gbs_u / (hbm_peak or 6650.0),
+                                                     "ms": st_h["ms_encode"], "note": "summed over the chunks of the last e2e step; later chunks unpack beside the previous chunk's forward kernels, so this is a lower bound of the kernel's own rate"}
         if win_line is not None:
             line["e2e_windows"] = win_line
         if hom_line is not None:
