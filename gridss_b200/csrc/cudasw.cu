@@ -654,6 +654,13 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
             CK(cudaEventRecord(join_ev[a], aux[a]));
             CK(cudaStreamWaitEvent(st, join_ev[a], 0));
         }
+        if (getenv("CUDASW_REV_STATS")) {  // experiment hook: pairs per strip-height variant (synchronises)
+            int hh[2 * kRevVariants + 1];
+            CK(cudaStreamSynchronize(st));
+            CK(cudaMemcpy(hh, dhr, sizeof hh, cudaMemcpyDeviceToHost));
+            fprintf(stderr, "[cudasw reverse] pairs %lld: S = 32/64/128/256/1024: %d %d %d %d %d; with N: %d %d %d %d %d; none %d\n", (long long)n,
+                    hh[0], hh[1], hh[2], hh[3], hh[4], hh[5], hh[6], hh[7], hh[8], hh[9], hh[10]);
+        }
     } else {
     CK(cudaMemsetAsync(d_strip + 1, 0, sizeof(unsigned long long), st));
     CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));

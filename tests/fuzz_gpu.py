@@ -47,6 +47,7 @@ def main():
     ap.add_argument("--checker", default="reference", choices=["reference", "model"])
     ap.add_argument("--c4-sample", type=int, default=0, help="instead: parity on the first N pairs of the C4 stream itself (seed 4004)")
     ap.add_argument("--c5", type=int, default=0, help="instead: parity on the first N pairs of C5 (10 kb contigs vs 20 kb windows, seed 5005)")
+    ap.add_argument("--c5-first", type=int, default=0, help="with --c5: start at this pair of the stream (pairs [first, N))")
     args = ap.parse_args()
     import gridss_b200 as g
     from gridss_b200.aligner import pack
@@ -109,7 +110,7 @@ def main():
     if args.c5 > 0:
         # the long-contig case takes the reference's 16-bit rerun and its band doubling
         step = 250
-        for first in range(0, args.c5, step):
+        for first in range(args.c5_first, args.c5, step):
             n = min(step, args.c5 - first)
             sb, so, rb, ro = S.generate(5, n, first=first)
             res, cig = al.align_blobs(sb, so, rb, ro)
@@ -121,7 +122,7 @@ def main():
             tot["undefined_in_reference"] += undef
             if bad and len(examples) < 5:
                 examples.append({"source": "C5", "pair": first + bad_first})
-        tot["by_source"] = {"C5 stream, seed 5005, pairs [0, %d)" % args.c5: {"pairs": tot["pairs"], "mismatches": tot["mismatches"]}}
+        tot["by_source"] = {"C5 stream, seed 5005, pairs [%d, %d)" % (args.c5_first, args.c5): {"pairs": tot["pairs"], "mismatches": tot["mismatches"]}}
         tot["checker"] = ("libsswjni.so as shipped by the reference" if use_ref else "oracle/ssw_model.c") + f", {cores} host threads"
         tot["examples"] = examples
         print(json.dumps(tot), flush=True)
