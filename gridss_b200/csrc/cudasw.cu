@@ -359,7 +359,7 @@ extern "C" int cudasw_create_ex(const cudasw_scoring* s, int device, int tie_bre
         if ((e = cudaMemcpy(h->d_pool, pool, sizeof pool, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(cudaGetErrorString(e));
         h->sc.pool_dev = h->d_pool;
     }
-    h->tc = TbConst{sc.match, sc.mismatch, sc.ambiguous, sc.gap_open, sc.gap_extend};
+    h->tc = TbConst{sc.match, sc.mismatch, sc.ambiguous, sc.gap_open, sc.gap_extend, h->sc.poolA, h->sc.poolB};
     if (2 * g_nvar + 1 > 127) { cudasw_destroy(h); g_create_error = "too many variants"; return CUDASW_EINVAL; }
     h->vt.n = g_nvar;
     h->vt.n_single = 0;

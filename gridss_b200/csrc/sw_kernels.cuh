@@ -1020,6 +1020,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 // ------------------------------------------------------------------------------------------
 struct TbConst {
     int32_t match, mismatch, ambiguous, go, ge;
+    uint32_t poolA, poolB;  // the PRMT byte pool of ScoreConst: byte x = substitution score of symbol-xor x
 };
 
 struct TbPool {
@@ -1029,8 +1030,10 @@ struct TbPool {
 };
 
 __device__ __forceinline__ int tb_sub(const TbConst& tc, uint32_t qb, uint32_t rb) {
-    uint32_t x = (qb ^ rb) & 7u;
-    return x == 0 ? tc.match : (x < 4 ? tc.mismatch : tc.ambiguous);
+    // x == 0: equal symbols (match); 1..3: both ACGT (mismatch); 4..7: exactly one N (ambiguous). One PRMT picks byte x of the
+    // pool and replicates its sign into the upper three bytes (selector nibbles x, x|8, x|8, x|8).
+    const uint32_t x = (qb ^ rb) & 7u;
+    return (int)prmt(tc.poolA, tc.poolB, x * 0x1111u + 0x8880u);
 }
 
 // Walks the direction matrix. When `outp` != nullptr writes ops (reversed order resolved by index).
@@ -1244,6 +1247,7 @@ __device__ int tb_dp_thread(const TbConst& tc, const uint8_t* __restrict__ ref, 
         const int end = min(i + band, refLen - 1);
         const int endp = min(i - 1 + band, refLen - 1);  // last column of the previous row
         const bool quirk = i >= 1 && i <= band + 1 && end == refLen - 1 && endp == end && end <= 2 * band + 1;
+        const int quirk_col = quirk ? end : -1;  // the reference's `edge` quirk: that cell's up neighbour reads as (0, 0)
         const uint32_t qb = qb_next;
         const uint32_t rw_in = rw_next;
         if (i + 1 < readLen) qb_next = read[i + 1];
@@ -1256,15 +1260,14 @@ __device__ int tb_dp_thread(const TbConst& tc, const uint8_t* __restrict__ ref, 
 #pragma unroll
         for (int x = 0; x < WMAX; x++) {
             const int j = j0 + x;
+            // row i-1 at the next diagonal = the cell above; a slot outside the band was never written in this pass: (0, 0)
             const int nxt_h = x + 1 < WMAX ? H[x + 1 < WMAX ? x + 1 : 0] : 0;
             const int nxt_e = x + 1 < WMAX ? E[x + 1 < WMAX ? x + 1 : 0] : 0;
             if (j >= beg && j <= end) {
-                int up_h = 0, up_e = 0;
-                if (j <= endp && !(quirk && j == end)) { up_h = nxt_h; up_e = nxt_e; }
-                const int hdiag = (i >= 1 && j >= 1) ? cur_h : 0;
+                const bool qk = j == quirk_col;
                 int h, e;
                 uint8_t dv;
-                tb_cell(tc, i, up_h, up_e, hdiag, tb_sub(tc, qb, rw[x]), hleft, fgap, mx, h, e, dv);
+                tb_cell(tc, qk ? 0 : nxt_h, qk ? 0 : nxt_e, cur_h, tb_sub(tc, qb, rw[x]), hleft, fgap, mx, h, e, dv);
                 H[x] = h;
                 E[x] = e;
                 dw |= (uint32_t)dv << (8 * (x & 3));

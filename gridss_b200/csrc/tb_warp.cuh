@@ -32,28 +32,32 @@ namespace cusw {
 // chain from one cell of a row to the next (left H -> F -> H) is two dependent instructions (VIADDMNMX, VIMNMX3):
 // everything that only depends on the previous row (E, the diagonal candidate, their maximum) and the direction bits
 // sit beside that chain.
-__device__ __forceinline__ void tb_cell(const TbConst& tc, int i, int up_h, int up_e, int hdiag, int s,
+// Borders need no special cases here because of how the callers keep their state: every (H, E) slot starts a band pass
+// at (0, 0) and is only ever written for an in-band cell, so a neighbour that lies outside the band or the matrix reads
+// as (0, 0) - which is exactly what the reference's rolling rows hold there (h_b = e_b = 0, ssw.c:596), and what its
+// first-row rule (-gapOpen / -gapExtend, ssw.c:607-608) amounts to. The one exception is the `edge` quirk, which the
+// callers apply by passing (0, 0) for the up neighbour.
+__device__ __forceinline__ void tb_cell(const TbConst& tc, int up_h, int up_e, int hdiag, int s,
                                         int& hleft, int& fgap, int& mx, int& h_out, int& e_out,
                                         uint8_t& dir_out) {
     // E (gap along the read, `I`): from the previous row only
-    const int te1 = i == 0 ? -tc.go : up_h - tc.go;
-    const int te2 = i == 0 ? -tc.ge : up_e - tc.ge;
+    const int te1 = up_h - tc.go;
+    const int te2 = up_e - tc.ge;
     const int E = max(te1, te2);
     const uint32_t dE = te1 > te2 ? 1u : 0u;
     const int e1 = max(E, 0);
     const int d = hdiag + s;
-    const int pre = max(e1, d);
     // F (gap along the reference, `D`) and H: the chain along the row
     const int tf2 = fgap - tc.ge;
     const int tf1 = hleft - tc.go;
     const int F = __viaddmax_s32(hleft, -tc.go, tf2);  // max(hleft - go, fgap - ge)
-    const int h = __vimax3_s32(pre, F, 0);             // max(max(e1, f1), d), f1 = max(F, 0)
+    const int h = __vimax3_s32(max(e1, d), F, 0);      // max(max(e1, f1), d), f1 = max(F, 0)
     fgap = F;
     hleft = h;
-    // direction bits (ties: extend beats open, diagonal beats gaps, F beats E)
+    // direction bits (ties: extend beats open, diagonal beats gaps, F beats E); h == d <=> max(e1, f1) <= d
     const uint32_t dF = tf1 > tf2 ? 1u : 0u;
     const int f1 = max(F, 0);
-    const uint32_t dH = (max(e1, f1) <= d) ? 1u : (e1 > f1 ? 2u + dE : 4u + dF);
+    const uint32_t dH = (h == d) ? 1u : (e1 > f1 ? 2u + dE : 4u + dF);
     dir_out = (uint8_t)(dH | (dE << 3) | (dF << 4));
     mx = max(mx, h);
     h_out = h;
@@ -103,6 +107,7 @@ __device__ int tb_dp_warp2(const TbConst& tc, const uint8_t* __restrict__ ref, c
         const int end = min(i + band, refLen - 1);
         const int endp = min(i - 1 + band, refLen - 1);  // last column of the previous row
         const bool quirk = i >= 1 && i <= band + 1 && end == refLen - 1 && endp == end && end <= 2 * band + 1;
+        const int quirk_col = quirk ? end : -1;
         const uint32_t qb = qb_next;
         uint32_t rw_in = 0u;
         if (act) {  // what the next row of this lane needs, in flight while this row is computed
@@ -128,12 +133,10 @@ __device__ int tb_dp_warp2(const TbConst& tc, const uint8_t* __restrict__ ref, c
                 const int nh = x + 1 < D ? sh[X0 + (x + 1 < D ? x + 1 : 0)] : uh;  // row i-1 at diagonal k+1
                 const int ne = x + 1 < D ? se[X0 + (x + 1 < D ? x + 1 : 0)] : ue;
                 if (j >= beg && j <= end) {
-                    int up_h = 0, up_e = 0;
-                    if (j <= endp && !(quirk && j == end)) { up_h = nh; up_e = ne; }
-                    const int hdiag = (i >= 1 && j >= 1) ? cur_h : 0;
+                    const bool qk = j == quirk_col;  // the reference's `edge` quirk: this cell's up neighbour reads as (0, 0)
                     int h, e;
                     uint8_t dv;
-                    tb_cell(tc, i, up_h, up_e, hdiag, tb_sub(tc, qb, rwin[X0 + x]), hleft, fgap, mx, h, e, dv);
+                    tb_cell(tc, qk ? 0 : nh, qk ? 0 : ne, cur_h, tb_sub(tc, qb, rwin[X0 + x]), hleft, fgap, mx, h, e, dv);
                     sh[X0 + x] = h; se[X0 + x] = e;
                     if (x == 0) { first_h = h; first_e = e; }
                     out_h = h; out_f = fgap;
@@ -225,12 +228,13 @@ __device__ int tb_dp_warp_mem(const TbConst& tc, const uint8_t* __restrict__ ref
                 if (x + 1 < nd) nxt = row[min(kb + x + 1, W - 1)];
                 else nxt = make_int2(upn_h, upn_e);
                 if (j >= beg && j <= end) {
+                    // (the scratch row is shared by all band widths of this pass only: zeroed above, written for in-band cells)
                     int up_h = 0, up_e = 0;
                     if (j <= endp && !(quirk && j == end)) { up_h = nxt.x; up_e = nxt.y; }
                     const int hdiag = (i >= 1 && j >= 1) ? cur.x : 0;
                     int h, e;
                     uint8_t dv;
-                    tb_cell(tc, i, up_h, up_e, hdiag, tb_sub(tc, qb, (uint32_t)ref[j]), hleft, fgap, mx, h, e, dv);
+                    tb_cell(tc, up_h, up_e, hdiag, tb_sub(tc, qb, (uint32_t)ref[j]), hleft, fgap, mx, h, e, dv);
                     CUSW_CHECK_PTR(drow + j, dir, dir + (long long)Wp * readLen, "direction byte (memory-backed DP)");
                     drow[j] = dv;
                     row[kb + x] = make_int2(h, e);
