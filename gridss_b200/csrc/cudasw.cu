@@ -213,7 +213,9 @@ struct cudasw {
                    bool ends_only = false);
     int post_chunk_ja(size_t ci, int64_t first, int64_t n, const int64_t* d_so, const int64_t* d_ro, int64_t cigar_cap, uint64_t* launches_out);
     int tie_break = CUDASW_TIEBREAK_SSW;
-    int size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off, int64_t rev_first, int64_t rev_cnt);
+    int size_strip_buffers(unsigned long long need_f, unsigned long long need_r);
+    void scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, const int64_t* h_seq_off, const int64_t* h_ref_off);
+    std::vector<unsigned long long> strip_need;  // per chunk: boundary-row bytes of its strip-mined pairs
     float last_post_ms = 0.f;
     int run(int64_t n, const uint8_t* d_seq, const int64_t* d_seq_off, const uint8_t* d_ref,
             const int64_t* d_ref_off, int64_t total_q, int64_t total_w, cudasw_result* out,
@@ -566,15 +568,7 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     launches++;
     CK(cudaEventRecord(chunk_ev[ci].pack1, st));
     CK(cudaGetLastError());
-    {
-        // grid sizes for the forward launches: pairs per query-length class, from the host's own copy of the offsets
-        std::vector<int>& hc = fwd_counts[ci];
-        hc.assign((size_t)g_nvar, 0);
-        for (int64_t i = first; i < first + cnt; i++) {
-            const int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
-            if (q > 0 && w > 0 && q <= max_rows && w <= max_cols) hc[(size_t)var_by_q[(size_t)q]]++;
-        }
-    }
+    (void)h_seq_off; (void)h_ref_off;  // (the per-class pair counts come from scan_batch)
     *launches_out += launches;
     return CUDASW_OK;
 }
@@ -936,20 +930,7 @@ int cudasw::post_chunk_ja(size_t ci, int64_t first, int64_t n, const int64_t* d_
 // 32-bit word per window column and pair. The forward buffer is sized for the chunk [first, first + cnt) whose forward
 // pass is about to be queued; the reverse buffer for `rev_first`/`rev_cnt`, the range ONE post_chunk call walks (the whole
 // batch unless CUDASW_POST_PER_CHUNK is set), so the kernels' bump allocation cannot run out.
-int cudasw::size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_off, const int64_t* h_ref_off,
-                               int64_t rev_first, int64_t rev_cnt) {
-    if (!g_var[g_nvar - 1].multi) return CUDASW_OK;
-    const int64_t single_rows = vt.n_single > 0 ? vt.rows[vt.n_single - 1] : 0;
-    auto need_of = [&](int64_t a, int64_t c) {
-        unsigned long long need = 0;
-        for (int64_t i = a; i < a + c; i++) {
-            const int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
-            if (q > single_rows && w > 0) need += ((((unsigned long long)w * 4ull + 15ull) & ~15ull) * 2ull);
-        }
-        return need;
-    };
-    const unsigned long long need_f = need_of(first, cnt);
-    const unsigned long long need_r = rev_cnt > 0 ? need_of(rev_first, rev_cnt) : 0;
+int cudasw::size_strip_buffers(unsigned long long need_f, unsigned long long need_r) {
     if (need_f > strip_fwd.cap || need_r > strip_rev.cap) {
         // the buffers may still be in use by the chunk before: let it finish before they are replaced
         CK(cudaStreamSynchronize(stream));
@@ -958,6 +939,55 @@ int cudasw::size_strip_buffers(int64_t first, int64_t cnt, const int64_t* h_seq_
         if (need_r > strip_rev.cap) CK(strip_rev.ensure((size_t)need_r + 256));
     }
     return CUDASW_OK;
+}
+
+// One pass over the host's copy of the offsets (several threads for large batches), while the first H2D copies are in
+// flight: per chunk the pairs per query-length class (the grids of the forward launches) and the boundary-row memory its
+// strip-mined pairs need; for the batch the longest query / window (the reverse pass's rings).
+void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, const int64_t* h_seq_off, const int64_t* h_ref_off) {
+    const bool have_multi = g_var[g_nvar - 1].multi;
+    const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
+                                  scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
+    const int max_cols = (1 << 24) - 2;
+    const int64_t single_rows = vt.n_single > 0 ? vt.rows[vt.n_single - 1] : 0;
+    fwd_counts.assign(ranges.size(), std::vector<int>((size_t)g_nvar, 0));
+    strip_need.assign(ranges.size(), 0ull);
+    struct Part { std::vector<int> counts; unsigned long long need = 0; int64_t mq = 0, mw = 0; };
+    int64_t mq = 0, mw = 0;
+    for (size_t ci = 0; ci < ranges.size(); ci++) {
+        const int64_t first = ranges[ci].first, cnt = ranges[ci].second;
+        const int nt = (int)std::min<int64_t>(8, std::max<int64_t>(1, cnt / 65536));
+        std::vector<Part> parts((size_t)nt);
+        auto work = [&](int t) {
+            Part& p = parts[(size_t)t];
+            p.counts.assign((size_t)g_nvar, 0);
+            const int64_t a = first + cnt * t / nt, b = first + cnt * (t + 1) / nt;
+            for (int64_t i = a; i < b; i++) {
+                const int64_t q = h_seq_off[i + 1] - h_seq_off[i], w = h_ref_off[i + 1] - h_ref_off[i];
+                p.mq = std::max(p.mq, q);
+                p.mw = std::max(p.mw, w);
+                if (q > 0 && w > 0 && q <= max_rows && w <= max_cols) {
+                    p.counts[(size_t)var_by_q[(size_t)q]]++;
+                    if (q > single_rows) p.need += ((((unsigned long long)w * 4ull + 15ull) & ~15ull) * 2ull);
+                }
+            }
+        };
+        if (nt == 1) work(0);
+        else {
+            std::vector<std::thread> th;
+            for (int t = 1; t < nt; t++) th.emplace_back(work, t);
+            work(0);
+            for (auto& x : th) x.join();
+        }
+        for (auto& p : parts) {
+            for (int v = 0; v < g_nvar; v++) fwd_counts[ci][(size_t)v] += p.counts[(size_t)v];
+            strip_need[ci] += p.need;
+            mq = std::max(mq, p.mq);
+            mw = std::max(mw, p.mw);
+        }
+    }
+    batch_max_q = std::min<int64_t>(std::max<int64_t>(mq, 1), 32767);
+    batch_max_w = std::min<int64_t>(std::max<int64_t>(mw, 1), (1 << 24));
 }
 
 int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
@@ -1050,16 +1080,6 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     }
     int64_t max_cnt = 0;
     for (auto& c : chunks) max_cnt = std::max(max_cnt, c.cnt);
-    {
-        // longest query / window of the batch (sizes the boundary rings of the banded reverse pass)
-        int64_t mq = 0, mw = 0;
-        for (int64_t i = 0; i < n; i++) {
-            mq = std::max(mq, h_seq_off[i + 1] - h_seq_off[i]);
-            mw = std::max(mw, h_ref_off[i + 1] - h_ref_off[i]);
-        }
-        batch_max_q = std::min<int64_t>(std::max<int64_t>(mq, 1), 32767);
-        batch_max_w = std::min<int64_t>(std::max<int64_t>(mw, 1), (1 << 24));
-    }
 
     // ---- capacity
     CK(enc_seq.ensure((size_t)total_q + 16));
@@ -1074,7 +1094,6 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         CK(cub_tmp.ensure(cub_bytes + 16));
         CK(cub_tmp_post.ensure(cub_bytes + 16));
     }
-    fwd_counts.resize(chunks.size());
     CK(fwd_slots.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1))));
     batch_maybe_n = !(packed && packed->refN == nullptr);
     if (!tb_pool.p) {
@@ -1181,6 +1200,12 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         if (packed) stats.h2d_bytes = packed_bytes + (uint64_t)(n + 1) * 16;
     }
 
+    {
+        // (runs on the host while the first copies are on their way)
+        std::vector<std::pair<int64_t, int64_t>> ranges;
+        for (auto& c : chunks) ranges.emplace_back(c.first, c.cnt);
+        scan_batch(ranges, h_seq_off, h_ref_off);
+    }
     // ---- the chunk pipeline: pack(i) | forward(i) | post(i-1), see pack_chunk
     auto drain = [&]() {  // nothing may stay in flight over the caller's buffers or this handle's scratch
         cudaStreamSynchronize(copy_stream); cudaStreamSynchronize(pack_stream); cudaStreamSynchronize(st);
@@ -1193,7 +1218,11 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         if (inputs_on_host) CK(cudaStreamWaitEvent(pack_stream, h2d_done[i], 0));
         int rc = pack_chunk(i, c.first, c.cnt, d_seq, d_so, d_ref, d_ro, c.q_lo, c.q_hi, c.w_lo, c.w_hi, gather, &launches, qgather, q_stride, w_stride, packed != nullptr, h_seq_off, h_ref_off);
         // reverse-pass strips: per chunk when post runs per chunk, else once for the whole batch (sized with the first chunk)
-        if (rc == CUDASW_OK) rc = size_strip_buffers(c.first, c.cnt, h_seq_off, h_ref_off, post_per_chunk ? c.first : 0, post_per_chunk ? c.cnt : (i == 0 ? n : 0));
+        if (rc == CUDASW_OK && g_var[g_nvar - 1].multi) {
+            unsigned long long need_all = 0;
+            for (auto x : strip_need) need_all += x;
+            rc = size_strip_buffers(strip_need[i], post_per_chunk ? strip_need[i] : need_all);
+        }
         if (rc == CUDASW_OK) rc = forward_chunk(i, c.first, c.cnt, d_so, d_ro, &launches);
         if (rc == CUDASW_OK && serial) rc = cudaStreamSynchronize(st) == cudaSuccess ? CUDASW_OK : CUDASW_ECUDA;
         if (rc == CUDASW_OK && post_per_chunk && tie_break == CUDASW_TIEBREAK_SSW && i > 0) rc = post_chunk(i - 1, chunks[i - 1].first, chunks[i - 1].cnt, d_so, d_ro, cigar_cap, &launches, ends_only);
