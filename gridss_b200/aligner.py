@@ -128,6 +128,8 @@ ABI = [
     ("cudasw_device_count", ctypes.c_int, []),
     ("cudasw_version", ctypes.c_char_p, []),
     ("cudasw_cigar_string", ctypes.c_int, [_vp, _i32, ctypes.c_char_p, _i32]),
+    # no allocation, no handle: device pointers in and out (include/cudasw.h; tests/test_zz_no_alloc.py)
+    ("cudasw_score_batch_noalloc", ctypes.c_int, [ctypes.POINTER(_Scoring), ctypes.c_int, _i32, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _vp, ctypes.c_char_p, _sz]),
 ]
 
 

@@ -41,7 +41,8 @@ def build(force: bool = False, verbose: bool = False, check: bool = False) -> st
     jobs = [(os.path.join(OBJ, "cudasw.o"), [os.path.join(CSRC, "cudasw.cu")]),
             (os.path.join(OBJ, "variants.o"), [os.path.join(CSRC, "variants.cu")]),
             (os.path.join(OBJ, "multi.o"), [os.path.join(CSRC, "multi.cpp")]),
-            (os.path.join(OBJ, "rev_variants.o"), [os.path.join(CSRC, "rev_variants.cu")])]
+            (os.path.join(OBJ, "rev_variants.o"), [os.path.join(CSRC, "rev_variants.cu")]),
+            (os.path.join(OBJ, "noalloc.o"), [os.path.join(CSRC, "noalloc.cu")])]
     for g in GROUPS:
         jobs.append((os.path.join(OBJ, f"score_g{g}.o"), [f"-DSCORE_G={g}", os.path.join(CSRC, "score_variants.cu")]))
 

@@ -262,6 +262,33 @@ const char* cudasw_version(void);
  * (libsswjni.so 0xa6c) + the string concat in SswJniAligner.java:52-59. */
 int cudasw_cigar_string(const uint32_t* ops, int32_t n_ops, char* buf, int32_t cap);
 
+/* ---- Forward score pass for callers that cannot allocate. NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * Needs no handle and calls no cudaMalloc / cudaFree / allocating library routine: every piece of scratch the engine
+ * normally allocates (encoded blobs, scoring constants, job list, strip boundary rows of the strip-mined forward kernel
+ * sw_score_kernel<32, 20, MULTI>) lives in one file-scope `static __device__` array of CUDASW_NOALLOC_SCRATCH_BYTES
+ * (gridss_b200/csrc/noalloc.cu) that every GPU loading libcudasw.so holds until exit. Hence the limits per call, which are
+ * rejected with CUDASW_ETOOLARGE and a message in errbuf: n_pairs <= CUDASW_NOALLOC_MAX_PAIRS, seq_bytes <=
+ * CUDASW_NOALLOC_MAX_SEQ_BYTES, ref_bytes <= CUDASW_NOALLOC_MAX_REF_BYTES.
+ * ALL data pointers are DEVICE pointers on `device`, provided by the caller: raw ASCII blobs and n_pairs + 1 offsets each
+ * as in cudasw_align_batch (clean() is applied on the device); seq_bytes / ref_bytes = size of the blobs (>= the last
+ * offset). d_out receives 4 int32 per pair: {score, ref_end, read_end, status}, equal to the same fields of the
+ * cudasw_result that cudasw_align_batch gives for the pair (score 0 -> ref_end -1, read_end 0; per-pair CUDASW_EINVAL /
+ * CUDASW_ETOOLARGE as there). scoring == NULL -> 1,-4,-4,6,1. The kernels are launched on `stream` (a cudaStream_t; NULL
+ * = the default stream) and the call returns WITHOUT synchronising: d_out is complete once the stream reaches that point.
+ * The first call on a device takes the array's device address (cudaGetSymbolAddress) and must be made outside a stream
+ * capture; n_pairs == 0 does only that. The current device is restored before returning.
+ * Every call shares the array: calls that overlap on one GPU (different streams, concurrent host threads) RACE; order
+ * them on one stream or with events. errbuf (may be NULL) receives a NUL-terminated message when the result is not 0. */
+#define CUDASW_NOALLOC_MAX_PAIRS 4096
+#define CUDASW_NOALLOC_MAX_SEQ_BYTES (1 << 20)
+#define CUDASW_NOALLOC_MAX_REF_BYTES (1 << 20)
+#define CUDASW_NOALLOC_SCRATCH_BYTES (10 * 1024 * 1024 + 128 * 1024) /* 10.125 MiB per GPU */
+int cudasw_score_batch_noalloc(const cudasw_scoring* scoring, int device, int32_t n_pairs,
+                               const uint8_t* d_seq_blob, const int64_t* d_seq_off, int64_t seq_bytes,
+                               const uint8_t* d_ref_blob, const int64_t* d_ref_off, int64_t ref_bytes,
+                               int32_t* d_out, void* stream, char* errbuf, size_t errbuf_cap);
+
 #ifdef __cplusplus
 }
 #endif
