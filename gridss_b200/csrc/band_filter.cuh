@@ -1,0 +1,269 @@
+// band_filter.cuh - a LOSSLESS k-mer filter in front of the forward score pass: most pairs only need the columns that a
+// diagonal band around their alignment can reach, and the filter PROVES after the fact that nothing outside mattered.
+// Pairs without such a proof run the forward pass over their whole window as before; results are identical either way.
+// (No counterpart in the reference - ssw.c sweeps the full matrix - the results are what must match, and do: see below.)
+//
+// Why it is exact. Let a = match > 0, p = min(|mismatch|, |ambiguous|), go / ge the gap costs (a gap of L bases costs
+// go + (L-1) ge >= go), n = min(q, w). Take ANY local alignment path P of score S(P) >= S0 with M match steps, X other
+// diagonal steps and g gaps with Lg gap bases in total:
+//   (1) S(P) <= a M - p X - go g   and   M + X <= n;
+//   (2) its match steps form at most X + g + 1 maximal runs, and a run of r matches contains r - k + 1 positions (i, j)
+//       with query[i .. i+k) == window[j .. j+k) ("hits"; the window holds no N here, so a match is an equal A/C/G/T
+//       symbol), hence P passes through at least M - (k-1)(X + g + 1) hits. Minimised over (1) - a fractional knapsack
+//       with one budget, solved in closed form by flt_hits_floor() - that is T(S0), non-decreasing in S0;
+//   (3) the diagonals j - i it visits span at most Lg <= L(S0) = max_gap_bases(n, a, S0, go, ge) (the bound the banded
+//       reverse pass rests on, rev_band.cuh), i.e. they touch at most m(S0) = ceil(L / 32) + 1 consecutive bins of 32.
+// The filter counts ALL hits of the pair per diagonal bin (never fewer: query k-mers are chained, not hashed away),
+// picks the densest bin pair [b, b+1], a margin of m_r bins either side, and runs the forward pass on the columns
+// [c0, c1] that the diagonals of bins [b - m_r, b + 1 + m_r] can reach, which gives a true score S0 (a DP over a
+// sub-rectangle never exceeds the full DP). If m(S0) <= m_r and every run of m_r bins that lies outside
+// [b - 1, b + 2] holds fewer than T(S0) hits ("noise"), then a path of score >= S0 that leaves the band would have to
+// collect >= T(S0) hits inside a window of m(S0) bins that is not inside the band - there is none. So every cell whose
+// true H is >= S0 is reached by paths inside the computed rectangle only: its value there is exact, the maximum is the
+// true maximum and the set of cells holding it - all the reference's tie-break (first column, then smallest row,
+// ssw.c:283-306) looks at - is the same. Otherwise the pair is handed to the full-window pass.
+#pragma once
+#include "sw_kernels.cuh"
+
+namespace cusw {
+
+constexpr int kFltK = 6;                      // k-mer length: 4^6 direct-mapped heads
+constexpr int kFltHeads = 1 << (2 * kFltK);
+constexpr int kFltBinShift = 5;               // 32 diagonals per bin
+constexpr int kFltMaxBins = 1024;             // q + w - 1 <= 32 * 1024 diagonals
+constexpr int kFltMaxQ = 2040;                // chain links are 16 bit; a bin then holds at most 32 * 2040 hits
+constexpr int kFltWarps = 4;                  // pairs per CTA of filter_kernel
+constexpr size_t kFltSmemPerWarp = kFltHeads * 2 + 2048 * 2 + kFltMaxBins * 2;  // heads, links, bins: 16 bit each (14 KB)
+
+struct FilterConst {
+    int ok;              // 0: this scoring gives no usable bound (match <= 0, free mismatches or free gaps)
+    int a, go, ge;       // match, gap open, gap extend
+    long long cn, cd;    // rho = cn / cd = min(0, (p - (k-1) a) / (p + a), (go - (k-1) a) / go), cd > 0
+    int est_pct;         // the margin is sized for a score of est_pct % of (a * hits of the densest bin pair)
+};
+
+inline FilterConst make_filter_const(int match, int mismatch, int ambiguous, int go, int ge) {
+    FilterConst f{};
+    f.a = match; f.go = go; f.ge = ge; f.cn = 0; f.cd = 1; f.est_pct = 80;
+    const long long a = match, p = std::min(-mismatch, -ambiguous), k1 = kFltK - 1;
+    f.ok = match > 0 && p > 0 && go > 0 && max_gap_bases(1000, match, 1, go, ge) >= 0;
+    if (!f.ok) return f;
+    auto take = [&](long long n, long long d) {  // d > 0
+        if (n * f.cd < f.cn * d) { f.cn = n; f.cd = d; }
+    };
+    take(p - k1 * a, p + a);
+    take(go - k1 * a, go);
+    return f;
+}
+
+// T(S0): floor of the least number of hits on a path of score >= S0 over at most n diagonal steps (see (2) above)
+__host__ __device__ __forceinline__ long long flt_hits_floor(const FilterConst& f, long long S0, long long n) {
+    long long bud = (long long)f.a * n - S0;
+    if (bud < 0) bud = 0;
+    const long long num = (S0 - (long long)(kFltK - 1) * f.a) * f.cd + bud * f.cn;
+    const long long den = (long long)f.a * f.cd;
+    long long t = num / den;
+    if (num % den != 0 && num < 0) --t;
+    return t;
+}
+// m(L): bins of 32 diagonals that a window of L + 1 consecutive diagonals can touch
+__host__ __device__ __forceinline__ int flt_bins_of(long long L) { return (int)((L + 31) >> kFltBinShift) + 1; }
+
+#ifdef CUSW_MAIN_TU
+// One warp per pair. Shared memory per warp: heads[4^k] (first query row + 1 of every k-mer), link[row] (next row with
+// the same k-mer), bins[diagonal / 32]; all 16 bit.
+__global__ void __launch_bounds__(32 * kFltWarps)
+filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __restrict__ wflags, FilterConst fc,
+              FilterRec* __restrict__ rec, unsigned long long* __restrict__ counters) {
+    extern __shared__ __align__(16) unsigned char flt_smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    unsigned short* heads = reinterpret_cast<unsigned short*>(flt_smem + (size_t)wib * kFltSmemPerWarp);
+    unsigned short* link = heads + kFltHeads;
+    uint32_t* bins2 = reinterpret_cast<uint32_t*>(link + 2048);  // two 16-bit counters per word (a bin holds <= 32 * kFltMaxQ hits)
+    uint32_t* psum = reinterpret_cast<uint32_t*>(heads);         // prefix sums of the bins: overlays the heads once the scan is over
+    for (int p = blockIdx.x * kFltWarps + wib; p < n; p += gridDim.x * kFltWarps) {
+        const int64_t qo = io.seq_off[p], ro = io.ref_off[p];
+        const int q = (int)(io.seq_off[p + 1] - qo), w = (int)(io.ref_off[p + 1] - ro);
+        FilterRec r{0, w, 0, 0};
+        const bool eligible = fc.ok && q >= kFltK && w >= kFltK && q <= kFltMaxQ && (long long)q + w <= 32ll * kFltMaxBins - 64 &&
+                              !(*any_n != 0 && wflags[p]);
+        if (!eligible) {  // warp-uniform
+            if (lane == 0) rec[p] = r;
+            continue;
+        }
+        const uint8_t* qs = io.enc_seq + qo;
+        const uint8_t* ws = io.enc_ref + ro;
+        const int nb = ((q + w - 2) >> kFltBinShift) + 1;
+        {   // clear
+            uint4* h4 = reinterpret_cast<uint4*>(heads);
+            for (int i = lane; i < kFltHeads / 8; i += 32) h4[i] = make_uint4(0u, 0u, 0u, 0u);
+            for (int i = lane; i < (nb + 3) / 2; i += 32) bins2[i] = 0u;
+        }
+        __syncwarp();
+        // Both sequences are read 512 bases per step, one aligned 16-byte vector per lane (prefetched a step ahead); a lane
+        // owns the k-mers that END in its vector and gets the five bases before it from the lane below (lane 0: from the
+        // previous step). body(vc, vn, pos0, checked): k-mer u of the lane (u = 0 .. 15) starts at base pos0 + u, its value is
+        // bits [2u, 2u + 12) of vc (sum of code[pos + t] << 2t), bits [2u, 2u + 12) of vn are non-zero when it holds an N
+        // (check_n only); !checked: every pos0 + u of the step is inside [0, len - k] for every lane.
+        auto scan = [&](const uint8_t* sq, int len, bool check_n, auto&& body) {
+            const int mis = (int)(reinterpret_cast<uintptr_t>(sq) & 15u);
+            const uint4* al = reinterpret_cast<const uint4*>(sq - mis);
+            const int total = len + mis;  // bytes of the aligned stream that are ours (the first `mis` are not)
+            const int ntiles = (total + 511) >> 9;
+            auto load = [&](int vi) { return 16 * vi < total ? al[vi] : make_uint4(0u, 0u, 0u, 0u); };
+            auto c8 = [](uint32_t x) { return ((x & 0x03030303u) * 0x01041040u) >> 24; };  // four bytes -> four 2-bit codes
+            uint4 nxt = load(lane);
+            uint32_t carry_c = 0u, carry_n = 0u;
+            for (int t = 0; t < ntiles; t++) {
+                const uint4 cur = nxt;
+                nxt = load(32 * (t + 1) + lane);
+                const uint32_t c32 = c8(cur.x) | (c8(cur.y) << 8) | (c8(cur.z) << 16) | (c8(cur.w) << 24);
+                uint32_t n32 = 0u;
+                if (check_n) n32 = c8(cur.x >> 2) | (c8(cur.y >> 2) << 8) | (c8(cur.z >> 2) << 16) | (c8(cur.w >> 2) << 24);
+                uint32_t pc = __shfl_up_sync(0xffffffffu, c32, 1), pn = check_n ? __shfl_up_sync(0xffffffffu, n32, 1) : 0u;
+                if (lane == 0) { pc = carry_c; pn = carry_n; }
+                carry_c = __shfl_sync(0xffffffffu, c32, 31);
+                if (check_n) carry_n = __shfl_sync(0xffffffffu, n32, 31);
+                const unsigned long long vc = ((unsigned long long)c32 << 10) | (pc >> 22);
+                const unsigned long long vn = ((unsigned long long)n32 << 10) | (pn >> 22);
+                body(vc, vn, 512 * t + 16 * lane - mis - (kFltK - 1), t == 0 || t + 2 > ntiles);
+            }
+        };
+        // query k-mers -> chains (rows holding an N have none). Plain stores, verified: of the lanes that push onto the same
+        // head in the same step one wins, the others see it and try again on top of it.
+        scan(qs, q, true, [&](unsigned long long vc, unsigned long long vn, int pos0, bool) {
+            for (int u = 0; u < 16; u++) {
+                const int i = pos0 + u;
+                const uint32_t km = (uint32_t)(vc >> (2 * u)) & (kFltHeads - 1);
+                bool pending = i >= 0 && i <= q - kFltK && ((uint32_t)(vn >> (2 * u)) & (kFltHeads - 1)) == 0u;
+                while (__any_sync(0xffffffffu, pending)) {
+                    unsigned short old = 0;
+                    if (pending) { old = heads[km]; }
+                    __syncwarp();
+                    if (pending) heads[km] = (unsigned short)(i + 1);
+                    __syncwarp();
+                    if (pending && heads[km] == (unsigned short)(i + 1)) { link[i] = old; pending = false; }
+                    __syncwarp();
+                }
+            }
+        });
+        __syncwarp();
+        // window k-mers -> hits per diagonal bin (the window holds A/C/G/T only): sixteen independent look-ups per lane and
+        // step, then the (rare) chains of the ones that found a head
+        scan(ws, w, false, [&](unsigned long long vc, unsigned long long, int pos0, bool checked) {
+            uint32_t found = 0u;
+            if (!checked) {
+#pragma unroll
+                for (int u = 0; u < 16; u++)
+                    if (heads[(uint32_t)(vc >> (2 * u)) & (kFltHeads - 1)] != 0) found |= 1u << u;
+            } else {
+#pragma unroll
+                for (int u = 0; u < 16; u++)
+                    if (pos0 + u >= 0 && pos0 + u <= w - kFltK && heads[(uint32_t)(vc >> (2 * u)) & (kFltHeads - 1)] != 0) found |= 1u << u;
+            }
+            while (found != 0u) {
+                const int u = __ffs((int)found) - 1;
+                found &= found - 1u;
+                const int j = pos0 + u;
+                uint32_t i1p = heads[(uint32_t)(vc >> (2 * u)) & (kFltHeads - 1)];
+                while (i1p != 0u) {
+                    const int i = (int)i1p - 1;
+                    const int b = (j - i + q - 1) >> kFltBinShift;
+                    atomicAdd(&bins2[b >> 1], 1u << (16 * (b & 1)));
+                    i1p = link[i];
+                }
+            }
+        });
+        __syncwarp();
+        auto bin_at = [&](int b) { return (bins2[b >> 1] >> (16 * (b & 1))) & 0xFFFFu; };
+        // densest pair of adjacent bins (ties: the first)
+        uint32_t bh = 0u;
+        int bb = 0;
+        for (int b = lane; b < nb; b += 32) {
+            const uint32_t s = bin_at(b) + bin_at(b + 1);  // bin nb is zero
+            if (s > bh) { bh = s; bb = b; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint32_t oh = __shfl_xor_sync(0xffffffffu, bh, o);
+            const int ob = __shfl_xor_sync(0xffffffffu, bb, o);
+            if (oh > bh || (oh == bh && ob < bb)) { bh = oh; bb = ob; }
+        }
+        const long long nmin = min(q, w);
+        const long long s_est = (long long)fc.a * bh * fc.est_pct / 100;
+        const long long L = s_est > 0 ? max_gap_bases(nmin, fc.a, (int)min(s_est, 32767ll), fc.go, fc.ge) : -1;
+        bool go_on = L >= 0;
+        int m_r = 0;
+        long long c0 = 0, c1 = w - 1;
+        if (go_on) {
+            m_r = flt_bins_of(L);
+            const long long Dlo = 32ll * (bb - m_r), Dhi = 32ll * (bb + 2 + m_r) - 1;  // diagonal index j - i + q - 1
+            c0 = max(0ll, Dlo - (q - 1));
+            c1 = min((long long)w - 1, Dhi);
+            go_on = (c1 - c0 + 1) * 10 <= 7ll * w;  // otherwise nothing to win
+        }
+        uint32_t noise = 0u;
+        if (go_on) {  // warp-uniform
+            // inclusive prefix sums of the bins, in place
+            uint32_t carry = 0u;
+            for (int base = 0; base < nb; base += 32) {
+                const int b = base + lane;
+                uint32_t v = b < nb ? bin_at(b) : 0u;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+                    if (lane >= o) v += u;
+                }
+                v += carry;
+                if (b < nb) psum[b] = v;
+                carry = __shfl_sync(0xffffffffu, v, 31);
+            }
+            __syncwarp();
+            // runs [bs, be) of m_r bins that lie entirely left of bin bb - 1 or right of bin bb + 2
+            for (int bs = lane; bs < nb; bs += 32) {
+                const int be = min(bs + m_r, nb);
+                if (be - 1 <= bb - 2 || bs >= bb + 3) {
+                    const uint32_t s = psum[be - 1] - (bs > 0 ? psum[bs - 1] : 0u);
+                    noise = max(noise, s);
+                }
+            }
+            noise = __reduce_max_sync(0xffffffffu, noise);
+            // not worth trying when even the estimated score could not be told from the noise
+            go_on = flt_hits_floor(fc, (long long)fc.a * bh, nmin) > (long long)noise;
+        }
+        if (lane == 0) {
+            if (go_on) { r.c0 = (int32_t)c0; r.wlen = (int32_t)(c1 - c0 + 1); r.margin_bins = m_r; r.noise = (int32_t)noise; }
+            rec[p] = r;
+            if (counters) atomicAdd(counters + (go_on ? 0 : 1), 1ull);
+        }
+        __syncwarp();
+    }
+}
+
+// After the sub-window forward pass: is the score it found a proof (see the header)? done[p] = 1 keeps the result,
+// 0 sends the pair to the full-window pass (its record is then reset to the whole window).
+__global__ void filter_certify_kernel(int n, const int64_t* __restrict__ seq_off, const int64_t* __restrict__ ref_off,
+                                      const int4* __restrict__ fwd, FilterConst fc, FilterRec* __restrict__ rec,
+                                      uint8_t* __restrict__ done, unsigned long long* __restrict__ counters) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    FilterRec r = rec[p];
+    if (r.margin_bins == 0) { done[p] = 1; return; }  // the first pass already swept the whole window
+    const long long q = seq_off[p + 1] - seq_off[p], w = ref_off[p + 1] - ref_off[p];
+    const long long nmin = q < w ? q : w;
+    const int4 f = fwd[p];
+    bool ok = f.w == 0 && f.x > 0;
+    if (ok) {
+        const long long L = max_gap_bases(nmin, fc.a, f.x, fc.go, fc.ge);
+        ok = L >= 0 && flt_bins_of(L) <= r.margin_bins && flt_hits_floor(fc, f.x, nmin) > (long long)r.noise;
+    }
+    done[p] = ok ? 1 : 0;
+    if (!ok) {
+        r.c0 = 0; r.wlen = (int32_t)w; r.margin_bins = 0; r.noise = 0;
+        rec[p] = r;
+        if (counters) atomicAdd(counters + 2, 1ull);
+    }
+}
+#endif  // CUSW_MAIN_TU
+
+}  // namespace cusw

@@ -26,6 +26,7 @@
 #define CUSW_MAIN_TU 1  // non-template kernels are emitted in this translation unit only
 #include "sw_kernels.cuh"
 #include "rev_band.cuh"
+#include "band_filter.cuh"
 #include "ja_mode.cuh"
 #include "variants.h"
 
@@ -156,6 +157,16 @@ struct cudasw {
     DevBuf<cudasw_result> res;
     DevBuf<uint32_t> cig;
     DevBuf<uint8_t> cub_tmp;
+    // k-mer filter in front of the forward pass (band_filter.cuh): per-pair column range + certificate data, the pairs whose
+    // sub-window result is proven, and the second (full-window) pass's own bins
+    FilterConst fc{};
+    bool use_filter = false;
+    DevBuf<FilterRec> frec;
+    DevBuf<uint8_t> fdone;
+    DevBuf<int> fwd_slots2;
+    DevBuf<uint8_t> cub_tmp_fwd2;
+    int* d_hist2 = nullptr;
+    unsigned long long* d_fcount = nullptr;  // [0] pairs given a band, [1] pairs the filter passed on, [2] certificates that failed
     DevBuf<uint16_t> anchor;  // per pair: seed estimate of the alignment's first window column / 4 (scheduling hint)
     DevBuf<uint8_t> wflags;  // per pair: window contains N (xor-selector flavour)
     DevBuf<uint8_t> tb_pool;
@@ -327,6 +338,17 @@ extern "C" int cudasw_create_ex(const cudasw_scoring* s, int device, int tie_bre
     if ((e = cudaMalloc(&h->d_strip, 4 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_rev_slots, 64 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_hist2, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_fcount, 4 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    cudaMemset(h->d_fcount, 0, 4 * sizeof(unsigned long long));
+    h->fc = make_filter_const(sc.match, sc.mismatch, sc.ambiguous, sc.gap_open, sc.gap_extend);
+    if (const char* fe = getenv("CUDASW_FILTER_EST")) h->fc.est_pct = std::min(std::max(atoi(fe), 10), 200);
+    {
+        const char* fe = getenv("CUDASW_FILTER");  // 0: every pair sweeps its whole window (the pre-filter pipeline)
+        h->use_filter = h->fc.ok && !(fe && atoi(fe) == 0);
+        if ((e = cudaFuncSetAttribute(filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kFltWarps * kFltSmemPerWarp))) != cudaSuccess)
+            return fail(cudaGetErrorString(e));
+    }
     if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
     if ((e = cudaMallocHost(&h->h_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
@@ -411,6 +433,9 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->d_qsegs.release(); h->d_qseg_off.release(); h->d_lit.release();
     h->hom_qs.release(); h->hom_ws.release(); h->hom_seq_off.release(); h->hom_ref_off.release(); h->hom_lit.release(); h->hom_res.release();
     if (h->d_hist) cudaFree(h->d_hist);
+    if (h->d_hist2) cudaFree(h->d_hist2);
+    if (h->d_fcount) cudaFree(h->d_fcount);
+    h->frec.release(); h->fdone.release(); h->fwd_slots2.release(); h->cub_tmp_fwd2.release();
     if (h->d_rev_slots) cudaFree(h->d_rev_slots);
     for (auto& r : h->rev_ring) r.release();
     if (h->d_pool) cudaFree(h->d_pool);
@@ -547,18 +572,25 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     if (packed) stats.encode_bytes += ((uint64_t)(q_hi - q_lo) + (uint64_t)(w_hi - w_lo)) * 5ull / 4ull + (pk_has_qn ? (uint64_t)(q_hi - q_lo) / 8 : 0) + (pk_has_wn ? (uint64_t)(w_hi - w_lo) / 8 : 0);
     else stats.encode_bytes += 2ull * (uint64_t)(q_hi - q_lo) + (gather ? (uint64_t)(w_hi - w_lo) * 11ull / 8ull : 2ull * (uint64_t)(w_hi - w_lo));
     launches++;
-    seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
-        (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first);
-    launches++;
     const bool have_multi = g_var[g_nvar - 1].multi;
     const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
                                   scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
     const int max_cols = (1 << 24) - 2;
     size_t cub_bytes = cub_tmp.cap;
     CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
+    if (use_filter) {
+        // per pair: hits per diagonal bin -> the column range the forward pass sweeps first (band_filter.cuh)
+        filter_kernel<<<(int)std::min<int64_t>((n + kFltWarps - 1) / kFltWarps, 148 * 2 * 8), 32 * kFltWarps, kFltWarps * kFltSmemPerWarp, st>>>(
+            (int)n, io, any_n, wflags.p + first, fc, frec.p + first, d_fcount);
+        launches++;
+    }
+    seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
+        (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first, use_filter ? frec.p + first : nullptr);
+    launches++;
     fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
                                                            keys.p + first, vals.p + first, d_hist, res.p + first, any_n,
-                                                           wflags.p + first, anchor.p + first, d_strip + 2);
+                                                           wflags.p + first, anchor.p + first, d_strip + 2,
+                                                           use_filter ? frec.p + first : nullptr, nullptr);
     launches++;
     CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p + first, keys_alt.p + first, vals.p + first,
                                        vals_alt.p + first, (int)n, 0, 32, st));
@@ -583,8 +615,33 @@ int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* 
     CK(cudaEventRecord(chunk_ev[ci].fwd0, st));
     CK(cudaMemsetAsync(d_strip, 0, sizeof(unsigned long long), st));
     StripPool spool{strip_fwd.p, (unsigned long long)strip_fwd.cap, d_strip};
+    if (use_filter) io.sub = frec.p + first;
     { int rc = launch_variants(fwd_set, false, vals_alt.p + first, io, nullptr, fwd.p + first, spool, &launches, fwd_counts[ci].data(),
                                fwd_slots.p + ci * (size_t)(2 * (2 * g_nvar + 1)), batch_maybe_n); if (rc != CUDASW_OK) return rc; }
+    if (use_filter) {
+        // Which sub-window results are proven (band_filter.cuh)? The others sweep their whole window now: binned again
+        // (everything proven lands in the "nothing to do" slot) and launched over the same host-side upper bounds.
+        const int64_t n = cnt;
+        const bool have_multi = g_var[g_nvar - 1].multi;
+        const int max_rows = std::min(have_multi ? 32767 : g_var[g_nvar - 1].rows,
+                                      scoring.match > 0 ? (32767 - scoring.gap_open) / scoring.match : 32767);
+        const int max_cols = (1 << 24) - 2;
+        int* any_n = reinterpret_cast<int*>(d_counters + 5);
+        int* slots2 = fwd_slots2.p + ci * (size_t)(2 * (2 * g_nvar + 1));
+        filter_certify_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, fwd.p + first, fc, frec.p + first,
+                                                                     fdone.p + first, d_fcount);
+        CK(cudaMemsetAsync(d_hist2, 0, 256 * sizeof(int), st));
+        fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
+                                                               keys.p + first, vals.p + first, d_hist2, res.p + first, any_n,
+                                                               wflags.p + first, anchor.p + first, d_strip + 2, frec.p + first, fdone.p + first);
+        size_t cub_bytes = cub_tmp_fwd2.cap;
+        CK(cub::DeviceRadixSort::SortPairs(cub_tmp_fwd2.p, cub_bytes, keys.p + first, keys_alt.p + first, vals.p + first,
+                                           vals_alt.p + first, (int)n, 0, 32, st));
+        slot_scan_kernel<<<1, 32, 0, st>>>(d_hist2, 2 * g_nvar + 1, slots2);
+        launches += 6;
+        { int rc = launch_variants(fwd_set, false, vals_alt.p + first, io, nullptr, fwd.p + first, spool, &launches, fwd_counts[ci].data(),
+                                   slots2, batch_maybe_n); if (rc != CUDASW_OK) return rc; }
+    }
     CK(cudaEventRecord(chunk_ev[ci].fwd1, st));
     CK(cudaGetLastError());
     *launches_out += launches;
@@ -1093,8 +1150,10 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         CK(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 27, st));
         CK(cub_tmp.ensure(cub_bytes + 16));
         CK(cub_tmp_post.ensure(cub_bytes + 16));
+        if (use_filter) CK(cub_tmp_fwd2.ensure(cub_bytes + 16));
     }
     CK(fwd_slots.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1))));
+    if (use_filter) { CK(frec.ensure(n)); CK(fdone.ensure(n)); CK(fwd_slots2.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1)))); }
     batch_maybe_n = !(packed && packed->refN == nullptr);
     if (!tb_pool.p) {
         size_t free_b = 0, total_b = 0;
@@ -1260,6 +1319,13 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(cudaEventRecord(ev[6], st));
     CK(cudaStreamSynchronize(st));
     stats.d2h_bytes = (uint64_t)n * sizeof(cudasw_result) + ncopy * 4;
+    if (use_filter && getenv("CUDASW_FILTER_STATS")) {  // experiment hook
+        unsigned long long fcnt[4];
+        CK(cudaMemcpy(fcnt, d_fcount, sizeof fcnt, cudaMemcpyDeviceToHost));
+        CK(cudaMemset(d_fcount, 0, sizeof fcnt));
+        fprintf(stderr, "[cudasw filter] pairs %lld: banded %llu, passed on %llu (ineligible pairs not counted), certificates failed %llu\n",
+                (long long)n, fcnt[0], fcnt[1], fcnt[2]);
+    }
 
     stats.pairs = (uint64_t)n;
     stats.kernel_launches = launches;

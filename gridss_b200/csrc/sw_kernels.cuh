@@ -292,11 +292,20 @@ struct ScoreConst {
     const uint32_t* pool_dev;  // 32 x {poolA, poolB, BB, GO2, NGE2, GOBB, 0, 0, profile[8]} in device memory (one copy per lane)
 };
 
+// What the k-mer filter (band_filter.cuh) decided for a pair. margin_bins == 0: no certificate sought, the forward pass
+// sweeps the whole window.
+struct FilterRec {
+    int32_t c0, wlen;     // the forward pass sweeps window columns [c0, c0 + wlen)
+    int32_t margin_bins;  // m_r
+    int32_t noise;        // most hits in any run of m_r bins outside the band's core
+};
+
 struct PairIO {
     const uint8_t* enc_seq;
     const uint8_t* enc_ref;
     const int64_t* seq_off;
     const int64_t* ref_off;
+    const FilterRec* sub = nullptr;  // forward pass only: per-pair column range (same indexing as the offsets)
 };
 
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t s) {
@@ -350,7 +359,8 @@ __device__ __forceinline__ bool seed_kmer(const uint8_t* __restrict__ p, uint32_
 __global__ void __launch_bounds__(32 * kSeedWarps)
 seed_anchor_kernel(int n, const uint8_t* __restrict__ enc_seq, const uint8_t* __restrict__ enc_ref,
                    const int64_t* __restrict__ seq_off, const int64_t* __restrict__ ref_off,
-                   uint16_t* __restrict__ anchor) {
+                   uint16_t* __restrict__ anchor, const FilterRec* __restrict__ sub = nullptr) {
+    // sub: pairs the k-mer filter gave a column range (band_filter.cuh) need no anchor (fwd_keys_kernel ignores it)
     __shared__ uint32_t table[kSeedWarps][kSeedTable];
     __shared__ unsigned int bins[kSeedWarps][kSeedBins / 2];  // two 16-bit counters per word
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -362,6 +372,10 @@ seed_anchor_kernel(int n, const uint8_t* __restrict__ enc_seq, const uint8_t* __
         const int64_t qo = seq_off[p], ro = ref_off[p];
         const int q = (int)(seq_off[p + 1] - qo), w = (int)(ref_off[p + 1] - ro);
         int col = 0;
+        if (sub && sub[p].margin_bins != 0) {
+            if (lane == 0) anchor[p] = 0;
+            continue;
+        }
         if (q >= kSeedK && w >= kSeedK && q <= 4096 && w + q <= 32 * kSeedBins) {  // uniform per warp
             tag = tag == 0xFFFFFu ? 1u : tag + 1u;
             for (int i = lane; i < kSeedBins / 2; i += 32) bin[i] = 0u;
@@ -412,20 +426,27 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
                                 int max_cols, uint32_t* __restrict__ keys, int* __restrict__ vals,
                                 int* __restrict__ hist, cudasw_result* __restrict__ res,
                                 const int* __restrict__ any_n, const uint8_t* __restrict__ wflags,
-                                const uint16_t* __restrict__ anchor, unsigned long long* __restrict__ cell_counts) {
+                                const uint16_t* __restrict__ anchor, unsigned long long* __restrict__ cell_counts,
+                                const FilterRec* __restrict__ sub = nullptr, const uint8_t* __restrict__ done = nullptr) {
+    // sub: the k-mer filter's column ranges (band_filter.cuh): the forward pass sweeps ws = sub[p].wlen columns.
+    // done != nullptr: the second (full-window) pass after the filter: pairs with done[p] != 0 have nothing left to do.
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     // cell_counts: [0] sum of q*w, [1] cells the forward kernels compute (padded rows, fill/drain columns)
     unsigned long long my_cells = 0, my_padded = 0;
-    int64_t q = 0, w = 0;
+    int64_t q = 0, w = 0, ws = 0;
+    const bool skip = p < n && done && done[p];
+    bool banded = false;
     if (p < n) {
         q = seq_off[p + 1] - seq_off[p];
         w = ref_off[p + 1] - ref_off[p];
-        if (q > 0 && w > 0) {
-            my_cells = (unsigned long long)q * (unsigned long long)w;
+        ws = w;
+        if (sub) { const FilterRec fr = sub[p]; ws = fr.wlen; banded = fr.margin_bins != 0; }
+        if (q > 0 && w > 0 && !skip) {
+            if (!done) my_cells = (unsigned long long)q * (unsigned long long)w;
             if (q <= max_rows) {
                 const int v0 = variant_of(vt, (int)q);
                 const unsigned long long strips = ((unsigned long long)q + vt.rows[v0] - 1) / vt.rows[v0];
-                my_padded = strips * (unsigned long long)vt.rows[v0] * (unsigned long long)(w + 2 * vt.lanes[v0] - 1);
+                my_padded = strips * (unsigned long long)vt.rows[v0] * (unsigned long long)(ws + 2 * vt.lanes[v0] - 1);
             }
         }
     }
@@ -434,7 +455,7 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
         my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
         my_padded += __shfl_xor_sync(0xffffffffu, my_padded, o);
     }
-    if ((threadIdx.x & 31) == 0 && my_cells) { atomicAdd(cell_counts, my_cells); atomicAdd(cell_counts + 1, my_padded); }
+    if ((threadIdx.x & 31) == 0 && (my_cells | my_padded)) { atomicAdd(cell_counts, my_cells); atomicAdd(cell_counts + 1, my_padded); }
     if (p >= n) return;
     cudasw_result r;
     r.score = 0; r.ref_begin = -1; r.ref_end = -1; r.read_begin = 0; r.read_end = 0;
@@ -443,14 +464,17 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
     // slots [0, n): query-profile flavour, [n, 2n): xor-selector flavour, 2n: nothing to do
     if (q <= 0 || w <= 0) { r.status = CUDASW_EINVAL; v = 2 * vt.n; }
     else if (q > max_rows || w > max_cols) { r.status = CUDASW_ETOOLARGE; v = 2 * vt.n; }
+    else if (skip) v = 2 * vt.n;
     else v = variant_of(vt, (int)q) + ((*any_n != 0 && wflags[p]) ? vt.n : 0);
-    res[p] = r;
+    if (!done) res[p] = r;
+    w = ws;
     // key = (slot : 7 | 0x1FFF - window length / 64 : 13 | seed anchor column / 4 : 12): inside a slot the LONGEST windows
     // come first, so the CTAs that run longest start first and a launch does not end in a tail of its slowest pairs
     // (mixed-length batches: C3's forward pass took twice as long with its variants launched one after the other)
     uint32_t wq = (uint32_t)(w >> 6);
     if (wq > 0x1FFFu) wq = 0x1FFFu;
-    keys[p] = ((uint32_t)v << 25) | ((0x1FFFu - wq) << 12) | (uint32_t)anchor[p];
+    // (a banded pair's alignment sits in the middle of its column range: no anchor needed to line the warps up)
+    keys[p] = ((uint32_t)v << 25) | ((0x1FFFu - wq) << 12) | (banded ? 0u : (uint32_t)anchor[p]);
     vals[p] = p;
     atomicAdd(&hist[v], 1);
 }
@@ -598,6 +622,11 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             w = (int)(io.ref_off[pair + 1] - ro);
             qptr += qo;
             rptr += ro;
+            if (io.sub) {  // the filter's column range: a window of its own as far as this kernel is concerned
+                const FilterRec fr = io.sub[pair];
+                rptr += fr.c0;
+                w = fr.wlen;
+            }
         }
     }
     constexpr int STEP = REV ? -1 : 1;
@@ -690,7 +719,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
 
     // ---- quiet chains (CHAIN flavours only; see qstep below)
 #ifndef CUSW_CHAIN_GATE  // A/B switch for tools/exp_build_run.sh
-#define CUSW_CHAIN_GATE 3
+#define CUSW_CHAIN_GATE 2  // (3 before the k-mer filter: its column ranges are ~2.5 x the rows, and chains pay there: C2 forward 24.0 -> 23.05 ms per 400 k pairs)
 #endif
     constexpr bool CHAIN = CHN && PROF && !REV && !MULTI;
     bool chain = false;  // warp-uniform: the previous step was a verified quiet step
@@ -1004,6 +1033,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         int score = (int)(key >> 40) - sc.B;
         int col = (int)(0xFFFFFFu - (uint32_t)((key >> 16) & 0xFFFFFFu)) - 1;
         int row = (int)(0xFFFFu - (uint32_t)(key & 0xFFFFu));
+        if (!REV && io.sub) col += io.sub[pair].c0;
         out[pair] = make_int4(score, col, row, failed ? 1 : 0);
     }
 }

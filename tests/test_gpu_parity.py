@@ -725,3 +725,92 @@ def test_strip_mined_queries_across_many_chunks(aligner, oracle, monkeypatch):
     monkeypatch.setenv("CUDASW_REV_FULL", "1")  # round 1's full-rectangle reverse kernels (strip pool sized for the whole batch)
     bad, undef = _compare(aligner, oracle, seqs, refs)
     assert bad == [] and undef == 0, bad[:3]
+
+
+# ---- the k-mer filter in front of the forward pass (csrc/band_filter.cuh): identical results with and without it
+def _digest_on_off(sb, so, rb, ro, monkeypatch, scoring=(1, -4, -4, 6, 1)):
+    import gridss_b200 as gb
+    from gridss_b200.shard import pair_digests
+
+    monkeypatch.setenv("CUDASW_FILTER", "0")
+    off = gb.AlignerFactory.create(*scoring)
+    monkeypatch.setenv("CUDASW_FILTER", "1")
+    on = gb.AlignerFactory.create(*scoring)
+    r0, c0 = off.align_blobs(sb, so, rb, ro)
+    r1, c1 = on.align_blobs(sb, so, rb, ro)
+    d0, d1 = pair_digests(r0, c0), pair_digests(r1, c1)
+    off.close()
+    on.close()
+    return np.flatnonzero(d0 != d1), r0, r1
+
+
+@pytest.mark.parametrize("cfg,n", [(1, 60000), (2, 40000), (3, 6000), (4, 50000)])
+def test_filter_on_off_identical_on_configs(synth, monkeypatch, cfg, n):
+    sb, so, rb, ro = synth.generate(cfg, n)
+    bad, r0, r1 = _digest_on_off(sb, so, rb, ro, monkeypatch)
+    assert bad.size == 0, (bad[:5], r0[bad[:3]], r1[bad[:3]])
+
+
+def _repeat_cases(rng, n):
+    """Pairs built to mislead a seed filter: the query occurs several times in the window (exactly, or with a few edits, or with a
+    gap), copies at equal score in different columns (tie-break: the FIRST column wins), tandem repeats, a strong decoy far away
+    from a slightly better true hit, queries that are half noise."""
+    A = np.frombuffer(b"ACGT", dtype=np.uint8)
+    seqs, refs = [], []
+    for t in range(n):
+        q = int(rng.integers(40, 600))
+        w = int(rng.integers(2 * q + 400, 7000))
+        ref = rng.choice(A, size=w)
+        core = rng.choice(A, size=q)
+        kind = t % 6
+        def put(at, s):
+            at = max(0, min(w - len(s), at))
+            ref[at: at + len(s)] = s
+        def edit(s, k):
+            s = s.copy()
+            for x in rng.integers(0, len(s), size=k):
+                s[x] = rng.choice(A)
+            return s
+        if kind == 0:    # two exact copies
+            put(int(rng.integers(0, w // 2 - q)) if w // 2 > q else 0, core); put(int(rng.integers(w // 2, w - q)), core)
+        elif kind == 1:  # a decoy with a few more edits, placed FIRST
+            put(int(rng.integers(0, w // 2 - q)) if w // 2 > q else 0, edit(core, 3)); put(int(rng.integers(w // 2, w - q)), edit(core, 2))
+        elif kind == 2:  # tandem repeat unit in both
+            unit = rng.choice(A, size=int(rng.integers(2, 30)))
+            core = np.resize(unit, q)
+            put(int(rng.integers(0, w - 3 * q)) if w > 3 * q else 0, np.resize(unit, min(3 * q, w)))
+        elif kind == 3:  # copy with a long gap in the window, and an ungapped shorter copy elsewhere
+            g = int(rng.integers(5, 120))
+            h = q // 2
+            s = np.concatenate([core[:h], rng.choice(A, size=g), core[h:]])
+            put(int(rng.integers(0, max(1, w // 2 - len(s)))), s); put(int(rng.integers(w // 2, w - q)), core[: int(q * 0.8)])
+        elif kind == 4:  # half of the query is noise; two copies of the good half
+            core[q // 2:] = rng.choice(A, size=q - q // 2)
+            hq = core[: q // 2]
+            put(int(rng.integers(0, w - q)), hq); put(int(rng.integers(0, w - q)), edit(hq, 1))
+        else:            # many weak copies
+            for _ in range(6):
+                put(int(rng.integers(0, w - q)), edit(core, int(rng.integers(0, max(2, q // 10)))))
+        seqs.append(core.tobytes())
+        refs.append(ref.tobytes())
+    return seqs, refs
+
+
+def test_filter_repeats_decoys_and_ties_vs_oracle(aligner, oracle, monkeypatch):
+    from gridss_b200.aligner import pack
+
+    rng = np.random.default_rng(20260)
+    seqs, refs = _repeat_cases(rng, 1800)
+    bad, undef = _compare(aligner, oracle, seqs, refs)
+    assert bad == [], bad[:3]
+    sb, so = pack(seqs)
+    rb, ro = pack(refs)
+    bad2, r0, r1 = _digest_on_off(sb, so, rb, ro, monkeypatch)
+    assert bad2.size == 0, (bad2[:5], r0[bad2[:3]], r1[bad2[:3]])
+
+
+def test_filter_other_scorings_on_off(synth, monkeypatch):
+    sb, so, rb, ro = synth.generate(3, 3000)
+    for sc in ((2, -3, -1, 5, 2), (1, -1, -1, 2, 1), (3, -2, -2, 4, 0), (1, -4, -4, 0, 1), (5, -4, -4, 10, 1)):
+        bad, r0, r1 = _digest_on_off(sb, so, rb, ro, monkeypatch, sc)
+        assert bad.size == 0, (sc, bad[:5], r0[bad[:3]], r1[bad[:3]])
