@@ -22,6 +22,17 @@
 // true H is >= S0 is reached by paths inside the computed rectangle only: its value there is exact, the maximum is the
 // true maximum and the set of cells holding it - all the reference's tie-break (first column, then smallest row,
 // ssw.c:283-306) looks at - is the same. Otherwise the pair is handed to the full-window pass.
+//
+// A tighter margin from the hits themselves ("evidence"). A run of r matches holds at most max(0, r - (k-1)) + (k-1)
+// bases, so M <= hits(P) + (k-1)(X + g + 1); with (1): S0 <= a hits(P) + a(k-1) + X (a(k-1) - p) + g (a(k-1) - go)
+// - ge (Lg - g), and X <= Xmax(S0) = (a n - S0) / (p + a) (from M + X <= n and a M >= S0 + p X). When go > a(k-1) and
+// ge > 0 that bounds the gap bases of P by its hits: Lg <= R / min(go - a(k-1), ge), R = a hits(P) + a(k-1) - S0 +
+// max(0, a(k-1) - p) Xmax. A path whose bins all lie outside the core [b-1, b+2] is excluded by the noise test above; any
+// other path spanning m bins lies inside bins [b-1-(m-1), b+2+(m-1)], whose hit total hc(m-1) bounds hits(P). Starting
+// from m = m(L(S0)) and iterating m <- min(m, m(Lg bound from hc(m-1))) only ever applies sound implications, so its
+// fixed point m_t bounds the bins of EVERY path of score >= S0, and the band only needs a margin of m_t bins. The same
+// bound on Lg (gap_bound) narrows the band of the reverse pass (rev_band.cuh), whose paths are alignment paths of
+// score S0 ending in the forward pass's cell.
 #pragma once
 #include "sw_kernels.cuh"
 
@@ -40,7 +51,10 @@ struct FilterConst {
     int a, go, ge;       // match, gap open, gap extend
     long long cn, cd;    // rho = cn / cd = min(0, (p - (k-1) a) / (p + a), (go - (k-1) a) / go), cd > 0
     int est_pct;         // the margin is sized for a score of est_pct % of (a * hits of the densest bin pair)
+    int ev_div;          // min(go - a(k-1), ge) when both are positive, else 0: no evidence bound for this scoring
+    int ev_alpha, ev_pa; // max(0, a(k-1) - p); p + a
 };
+constexpr int kFltHc = 16;  // hc(j), j < kFltHc, is kept per pair for the certificate
 
 inline FilterConst make_filter_const(int match, int mismatch, int ambiguous, int go, int ge) {
     FilterConst f{};
@@ -53,6 +67,9 @@ inline FilterConst make_filter_const(int match, int mismatch, int ambiguous, int
     };
     take(p - k1 * a, p + a);
     take(go - k1 * a, go);
+    f.ev_div = (go - k1 * a > 0 && ge > 0) ? (int)std::min<long long>(go - k1 * a, ge) : 0;
+    f.ev_alpha = (int)std::max<long long>(0, k1 * a - p);
+    f.ev_pa = (int)(p + a);
     return f;
 }
 
@@ -69,12 +86,31 @@ __host__ __device__ __forceinline__ long long flt_hits_floor(const FilterConst& 
 // m(L): bins of 32 diagonals that a window of L + 1 consecutive diagonals can touch
 __host__ __device__ __forceinline__ int flt_bins_of(long long L) { return (int)((L + 31) >> kFltBinShift) + 1; }
 
+// The evidence iteration (header): hc(j) = hits in the core bins extended by j bins either side. Starts from m0 bins (from the
+// worst-case gap bound L0), returns the fixed point m_t and leaves the gap-base bound that goes with it in *gap_bound.
+template <typename HC>
+__host__ __device__ __forceinline__ int flt_tight_bins(const FilterConst& f, long long S, long long n, int m0, long long L0, HC&& hc, long long* gap_bound) {
+    *gap_bound = L0;
+    if (f.ev_div == 0 || m0 - 1 >= kFltHc) return m0;
+    const long long xmax = ((long long)f.a * n - S) / f.ev_pa;
+    int m = m0;
+    for (int it = 0; it < 16; it++) {
+        long long R = (long long)f.a * (long long)hc(m - 1) + (long long)f.a * (kFltK - 1) - S + (long long)f.ev_alpha * (xmax > 0 ? xmax : 0);
+        long long Lt = R > 0 ? R / f.ev_div : 0;
+        if (Lt < *gap_bound) *gap_bound = Lt;
+        const int m2 = flt_bins_of(*gap_bound);
+        if (m2 >= m) break;
+        m = m2;
+    }
+    return m;
+}
+
 #ifdef CUSW_MAIN_TU
 // One warp per pair. Shared memory per warp: heads[4^k] (first query row + 1 of every k-mer), link[row] (next row with
 // the same k-mer), bins[diagonal / 32]; all 16 bit.
 __global__ void __launch_bounds__(32 * kFltWarps)
 filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __restrict__ wflags, FilterConst fc,
-              FilterRec* __restrict__ rec, unsigned long long* __restrict__ counters) {
+              FilterRec* __restrict__ rec, uint32_t* __restrict__ hc_out, unsigned long long* __restrict__ counters) {
     extern __shared__ __align__(16) unsigned char flt_smem[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     unsigned short* heads = reinterpret_cast<unsigned short*>(flt_smem + (size_t)wib * kFltSmemPerWarp);
@@ -84,7 +120,7 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
     for (int p = blockIdx.x * kFltWarps + wib; p < n; p += gridDim.x * kFltWarps) {
         const int64_t qo = io.seq_off[p], ro = io.ref_off[p];
         const int q = (int)(io.seq_off[p + 1] - qo), w = (int)(io.ref_off[p + 1] - ro);
-        FilterRec r{0, w, 0, 0};
+        FilterRec r{0, w, 0, 0, -1};
         const bool eligible = fc.ok && q >= kFltK && w >= kFltK && q <= kFltMaxQ && (long long)q + w <= 32ll * kFltMaxBins - 64 &&
                               !(*any_n != 0 && wflags[p]);
         if (!eligible) {  // warp-uniform
@@ -100,7 +136,7 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
             for (int i = lane; i < (nb + 3) / 2; i += 32) bins2[i] = 0u;
         }
         __syncwarp();
-        // Both sequences are read 512 bases per step, one aligned 16-byte vector per lane (prefetched a step ahead); a lane
+        // Both sequences are read 512 bases per step, one aligned 16-byte vector per lane (prefetched two steps ahead); a lane
         // owns the k-mers that END in its vector and gets the five bases before it from the lane below (lane 0: from the
         // previous step). body(vc, vn, pos0, checked): k-mer u of the lane (u = 0 .. 15) starts at base pos0 + u, its value is
         // bits [2u, 2u + 12) of vc (sum of code[pos + t] << 2t), bits [2u, 2u + 12) of vn are non-zero when it holds an N
@@ -112,11 +148,12 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
             const int ntiles = (total + 511) >> 9;
             auto load = [&](int vi) { return 16 * vi < total ? al[vi] : make_uint4(0u, 0u, 0u, 0u); };
             auto c8 = [](uint32_t x) { return ((x & 0x03030303u) * 0x01041040u) >> 24; };  // four bytes -> four 2-bit codes
-            uint4 nxt = load(lane);
+            uint4 nxt = load(lane), nxt2 = load(32 + lane);  // two steps in flight: the kernel lives on HBM latency
             uint32_t carry_c = 0u, carry_n = 0u;
             for (int t = 0; t < ntiles; t++) {
                 const uint4 cur = nxt;
-                nxt = load(32 * (t + 1) + lane);
+                nxt = nxt2;
+                nxt2 = load(32 * (t + 2) + lane);
                 const uint32_t c32 = c8(cur.x) | (c8(cur.y) << 8) | (c8(cur.z) << 16) | (c8(cur.w) << 24);
                 uint32_t n32 = 0u;
                 if (check_n) n32 = c8(cur.x >> 2) | (c8(cur.y >> 2) << 8) | (c8(cur.z >> 2) << 16) | (c8(cur.w >> 2) << 24);
@@ -190,21 +227,15 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
             if (oh > bh || (oh == bh && ob < bb)) { bh = oh; bb = ob; }
         }
         const long long nmin = min(q, w);
-        const long long s_est = (long long)fc.a * bh * fc.est_pct / 100;
-        const long long L = s_est > 0 ? max_gap_bases(nmin, fc.a, (int)min(s_est, 32767ll), fc.go, fc.ge) : -1;
+        const long long s_est = min((long long)fc.a * bh * fc.est_pct / 100, 32767ll);
+        const long long L = s_est > 0 ? max_gap_bases(nmin, fc.a, (int)s_est, fc.go, fc.ge) : -1;
         bool go_on = L >= 0;
-        int m_r = 0;
+        int m_old = 0, m_band = 0;
         long long c0 = 0, c1 = w - 1;
-        if (go_on) {
-            m_r = flt_bins_of(L);
-            const long long Dlo = 32ll * (bb - m_r), Dhi = 32ll * (bb + 2 + m_r) - 1;  // diagonal index j - i + q - 1
-            c0 = max(0ll, Dlo - (q - 1));
-            c1 = min((long long)w - 1, Dhi);
-            go_on = (c1 - c0 + 1) * 10 <= 7ll * w;  // otherwise nothing to win
-        }
         uint32_t noise = 0u;
         if (go_on) {  // warp-uniform
-            // inclusive prefix sums of the bins, in place
+            m_old = flt_bins_of(L);
+            // inclusive prefix sums of the bins
             uint32_t carry = 0u;
             for (int base = 0; base < nb; base += 32) {
                 const int b = base + lane;
@@ -219,20 +250,33 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
                 carry = __shfl_sync(0xffffffffu, v, 31);
             }
             __syncwarp();
-            // runs [bs, be) of m_r bins that lie entirely left of bin bb - 1 or right of bin bb + 2
+            // runs [bs, be) of m_old bins that lie entirely left of bin bb - 1 or right of bin bb + 2
             for (int bs = lane; bs < nb; bs += 32) {
-                const int be = min(bs + m_r, nb);
+                const int be = min(bs + m_old, nb);
                 if (be - 1 <= bb - 2 || bs >= bb + 3) {
                     const uint32_t s = psum[be - 1] - (bs > 0 ? psum[bs - 1] : 0u);
                     noise = max(noise, s);
                 }
             }
             noise = __reduce_max_sync(0xffffffffu, noise);
-            // not worth trying when even the estimated score could not be told from the noise
-            go_on = flt_hits_floor(fc, (long long)fc.a * bh, nmin) > (long long)noise;
+            // hc(lane): hits of the core bins [bb - 1, bb + 2] extended by `lane` bins either side
+            uint32_t my_hc;
+            {
+                const int lo = max(0, bb - 1 - lane), hi = min(nb - 1, bb + 2 + lane);
+                my_hc = psum[hi] - (lo > 0 ? psum[lo - 1] : 0u);
+            }
+            if (lane < kFltHc) hc_out[(size_t)p * kFltHc + lane] = my_hc;
+            long long gb;
+            m_band = flt_tight_bins(fc, s_est, nmin, m_old, L, [&](int j) { return __shfl_sync(0xffffffffu, my_hc, j); }, &gb);
+            const long long Dlo = 32ll * (bb - m_band), Dhi = 32ll * (bb + 2 + m_band) - 1;  // diagonal index j - i + q - 1
+            c0 = max(0ll, Dlo - (q - 1));
+            c1 = min((long long)w - 1, Dhi);
+            // nothing to win when the range is most of the window; not worth trying when even the estimated score could not
+            // be told from the noise
+            go_on = m_old <= 255 && (c1 - c0 + 1) * 10 <= 7ll * w && flt_hits_floor(fc, (long long)fc.a * bh, nmin) > (long long)noise;
         }
         if (lane == 0) {
-            if (go_on) { r.c0 = (int32_t)c0; r.wlen = (int32_t)(c1 - c0 + 1); r.margin_bins = m_r; r.noise = (int32_t)noise; }
+            if (go_on) { r.c0 = (int32_t)c0; r.wlen = (int32_t)(c1 - c0 + 1); r.margin_bins = m_band | (m_old << 8); r.noise = (int32_t)noise; }
             rec[p] = r;
             if (counters) atomicAdd(counters + (go_on ? 0 : 1), 1ull);
         }
@@ -244,22 +288,33 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
 // 0 sends the pair to the full-window pass (its record is then reset to the whole window).
 __global__ void filter_certify_kernel(int n, const int64_t* __restrict__ seq_off, const int64_t* __restrict__ ref_off,
                                       const int4* __restrict__ fwd, FilterConst fc, FilterRec* __restrict__ rec,
-                                      uint8_t* __restrict__ done, unsigned long long* __restrict__ counters) {
+                                      const uint32_t* __restrict__ hc_in, uint8_t* __restrict__ done,
+                                      unsigned long long* __restrict__ counters) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     FilterRec r = rec[p];
     if (r.margin_bins == 0) { done[p] = 1; return; }  // the first pass already swept the whole window
+    const int m_band = r.margin_bins & 0xFF, m_old = r.margin_bins >> 8;
     const long long q = seq_off[p + 1] - seq_off[p], w = ref_off[p + 1] - ref_off[p];
     const long long nmin = q < w ? q : w;
     const int4 f = fwd[p];
     bool ok = f.w == 0 && f.x > 0;
+    long long gb = -1;
     if (ok) {
         const long long L = max_gap_bases(nmin, fc.a, f.x, fc.go, fc.ge);
-        ok = L >= 0 && flt_bins_of(L) <= r.margin_bins && flt_hits_floor(fc, f.x, nmin) > (long long)r.noise;
+        // paths outside the core: too few hits in any window they could span
+        ok = L >= 0 && flt_bins_of(L) <= m_old && flt_hits_floor(fc, f.x, nmin) > (long long)r.noise;
+        if (ok) {  // paths through the core: inside the band
+            const uint32_t* hc = hc_in + (size_t)p * kFltHc;
+            ok = flt_tight_bins(fc, f.x, nmin, flt_bins_of(L), L, [&](int j) { return hc[j]; }, &gb) <= m_band;
+        }
     }
     done[p] = ok ? 1 : 0;
-    if (!ok) {
-        r.c0 = 0; r.wlen = (int32_t)w; r.margin_bins = 0; r.noise = 0;
+    if (ok) {
+        r.gap_bound = (int32_t)gb;
+        rec[p] = r;
+    } else {
+        r.c0 = 0; r.wlen = (int32_t)w; r.margin_bins = 0; r.noise = 0; r.gap_bound = -1;
         rec[p] = r;
         if (counters) atomicAdd(counters + 2, 1ull);
     }

@@ -162,6 +162,7 @@ struct cudasw {
     FilterConst fc{};
     bool use_filter = false;
     DevBuf<FilterRec> frec;
+    DevBuf<uint32_t> fhc;  // per pair: hits of the core bins extended by j bins either side, j < kFltHc
     DevBuf<uint8_t> fdone;
     DevBuf<int> fwd_slots2;
     DevBuf<uint8_t> cub_tmp_fwd2;
@@ -435,7 +436,7 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     if (h->d_hist) cudaFree(h->d_hist);
     if (h->d_hist2) cudaFree(h->d_hist2);
     if (h->d_fcount) cudaFree(h->d_fcount);
-    h->frec.release(); h->fdone.release(); h->fwd_slots2.release(); h->cub_tmp_fwd2.release();
+    h->frec.release(); h->fhc.release(); h->fdone.release(); h->fwd_slots2.release(); h->cub_tmp_fwd2.release();
     if (h->d_rev_slots) cudaFree(h->d_rev_slots);
     for (auto& r : h->rev_ring) r.release();
     if (h->d_pool) cudaFree(h->d_pool);
@@ -581,7 +582,7 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     if (use_filter) {
         // per pair: hits per diagonal bin -> the column range the forward pass sweeps first (band_filter.cuh)
         filter_kernel<<<(int)std::min<int64_t>((n + kFltWarps - 1) / kFltWarps, 148 * 2 * 8), 32 * kFltWarps, kFltWarps * kFltSmemPerWarp, st>>>(
-            (int)n, io, any_n, wflags.p + first, fc, frec.p + first, d_fcount);
+            (int)n, io, any_n, wflags.p + first, fc, frec.p + first, fhc.p + (size_t)first * kFltHc, d_fcount);
         launches++;
     }
     seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
@@ -629,7 +630,7 @@ int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* 
         int* any_n = reinterpret_cast<int*>(d_counters + 5);
         int* slots2 = fwd_slots2.p + ci * (size_t)(2 * (2 * g_nvar + 1));
         filter_certify_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, fwd.p + first, fc, frec.p + first,
-                                                                     fdone.p + first, d_fcount);
+                                                                     fhc.p + (size_t)first * kFltHc, fdone.p + first, d_fcount);
         CK(cudaMemsetAsync(d_hist2, 0, 256 * sizeof(int), st));
         fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
                                                                keys.p + first, vals.p + first, d_hist2, res.p + first, any_n,
@@ -658,6 +659,7 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
     cudaEvent_t* join_ev = post_set.join_ev;
     uint64_t launches = 0;
     PairIO io{enc_seq.p, enc_ref.p, d_so + first, d_ro + first};
+    if (use_filter) io.sub = frec.p + first;  // the banded reverse pass reads the certified gap bounds
     int4* fwd_c = fwd.p + first;
     int4* rev_c = rev.p + first;
     cudasw_result* res_c = res.p + first;
@@ -678,7 +680,7 @@ int cudasw::post_chunk(size_t ci, int64_t first, int64_t n, const int64_t* d_so,
         CK(cudaMemsetAsync(dhr, 0, 32 * sizeof(int), st));
         const int few_pairs = n < 4096 ? 1 : 0;
         rev_band_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, fwd_c, res_c, sc.match, sc.B, sc.ge, few_pairs, keys.p, vals.p, dhr,
-                                                                    reinterpret_cast<int*>(d_counters + 5), wflags_c);
+                                                                    reinterpret_cast<int*>(d_counters + 5), wflags_c, io.sub);
         launches++;
         CK(cub::DeviceRadixSort::SortPairs(cub_tmp_post.p, cub_bytes, keys.p, keys_alt.p, vals.p, vals_alt.p, (int)n, 0, 24, st));
         launches += 3;
@@ -1153,7 +1155,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         if (use_filter) CK(cub_tmp_fwd2.ensure(cub_bytes + 16));
     }
     CK(fwd_slots.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1))));
-    if (use_filter) { CK(frec.ensure(n)); CK(fdone.ensure(n)); CK(fwd_slots2.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1)))); }
+    if (use_filter) { CK(frec.ensure(n)); CK(fhc.ensure((size_t)n * kFltHc)); CK(fdone.ensure(n)); CK(fwd_slots2.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1)))); }
     batch_maybe_n = !(packed && packed->refN == nullptr);
     if (!tb_pool.p) {
         size_t free_b = 0, total_b = 0;

@@ -52,7 +52,8 @@ __host__ __device__ __forceinline__ long long rev_ring_half(int v, long long max
 // that tolerates N in the window), 2 * kRevVariants = nothing to walk back; inside a slot the long jobs come first.
 __global__ void rev_band_keys_kernel(int n, const int4* __restrict__ fwd, cudasw_result* __restrict__ res, int match, int go,
                                      int ge, int few_pairs, uint32_t* __restrict__ keys, int* __restrict__ vals,
-                                     int* __restrict__ hist, const int* __restrict__ any_n, const uint8_t* __restrict__ wflags) {
+                                     int* __restrict__ hist, const int* __restrict__ any_n, const uint8_t* __restrict__ wflags,
+                                     const FilterRec* __restrict__ sub = nullptr) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const int4 f = fwd[p];
@@ -63,6 +64,7 @@ __global__ void rev_band_keys_kernel(int n, const int4* __restrict__ fwd, cudasw
         const int rows = f.z + 1;
         long long L = max_gap_bases(rows, match, f.x, go, ge);
         if (L < 0 || L > f.y + 1) L = f.y + 1;
+        if (sub) { const int gb = sub[p].gap_bound; if (gb >= 0 && gb < L) L = gb; }
         const int v = rev_variant_of(rows, L, few_pairs);
         slot = v + ((*any_n != 0 && wflags[p]) ? kRevVariants : 0);
         const long long S = 32ll * rev_variant_lanes(v);
@@ -136,6 +138,10 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
         rptr += io.ref_off[pair] + f.y;
         dmax = max_gap_bases(q, sc.match, target, sc.B, sc.ge);
         if (dmax < 0 || dmax > (long long)q + w) dmax = (long long)q + w;  // unbounded: no cell is outside the band
+        if (io.sub) {  // the k-mer filter's proven bound on the gap bases of any alignment of this score (band_filter.cuh)
+            const int gb = io.sub[pair].gap_bound;
+            if (gb >= 0 && gb < dmax) dmax = gb;
+        }
         // an alignment of `target` inside q rows spans at most q + dmax columns
         const long long lim = (long long)q + dmax + 1;
         if (lim < w) w = (int)lim;

@@ -296,8 +296,9 @@ struct ScoreConst {
 // sweeps the whole window.
 struct FilterRec {
     int32_t c0, wlen;     // the forward pass sweeps window columns [c0, c0 + wlen)
-    int32_t margin_bins;  // m_r
-    int32_t noise;        // most hits in any run of m_r bins outside the band's core
+    int32_t margin_bins;  // bins of margin either side of the core: m_band | (m_old << 8)
+    int32_t noise;        // most hits in any run of m_old bins outside the band's core
+    int32_t gap_bound;    // once certified: no alignment of the pair's score has more gap bases than this (-1: not known)
 };
 
 struct PairIO {

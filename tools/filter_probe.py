@@ -9,6 +9,8 @@ import numpy as np
 
 K = 6
 BIN = 32
+EVIDENCE = True
+REV = []
 
 
 def max_gap_bases(rows, match, target, go, ge):
@@ -139,6 +141,33 @@ def probe(cfg, n, sc=(1, -4, -4, 6, 1), est=0.8, est_t=1.0):
             be = min(bs + m_r, nb)
             if be - 1 <= bstar - 2 or bs >= bstar + 3:
                 noise = max(noise, int(cs[be] - cs[bs]))
+        # evidence-based gap bound: a path through the core sees at most hc(j) hits when it spans j extra bins either side
+        def hc(j):
+            lo, hi = max(0, bstar - 1 - j), min(nb - 1, bstar + 2 + j)
+            return int(cs[hi + 1] - cs[lo])
+
+        def m_tight(S, m0):
+            a, mm, amb, go, ge = sc
+            kap = K - 1
+            pmin = min(-mm, -amb)
+            if go - a * kap <= 0 or ge <= 0:
+                return m0, None
+            xmax = (a * nmin - S) // (pmin + a)
+            alpha = max(0, a * kap - pmin)
+            m = m0
+            Lt = None
+            for _ in range(8):
+                R = a * hc(m - 1) + a * kap - S + alpha * xmax
+                Lt = max(0, R // min(go - a * kap, ge))
+                m2 = min(m, bins_of(Lt))
+                if m2 == m:
+                    break
+                m = m2
+            return m, Lt
+
+        m_old = m_r
+        if EVIDENCE:
+            m_r, _ = m_tight(S_est, m_old)
         Dlo, Dhi = BIN * (bstar - m_r), BIN * (bstar + 2 + m_r) - 1
         Dlo, Dhi = max(Dlo, 0), min(Dhi, q + w - 2)
         wd = Dhi - Dlo + 1
@@ -153,13 +182,25 @@ def probe(cfg, n, sc=(1, -4, -4, 6, 1), est=0.8, est_t=1.0):
         n_try += 1
         S0 = int(m.res[p]["score"])  # (the band DP's score; equals the true one whenever the certificate holds)
         Lg0 = max_gap_bases(nmin, sc[0], S0, sc[3], sc[4])
-        ok = S0 > 0 and Lg0 >= 0 and bins_of(Lg0) <= m_r and hits_floor(S0, nmin, sc) > noise
+        if EVIDENCE:
+            ok = S0 > 0 and Lg0 >= 0 and bins_of(Lg0) <= m_old and hits_floor(S0, nmin, sc) > noise
+            if ok:
+                mt, Lt = m_tight(S0, bins_of(Lg0))
+                ok = mt <= m_r
+                if ok:
+                    REV.append((Lg0, min(Lg0, Lt) if Lt is not None else Lg0))
+        else:
+            ok = S0 > 0 and Lg0 >= 0 and bins_of(Lg0) <= m_r and hits_floor(S0, nmin, sc) > noise
         if ok:
             n_cert += 1
             band_cells += cells
         else:
             why["cert failed"] = why.get("cert failed", 0) + 1
             band_cells += cells + full
+    if REV:
+        r = np.array(REV)
+        print(f"   forward gap bound: worst-case {r[:, 0].mean():.1f} -> evidence {r[:, 1].mean():.1f} (mean over certified pairs)")
+        REV.clear()
     print(f"C{cfg}: pairs {n} tried {n_try} certified {n_cert}; cells visited {band_cells / tot_cells:.3f} of full; other: {why}")
 
 
