@@ -248,6 +248,8 @@ def main():
     fwd_ms = 0.0
     launches = 0
     phase = {}
+    visited_cells = 0.0
+    flt_banded = flt_failed = 0
     for _ in range(args.steps):
         st = step_device()
         dev_ms += st["ms_total"]
@@ -256,6 +258,8 @@ def main():
         for k in ("ms_pack", "ms_encode", "ms_forward", "ms_reverse", "ms_traceback", "ms_d2h"):
             phase[k] = phase.get(k, 0.0) + st[k] / args.steps
         enc_bytes = st["encode_bytes"]
+        visited_cells += float(st["forward_cells_padded"])
+        flt_banded, flt_failed = int(st["filter_banded"]), int(st["filter_failed"])
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.summary()
@@ -419,7 +423,12 @@ def main():
         total_pairs = float(n) * world * args.steps
         total_cells = cells_per_step * world * args.steps
         value = total_pairs / (dev_ms / 1e3)
-        fwd_cups = cells_per_step * args.steps / (fwd_ms / 1e3)  # one GPU's kernel (rank max time)
+        # Cells: the k-mer filter (csrc/band_filter.cuh) lets the forward kernels sweep a proven column range of most
+        # windows, so the cells they VISIT (counted on the device, padded rows and fill/drain columns included) are a fraction
+        # of the algorithmic q x w. The roofline is about the kernel: it counts visited cells; the algorithmic rate is
+        # reported beside it as gcups_effective.
+        eff_cups = cells_per_step * args.steps / (fwd_ms / 1e3)  # q x w of every pair / forward time (rank max time)
+        fwd_cups = visited_cells / (fwd_ms / 1e3)                # cells the forward kernels computed / forward time
         peak_laneops = sms * 128 * f_sm  # INT32 lane-ops/s at the clock seen during the run
         achieved_laneops = fwd_cups * INT_OPS_PER_CELL / 2.0  # packed s16x2: two cells per lane-op
         # the integer pipes measured on THIS box in THIS run (tools/int_peak.cu, dependent-free asm streams, < 1 s)
@@ -437,8 +446,8 @@ def main():
         mix = json.load(open(mix_file)) if os.path.exists(mix_file) else {}
         alu_issue = measured.get("VIADDMNMX.S16x2_Tlaneops")
         alu_pipe_frac = None
-        if mix.get("alu_lane_ops_per_cell") and alu_issue:
-            alu_pipe_frac = fwd_cups * mix["alu_lane_ops_per_cell"] / (alu_issue * 1e12)
+        if mix.get("alu_lane_ops_per_visited_cell") and alu_issue:
+            alu_pipe_frac = fwd_cups * mix["alu_lane_ops_per_visited_cell"] / (alu_issue * 1e12)
         line = {
             "metric": "alignments/sec", "value": value, "unit": "alignments/s", "n_gpus": world, "steps": args.steps,
             "warmup": warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -472,15 +481,22 @@ def main():
                 "frac": achieved_laneops / peak_laneops,
                 "traffic": mix.get("dram_bytes_per_pair", 0) * n if mix.get("dram_bytes_per_pair") else None,
                 "traffic_source": ("%s (dram__bytes_read+write per pair x pairs per launch) - from that committed ncu capture, NOT measured by this run; algorithmic q+w = 4300 B/pair" % mix.get("source")) if mix else None,
-                "gcups_kernel": fwd_cups / 1e9, "int_ops_per_cell": INT_OPS_PER_CELL, "packing": 2,
+                "gcups_kernel": fwd_cups / 1e9, "gcups_effective": eff_cups / 1e9, "int_ops_per_cell": INT_OPS_PER_CELL, "packing": 2,
+                "cells_algorithmic_per_step": cells_per_step, "cells_visited_per_step": visited_cells / args.steps,
+                "visited_frac": visited_cells / args.steps / cells_per_step,
+                "filter": {"pairs_banded_last_step": flt_banded, "certificates_failed_last_step": flt_failed,
+                           "what": "lossless k-mer filter + certificate in front of the forward pass (csrc/band_filter.cuh): banded pairs sweep only the columns a proven "
+                                   "diagonal band can reach; a failed certificate sends the pair through the full window; results are bit-identical either way "
+                                   "(tests/test_gpu_parity.py::test_filter_*, CUDASW_FILTER=0 switches it off)"},
                 "peak_source": f"{sms} SMs x 128 lanes x {f_sm / 1e6:.0f} MHz (nominal INT32 lane rate at the median SM clock sampled during the run); "
                                "measured on this box in this run by tools/int_peak (dependent-free asm streams): see measured_issue_rates_Tlaneops",
                 "measured_issue_rates_Tlaneops": {k.replace("_Tlaneops", ""): v for k, v in measured.items() if k.endswith("_Tlaneops")} or measured,
                 "alu_pipe_frac": alu_pipe_frac,
-                "alu_pipe_frac_how": "ALU-pipe lane-ops the kernel EXECUTES per cell (%s, from %s) x cells/s of this run / the measured VIADDMNMX.S16x2 issue rate; "
-                                     "this is the fraction of the pipe the kernel actually lives on" % (mix.get("alu_lane_ops_per_cell"), mix.get("source")),
-                "note": "frac counts the ALGORITHMIC 12 integer ops per cell of SURVEY.md 8d against the nominal INT32 rate and can exceed 1: one VIADDMNMX does three of "
-                        "those ops, and quiet steps (no gap can be open) skip the E/F updates exactly. alu_pipe_frac is the bounded yardstick.",
+                "alu_pipe_frac_how": "ALU-pipe lane-ops the kernel EXECUTES per visited cell (%s, from %s) x visited cells/s of this run / the measured VIADDMNMX.S16x2 issue rate; "
+                                     "this is the fraction of the pipe the kernel actually lives on" % (mix.get("alu_lane_ops_per_visited_cell"), mix.get("source")),
+                "note": "achieved = SURVEY.md 8d's 12 integer ops per cell x the cells the forward kernels VISITED per second / 2 (s16x2), against the nominal INT32 rate. "
+                        "It can still exceed what the pipe can issue for this mix (one VIADDMNMX does three of those ops, quiet steps skip the E/F updates exactly): "
+                        "alu_pipe_frac is the bounded yardstick. gcups_effective counts every q x w cell, visited or proven irrelevant.",
                 "measured_cellmix_ceiling_TCUPS": measured.get("cellmix_TCUPS"),
                 "frac_of_measured_cellmix_ceiling": (fwd_cups / 1e12 / measured["cellmix_TCUPS"]) if measured.get("cellmix_TCUPS") else None,
             },

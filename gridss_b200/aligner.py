@@ -76,6 +76,8 @@ class Stats(ctypes.Structure):
         ("forward_cells_padded", ctypes.c_uint64),
         ("ms_encode", ctypes.c_float),
         ("encode_bytes", ctypes.c_uint64),
+        ("filter_banded", ctypes.c_uint64),
+        ("filter_failed", ctypes.c_uint64),
     ]
 
     def as_dict(self):

@@ -161,6 +161,8 @@ struct cudasw {
     // sub-window result is proven, and the second (full-window) pass's own bins
     FilterConst fc{};
     bool use_filter = false;
+    bool filter_always = false;         // CUDASW_FILTER=2: also for chunks of less than two waves of forward CTAs (tests)
+    std::vector<char> chunk_filter;     // per chunk: the filter runs (scan_batch)
     DevBuf<FilterRec> frec;
     DevBuf<uint32_t> fhc;  // per pair: hits of the core bins extended by j bins either side, j < kFltHc
     DevBuf<uint8_t> fdone;
@@ -347,13 +349,14 @@ extern "C" int cudasw_create_ex(const cudasw_scoring* s, int device, int tie_bre
     {
         const char* fe = getenv("CUDASW_FILTER");  // 0: every pair sweeps its whole window (the pre-filter pipeline)
         h->use_filter = h->fc.ok && !(fe && atoi(fe) == 0);
+        h->filter_always = fe && atoi(fe) == 2;
         if ((e = cudaFuncSetAttribute(filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kFltWarps * kFltSmemPerWarp))) != cudaSuccess)
             return fail(cudaGetErrorString(e));
     }
     if ((e = cudaMalloc(&h->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
     if ((e = cudaMallocHost(&h->h_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
-    if ((e = cudaMallocHost(&h->h_cells, 2 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMallocHost(&h->h_cells, 8 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMallocHost(&h->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess)
         return fail(cudaGetErrorString(e));
 
@@ -579,19 +582,22 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     const int max_cols = (1 << 24) - 2;
     size_t cub_bytes = cub_tmp.cap;
     CK(cudaMemsetAsync(d_hist, 0, 256 * sizeof(int), st));
-    if (use_filter) {
+    const bool flt = use_filter && chunk_filter[ci];
+    if (use_filter && !flt)  // every record names the whole window (the reverse pass reads the records of the whole batch)
+        CK(cudaMemsetAsync(frec.p + first, 0xFF, (size_t)n * sizeof(FilterRec), st));
+    if (flt) {
         // per pair: hits per diagonal bin -> the column range the forward pass sweeps first (band_filter.cuh)
         filter_kernel<<<(int)std::min<int64_t>((n + kFltWarps - 1) / kFltWarps, 148 * 2 * 8), 32 * kFltWarps, kFltWarps * kFltSmemPerWarp, st>>>(
             (int)n, io, any_n, wflags.p + first, fc, frec.p + first, fhc.p + (size_t)first * kFltHc, d_fcount);
         launches++;
     }
     seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
-        (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first, use_filter ? frec.p + first : nullptr);
+        (int)n, enc_seq.p, enc_ref.p, io.seq_off, io.ref_off, anchor.p + first, flt ? frec.p + first : nullptr);
     launches++;
     fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
                                                            keys.p + first, vals.p + first, d_hist, res.p + first, any_n,
                                                            wflags.p + first, anchor.p + first, d_strip + 2,
-                                                           use_filter ? frec.p + first : nullptr, nullptr);
+                                                           flt ? frec.p + first : nullptr, nullptr);
     launches++;
     CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p + first, keys_alt.p + first, vals.p + first,
                                        vals_alt.p + first, (int)n, 0, 32, st));
@@ -616,10 +622,11 @@ int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* 
     CK(cudaEventRecord(chunk_ev[ci].fwd0, st));
     CK(cudaMemsetAsync(d_strip, 0, sizeof(unsigned long long), st));
     StripPool spool{strip_fwd.p, (unsigned long long)strip_fwd.cap, d_strip};
-    if (use_filter) io.sub = frec.p + first;
+    const bool flt = use_filter && chunk_filter[ci];
+    if (flt) io.sub = frec.p + first;
     { int rc = launch_variants(fwd_set, false, vals_alt.p + first, io, nullptr, fwd.p + first, spool, &launches, fwd_counts[ci].data(),
                                fwd_slots.p + ci * (size_t)(2 * (2 * g_nvar + 1)), batch_maybe_n); if (rc != CUDASW_OK) return rc; }
-    if (use_filter) {
+    if (flt) {
         // Which sub-window results are proven (band_filter.cuh)? The others sweep their whole window now: binned again
         // (everything proven lands in the "nothing to do" slot) and launched over the same host-side upper bounds.
         const int64_t n = cnt;
@@ -1011,7 +1018,8 @@ void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, 
     const int64_t single_rows = vt.n_single > 0 ? vt.rows[vt.n_single - 1] : 0;
     fwd_counts.assign(ranges.size(), std::vector<int>((size_t)g_nvar, 0));
     strip_need.assign(ranges.size(), 0ull);
-    struct Part { std::vector<int> counts; unsigned long long need = 0; int64_t mq = 0, mw = 0; };
+    struct Part { std::vector<int> counts; unsigned long long need = 0; int64_t mq = 0, mw = 0; double cells = 0.0; };
+    std::vector<double> chunk_cells(ranges.size(), 0.0);
     int64_t mq = 0, mw = 0;
     for (size_t ci = 0; ci < ranges.size(); ci++) {
         const int64_t first = ranges[ci].first, cnt = ranges[ci].second;
@@ -1027,6 +1035,7 @@ void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, 
                 p.mw = std::max(p.mw, w);
                 if (q > 0 && w > 0 && q <= max_rows && w <= max_cols) {
                     p.counts[(size_t)var_by_q[(size_t)q]]++;
+                    p.cells += (double)q * (double)w;
                     if (q > single_rows) p.need += ((((unsigned long long)w * 4ull + 15ull) & ~15ull) * 2ull);
                 }
             }
@@ -1041,10 +1050,17 @@ void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, 
         for (auto& p : parts) {
             for (int v = 0; v < g_nvar; v++) fwd_counts[ci][(size_t)v] += p.counts[(size_t)v];
             strip_need[ci] += p.need;
+            chunk_cells[ci] += p.cells;
             mq = std::max(mq, p.mq);
             mw = std::max(mw, p.mw);
         }
     }
+    // The filter pays once the forward pass is throughput-bound: a small chunk runs as long as its longest CTA, and a
+    // sub-window pass followed by a full-window pass for the few unproven pairs is then longer than the full-window pass
+    // alone (C1 10 k pairs = 3 G cells: 1.26 against 0.76 ms; C2 5 k pairs = 6 G cells: 2.13 against 1.37 ms; C3 10 k
+    // pairs = 21 G cells: 15.4 against 33.4 ms).
+    chunk_filter.assign(ranges.size(), 0);
+    for (size_t ci = 0; ci < ranges.size(); ci++) chunk_filter[ci] = use_filter && (filter_always || chunk_cells[ci] >= 12e9);
     batch_max_q = std::min<int64_t>(std::max<int64_t>(mq, 1), 32767);
     batch_max_w = std::min<int64_t>(std::max<int64_t>(mw, 1), (1 << 24));
 }
@@ -1181,6 +1197,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     CK(cudaEventRecord(ev[0], st));
     CK(cudaMemsetAsync(d_counters, 0, 8 * sizeof(unsigned long long), st));
     CK(cudaMemsetAsync(d_strip + 2, 0, 2 * sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(d_fcount, 0, 4 * sizeof(unsigned long long), st));
     CK(cudaEventRecord(ev[1], st));
     CK(cudaStreamWaitEvent(pack_stream, ev[1], 0));  // the counters (any-N flag) are reset before the first encode
     // ---- H2D: everything is queued on the copy stream now, one event per chunk
@@ -1318,16 +1335,15 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
     unsigned long long ncopy = std::min<unsigned long long>(used, (unsigned long long)cigar_cap);
     if (ncopy) CK(cudaMemcpyAsync(cigar_blob, cig.p, (size_t)ncopy * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(h_cells, d_strip + 2, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_cells + 4, d_fcount, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(ev[6], st));
     CK(cudaStreamSynchronize(st));
     stats.d2h_bytes = (uint64_t)n * sizeof(cudasw_result) + ncopy * 4;
-    if (use_filter && getenv("CUDASW_FILTER_STATS")) {  // experiment hook
-        unsigned long long fcnt[4];
-        CK(cudaMemcpy(fcnt, d_fcount, sizeof fcnt, cudaMemcpyDeviceToHost));
-        CK(cudaMemset(d_fcount, 0, sizeof fcnt));
+    stats.filter_banded = use_filter ? h_cells[4] : 0;
+    stats.filter_failed = use_filter ? h_cells[6] : 0;
+    if (use_filter && getenv("CUDASW_FILTER_STATS"))  // experiment hook
         fprintf(stderr, "[cudasw filter] pairs %lld: banded %llu, passed on %llu (ineligible pairs not counted), certificates failed %llu\n",
-                (long long)n, fcnt[0], fcnt[1], fcnt[2]);
-    }
+                (long long)n, h_cells[4], h_cells[5], h_cells[6]);
 
     stats.pairs = (uint64_t)n;
     stats.kernel_launches = launches;

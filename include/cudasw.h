@@ -72,6 +72,8 @@ typedef struct cudasw_stats {
     uint64_t forward_cells_padded; /* cells actually computed by the forward kernels */
     float ms_encode;               /* part of ms_pack: the HBM-bound encode (or window gather) kernels alone */
     uint64_t encode_bytes;         /* bytes those kernels read + wrote */
+    uint64_t filter_banded;        /* pairs whose forward pass first swept a k-mer-filtered column range (band_filter.cuh) */
+    uint64_t filter_failed;        /* ... of which the certificate failed: swept their whole window in a second pass */
 } cudasw_stats;
 
 /* Create an engine on CUDA device `device`. Replaces the AlignerFactory static initialiser's
