@@ -66,7 +66,17 @@ def full_capture(rep, name, title, cmd, notes=""):
     if notes:
         out += ["", notes]
     open(os.path.join(P, name), "w").write("\n".join(out) + "\n")
+    UNITS.clear()
+    UNITS.update({k: u[h.index(k)] for k in h if k in KEYS})
     return {k: v[h.index(k)] for k in h if k in KEYS}
+
+
+UNITS = {}  # units of the last full_capture()
+
+
+def mbytes(m, k):
+    x = float(str(m[k]).replace(",", ""))
+    return x * {"byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}.get(UNITS.get(k, "Mbyte"), 1.0)
 
 
 def alu_mix(tag, m, cmd_pairs=50000, q=300, w=4000):
@@ -94,6 +104,52 @@ if __name__ == "__main__" and len(sys.argv) > 4 and sys.argv[1] == "one":
     # python tools/profile_summaries.py one <rep in gpurun_out> <md under profiles> <title> [command]
     m = full_capture(sys.argv[2], sys.argv[3], sys.argv[4], sys.argv[5] if len(sys.argv) > 5 else "")
     print({k: m[k] for k in list(m)[:10]})
+    sys.exit(0)
+
+def alu_mix_visited(tag, m, plain_log, q=300, w=4000, rows_padded=304, lanes=8):
+    """profiles/fwd_alu_mix.json for the k-mer-filtered pipeline: ALU-pipe lane-ops per VISITED cell of the forward kernel's
+    sub-window pass. The visited cells of the captured launch = what the bench line of the same command reports per step,
+    minus the second (full-window) pass of the pairs whose certificate failed."""
+    import json
+
+    def f(k):
+        return float(str(m[k]).replace(",", ""))
+
+    line = json.loads(open(plain_log).read().strip().splitlines()[-1])
+    rf = line["roofline"]
+    pairs = line["config"]["pairs_per_gpu_per_step"]
+    failed = rf["filter"]["certificates_failed_last_step"]
+    visited = rf["cells_visited_per_step"] - failed * rows_padded * (w + 2 * lanes - 1)
+    cyc, alu = f("sm__cycles_elapsed.avg"), f("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active") / 100.0
+    smsps = 148 * 4
+    warp_inst = alu * cyc * smsps * 0.5  # the ALU pipe takes one warp instruction every other clock (16 lanes)
+    rd, wr = mbytes(m, "dram__bytes_read.sum"), mbytes(m, "dram__bytes_write.sum")
+    out = {"alu_lane_ops_per_visited_cell": round(warp_inst * 32 / visited, 3), "visited_cells_of_the_launch": visited,
+           "dram_bytes_per_pair": round((rd + wr) * 1e6 / pairs, 1), "source": f"profiles/ncu_fwd_{tag}.md",
+           "how": f"sm__inst_executed_pipe_alu {alu * 100:.3f} % x sm__cycles_elapsed {cyc:.0f} x {smsps} SMSPs x 0.5 warp-inst/clk (16-lane ALU pipe) x 32 lanes / "
+                  f"{visited:.4g} visited cells (bench line of the same command: cells_visited_per_step {rf['cells_visited_per_step']:.4g} minus {failed} unproven pairs x "
+                  f"{rows_padded} x {w + 2 * lanes - 1} of the second pass); dram__bytes_read+write {rd + wr:.2f} MB / {pairs} pairs"}
+    json.dump(out, open(os.path.join(P, "fwd_alu_mix.json"), "w"), indent=1)
+    print("fwd_alu_mix", out)
+
+
+if __name__ == "__main__" and len(sys.argv) > 2 and sys.argv[2] == "r02f":
+    # round 2, k-mer-filtered pipeline (tools/gpu_session5.sh)
+    tag = sys.argv[1]
+    cmd = "python bench.py --steps 2 --warmup 3 --pairs 50000 --no-cpu-baseline --no-windows --no-homology --no-worst-case --no-int-peak"
+    launch_list(tag, cmd)
+    caps = [("fwd", "forward score kernel, sub-window pass of the k-mer-filtered pipeline (C2, chained query-profile flavour)", "sw_score_kernelILi8ELi19ELb0ELb0ELb1ELb1E -s 6", cmd),
+            ("filter", "k-mer filter kernel (hits per diagonal bin, column range, certificate data; C2)", "filter_kernel -s 3", cmd),
+            ("rev", "banded reverse pass with the certified gap bound (C2)", "sw_rev_band_kernelILi1ELi16ELb1E -s 3", cmd)]
+    for name, title, kre, c in caps:
+        rep = f"prof_{name}_{tag}.ncu-rep"
+        if os.path.exists(os.path.join(O, rep)):
+            m = full_capture(rep, f"ncu_{name}_{tag}.md", title, f"ncu --set full --clock-control none --import-source on --kernel-name-base mangled -k regex:{kre} -c 1 {c}")
+            print(name, {k: m[k] for k in list(m)[:8]})
+            if name == "fwd":
+                alu_mix_visited(tag, m, os.path.join(O, f"plain_{tag}.log"))
+    import shutil
+    shutil.copy(os.path.join(O, f"plain_{tag}.log"), os.path.join(P, f"bench_{tag}_50k_profiled_command.json"))
     sys.exit(0)
 
 if __name__ == "__main__" and len(sys.argv) > 2 and sys.argv[2] == "r02":
