@@ -804,7 +804,7 @@ def test_filter_repeats_decoys_and_ties_vs_oracle(aligner, oracle, monkeypatch):
     rng = np.random.default_rng(20260)
     seqs, refs = _repeat_cases(rng, 1800)
     monkeypatch.setenv("CUDASW_FILTER", "2")
-    forced = gb.AlignerFactory.create()
+    forced = gb.CudaAligner(1, -4, -4, 6, 1)  # (AlignerFactory.create() without arguments is the shared default instance)
     bad, undef = _compare(forced, oracle, seqs, refs)
     forced.close()
     assert bad == [], bad[:3]
