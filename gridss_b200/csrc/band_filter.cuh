@@ -44,7 +44,18 @@ constexpr int kFltBinShift = 5;               // 32 diagonals per bin
 constexpr int kFltMaxBins = 1024;             // q + w - 1 <= 32 * 1024 diagonals
 constexpr int kFltMaxQ = 2040;                // chain links are 16 bit; a bin then holds at most 32 * 2040 hits
 constexpr int kFltWarps = 4;                  // pairs per CTA of filter_kernel
-constexpr size_t kFltSmemPerWarp = kFltHeads * 2 + 2048 * 2 + kFltMaxBins * 2;  // heads, links, bins: 16 bit each (14 KB)
+constexpr size_t kFltSmemPerWarp = kFltHeads * 2 + 2048 * 2 + kFltMaxBins * 2;  // heads, links, bins: 16 bit each (14 KB at most)
+// The launch sizes the links and bins for the batch's longest query / most diagonals (the host knows both), so that short
+// pairs leave room for more warps per SM: C2 (300 x 4000) needs 9.5 KB per warp instead of 14.
+struct FilterSmem { int link_cap, bins_cap; };  // entries; both multiples of 64
+__host__ __device__ __forceinline__ size_t flt_smem_per_warp(FilterSmem m) { return (size_t)kFltHeads * 2 + (size_t)m.link_cap * 2 + (size_t)m.bins_cap * 2; }
+inline FilterSmem make_filter_smem(long long max_q, long long max_w) {
+    long long lc = std::min<long long>(std::max<long long>(max_q, 64), 2048), bc = std::min<long long>((max_q + max_w) / 32 + 4, kFltMaxBins);
+    FilterSmem m;
+    m.link_cap = (int)((lc + 63) & ~63ll);
+    m.bins_cap = (int)std::min<long long>((bc + 63) & ~63ll, kFltMaxBins);
+    return m;
+}
 
 struct FilterConst {
     int ok;              // 0: this scoring gives no usable bound (match <= 0, free mismatches or free gaps)
@@ -110,19 +121,19 @@ __host__ __device__ __forceinline__ int flt_tight_bins(const FilterConst& f, lon
 // the same k-mer), bins[diagonal / 32]; all 16 bit.
 __global__ void __launch_bounds__(32 * kFltWarps)
 filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __restrict__ wflags, FilterConst fc,
-              FilterRec* __restrict__ rec, uint32_t* __restrict__ hc_out, unsigned long long* __restrict__ counters) {
+              FilterRec* __restrict__ rec, uint32_t* __restrict__ hc_out, unsigned long long* __restrict__ counters, FilterSmem sm) {
     extern __shared__ __align__(16) unsigned char flt_smem[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    unsigned short* heads = reinterpret_cast<unsigned short*>(flt_smem + (size_t)wib * kFltSmemPerWarp);
+    unsigned short* heads = reinterpret_cast<unsigned short*>(flt_smem + (size_t)wib * flt_smem_per_warp(sm));
     unsigned short* link = heads + kFltHeads;
-    uint32_t* bins2 = reinterpret_cast<uint32_t*>(link + 2048);  // two 16-bit counters per word (a bin holds <= 32 * kFltMaxQ hits)
+    uint32_t* bins2 = reinterpret_cast<uint32_t*>(link + sm.link_cap);  // two 16-bit counters per word (a bin holds <= 32 * kFltMaxQ hits)
     uint32_t* psum = reinterpret_cast<uint32_t*>(heads);         // prefix sums of the bins: overlays the heads once the scan is over
     for (int p = blockIdx.x * kFltWarps + wib; p < n; p += gridDim.x * kFltWarps) {
         const int64_t qo = io.seq_off[p], ro = io.ref_off[p];
         const int q = (int)(io.seq_off[p + 1] - qo), w = (int)(io.ref_off[p + 1] - ro);
         FilterRec r{0, w, 0, 0, -1};
         const bool eligible = fc.ok && q >= kFltK && w >= kFltK && q <= kFltMaxQ && (long long)q + w <= 32ll * kFltMaxBins - 64 &&
-                              !(*any_n != 0 && wflags[p]);
+                              q <= sm.link_cap && ((q + w - 2) >> kFltBinShift) + 3 <= sm.bins_cap && !(*any_n != 0 && wflags[p]);
         if (!eligible) {  // warp-uniform
             if (lane == 0) rec[p] = r;
             continue;

@@ -587,8 +587,9 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
         CK(cudaMemsetAsync(frec.p + first, 0xFF, (size_t)n * sizeof(FilterRec), st));
     if (flt) {
         // per pair: hits per diagonal bin -> the column range the forward pass sweeps first (band_filter.cuh)
-        filter_kernel<<<(int)std::min<int64_t>((n + kFltWarps - 1) / kFltWarps, 148 * 2 * 8), 32 * kFltWarps, kFltWarps * kFltSmemPerWarp, st>>>(
-            (int)n, io, any_n, wflags.p + first, fc, frec.p + first, fhc.p + (size_t)first * kFltHc, d_fcount);
+        const FilterSmem fsm = make_filter_smem(std::min<int64_t>(batch_max_q, kFltMaxQ), std::min<int64_t>(batch_max_w, 32ll * kFltMaxBins));
+        filter_kernel<<<(int)std::min<int64_t>((n + kFltWarps - 1) / kFltWarps, 148 * 2 * 8), 32 * kFltWarps, kFltWarps * flt_smem_per_warp(fsm), st>>>(
+            (int)n, io, any_n, wflags.p + first, fc, frec.p + first, fhc.p + (size_t)first * kFltHc, d_fcount, fsm);
         launches++;
     }
     seed_anchor_kernel<<<(int)std::min<int64_t>((n + kSeedWarps - 1) / kSeedWarps, 148 * 5 * 4), 32 * kSeedWarps, 0, st>>>(
@@ -1018,8 +1019,8 @@ void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, 
     const int64_t single_rows = vt.n_single > 0 ? vt.rows[vt.n_single - 1] : 0;
     fwd_counts.assign(ranges.size(), std::vector<int>((size_t)g_nvar, 0));
     strip_need.assign(ranges.size(), 0ull);
-    struct Part { std::vector<int> counts; unsigned long long need = 0; int64_t mq = 0, mw = 0; double cells = 0.0; };
-    std::vector<double> chunk_cells(ranges.size(), 0.0);
+    struct Part { std::vector<int> counts; unsigned long long need = 0; int64_t mq = 0, mw = 0; double cells = 0.0, sq = 0.0, sw = 0.0; };
+    std::vector<double> chunk_cells(ranges.size(), 0.0), chunk_q(ranges.size(), 0.0), chunk_w(ranges.size(), 0.0);
     int64_t mq = 0, mw = 0;
     for (size_t ci = 0; ci < ranges.size(); ci++) {
         const int64_t first = ranges[ci].first, cnt = ranges[ci].second;
@@ -1036,6 +1037,8 @@ void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, 
                 if (q > 0 && w > 0 && q <= max_rows && w <= max_cols) {
                     p.counts[(size_t)var_by_q[(size_t)q]]++;
                     p.cells += (double)q * (double)w;
+                    p.sq += (double)q;
+                    p.sw += (double)w;
                     if (q > single_rows) p.need += ((((unsigned long long)w * 4ull + 15ull) & ~15ull) * 2ull);
                 }
             }
@@ -1051,6 +1054,8 @@ void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, 
             for (int v = 0; v < g_nvar; v++) fwd_counts[ci][(size_t)v] += p.counts[(size_t)v];
             strip_need[ci] += p.need;
             chunk_cells[ci] += p.cells;
+            chunk_q[ci] += p.sq;
+            chunk_w[ci] += p.sw;
             mq = std::max(mq, p.mq);
             mw = std::max(mw, p.mw);
         }
@@ -1060,7 +1065,10 @@ void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, 
     // alone (C1 10 k pairs = 3 G cells: 1.26 against 0.76 ms; C2 5 k pairs = 6 G cells: 2.13 against 1.37 ms; C3 10 k
     // pairs = 21 G cells: 15.4 against 33.4 ms).
     chunk_filter.assign(ranges.size(), 0);
-    for (size_t ci = 0; ci < ranges.size(); ci++) chunk_filter[ci] = use_filter && (filter_always || chunk_cells[ci] >= 12e9);
+    // Nor does it pay when the windows are hardly longer than the queries (BreakpointHomology's 600 x 620: the column range
+    // a band can reach is the whole window, every pair would be passed on after the filter kernel had looked at it).
+    for (size_t ci = 0; ci < ranges.size(); ci++)
+        chunk_filter[ci] = use_filter && (filter_always || (chunk_cells[ci] >= 12e9 && chunk_w[ci] >= 1.5 * chunk_q[ci]));
     batch_max_q = std::min<int64_t>(std::max<int64_t>(mq, 1), 32767);
     batch_max_w = std::min<int64_t>(std::max<int64_t>(mw, 1), (1 << 24));
 }
