@@ -240,7 +240,7 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
         const long long nmin = min(q, w);
         const long long s_est = min((long long)fc.a * bh * fc.est_pct / 100, 32767ll);
         const long long L = s_est > 0 ? max_gap_bases(nmin, fc.a, (int)s_est, fc.go, fc.ge) : -1;
-        bool go_on = L >= 0;
+        bool go_on = L >= 0, evidence_only = false;
         int m_old = 0, m_band = 0;
         long long c0 = 0, c1 = w - 1;
         uint32_t noise = 0u;
@@ -284,10 +284,15 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
             c1 = min((long long)w - 1, Dhi);
             // nothing to win when the range is most of the window; not worth trying when even the estimated score could not
             // be told from the noise
-            go_on = m_old <= 255 && (c1 - c0 + 1) * 10 <= 7ll * w && flt_hits_floor(fc, (long long)fc.a * bh, nmin) > (long long)noise;
+            const bool told_apart = m_old <= 255 && flt_hits_floor(fc, (long long)fc.a * bh, nmin) > (long long)noise;
+            go_on = told_apart && (c1 - c0 + 1) * 10 <= 7ll * w;
+            // A pair that sweeps its whole window anyway (long query in a short window) can still have the gap bases of its
+            // alignments bounded by the hits, which is what the reverse pass's band is made of: keep the certificate data.
+            evidence_only = told_apart && !go_on;
         }
         if (lane == 0) {
             if (go_on) { r.c0 = (int32_t)c0; r.wlen = (int32_t)(c1 - c0 + 1); r.margin_bins = m_band | (m_old << 8); r.noise = (int32_t)noise; }
+            else if (evidence_only) { r.margin_bins = kFltWholeWindow | m_band | (m_old << 8); r.noise = (int32_t)noise; }
             rec[p] = r;
             if (counters) atomicAdd(counters + (go_on ? 0 : 1), 1ull);
         }
@@ -304,8 +309,9 @@ __global__ void filter_certify_kernel(int n, const int64_t* __restrict__ seq_off
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     FilterRec r = rec[p];
-    if (r.margin_bins == 0) { done[p] = 1; return; }  // the first pass already swept the whole window
-    const int m_band = r.margin_bins & 0xFF, m_old = r.margin_bins >> 8;
+    if (r.margin_bins == 0) { done[p] = 1; return; }  // the first pass already swept the whole window, nothing to prove
+    const bool whole = (r.margin_bins & kFltWholeWindow) != 0;  // swept the whole window; only the gap bound is sought
+    const int m_band = whole ? 1 << 20 : r.margin_bins & 0xFF, m_old = (r.margin_bins >> 8) & 0xFF;
     const long long q = seq_off[p + 1] - seq_off[p], w = ref_off[p + 1] - ref_off[p];
     const long long nmin = q < w ? q : w;
     const int4 f = fwd[p];
@@ -320,10 +326,12 @@ __global__ void filter_certify_kernel(int n, const int64_t* __restrict__ seq_off
             ok = flt_tight_bins(fc, f.x, nmin, flt_bins_of(L), L, [&](int j) { return hc[j]; }, &gb) <= m_band;
         }
     }
-    done[p] = ok ? 1 : 0;
+    done[p] = (ok || whole) ? 1 : 0;
     if (ok) {
         r.gap_bound = (int32_t)gb;
         rec[p] = r;
+    } else if (whole) {
+        // (the forward result is the full sweep's; the record stays as it is, without a gap bound)
     } else {
         r.c0 = 0; r.wlen = (int32_t)w; r.margin_bins = 0; r.noise = 0; r.gap_bound = -1;
         rec[p] = r;

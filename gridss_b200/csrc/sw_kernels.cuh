@@ -296,10 +296,12 @@ struct ScoreConst {
 // sweeps the whole window.
 struct FilterRec {
     int32_t c0, wlen;     // the forward pass sweeps window columns [c0, c0 + wlen)
-    int32_t margin_bins;  // bins of margin either side of the core: m_band | (m_old << 8)
+    int32_t margin_bins;  // bins of margin either side of the core: m_band | (m_old << 8) [| kFltWholeWindow]
     int32_t noise;        // most hits in any run of m_old bins outside the band's core
     int32_t gap_bound;    // once certified: no alignment of the pair's score has more gap bases than this (-1: not known)
 };
+
+constexpr int32_t kFltWholeWindow = 1 << 30;  // FilterRec::margin_bins: the range is the whole window, the certificate only yields gap_bound
 
 struct PairIO {
     const uint8_t* enc_seq;
@@ -373,7 +375,7 @@ seed_anchor_kernel(int n, const uint8_t* __restrict__ enc_seq, const uint8_t* __
         const int64_t qo = seq_off[p], ro = ref_off[p];
         const int q = (int)(seq_off[p + 1] - qo), w = (int)(ref_off[p + 1] - ro);
         int col = 0;
-        if (sub && sub[p].margin_bins != 0) {
+        if (sub && sub[p].margin_bins != 0 && !(sub[p].margin_bins & kFltWholeWindow)) {
             if (lane == 0) anchor[p] = 0;
             continue;
         }
@@ -441,7 +443,7 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
         q = seq_off[p + 1] - seq_off[p];
         w = ref_off[p + 1] - ref_off[p];
         ws = w;
-        if (sub) { const FilterRec fr = sub[p]; ws = fr.wlen; banded = fr.margin_bins != 0; }
+        if (sub) { const FilterRec fr = sub[p]; ws = fr.wlen; banded = fr.margin_bins != 0 && !(fr.margin_bins & kFltWholeWindow); }
         if (q > 0 && w > 0 && !skip) {
             if (!done) my_cells = (unsigned long long)q * (unsigned long long)w;
             if (q <= max_rows) {
