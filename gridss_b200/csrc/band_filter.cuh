@@ -157,7 +157,12 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
             const uint4* al = reinterpret_cast<const uint4*>(sq - mis);
             const int total = len + mis;  // bytes of the aligned stream that are ours (the first `mis` are not)
             const int ntiles = (total + 511) >> 9;
-            auto load = [&](int vi) { return 16 * vi < total ? al[vi] : make_uint4(0u, 0u, 0u, 0u); };
+            auto load = [&](int vi) {
+                if (16 * vi >= total) return make_uint4(0u, 0u, 0u, 0u);
+                // (a vector may start up to 15 bytes before the sequence and end up to 15 bytes after it: inside the blob, or its 16 bytes of slack)
+                CUSW_CHECK_PTR(reinterpret_cast<const uint8_t*>(al + vi) + 15, sq - 15, sq + len + 16, "filter: sequence vector");
+                return al[vi];
+            };
             auto c8 = [](uint32_t x) { return ((x & 0x03030303u) * 0x01041040u) >> 24; };  // four bytes -> four 2-bit codes
             uint4 nxt = load(lane), nxt2 = load(32 + lane);  // two steps in flight: the kernel lives on HBM latency
             uint32_t carry_c = 0u, carry_n = 0u;
@@ -190,7 +195,11 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
                     __syncwarp();
                     if (pending) heads[km] = (unsigned short)(i + 1);
                     __syncwarp();
-                    if (pending && heads[km] == (unsigned short)(i + 1)) { link[i] = old; pending = false; }
+                    if (pending && heads[km] == (unsigned short)(i + 1)) {
+                        CUSW_CHECK_PTR(link + i, link, link + sm.link_cap, "filter: chain link");
+                        link[i] = old;
+                        pending = false;
+                    }
                     __syncwarp();
                 }
             }
@@ -217,6 +226,8 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
                 while (i1p != 0u) {
                     const int i = (int)i1p - 1;
                     const int b = (j - i + q - 1) >> kFltBinShift;
+                    CUSW_CHECK_PTR(bins2 + (b >> 1), bins2, bins2 + sm.bins_cap / 2, "filter: diagonal bin");
+                    CUSW_CHECK_PTR(link + i, link, link + sm.link_cap, "filter: chain link (walk)");
                     atomicAdd(&bins2[b >> 1], 1u << (16 * (b & 1)));
                     i1p = link[i];
                 }
