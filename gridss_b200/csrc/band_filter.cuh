@@ -64,7 +64,29 @@ struct FilterConst {
     int est_pct;         // the margin is sized for a score of est_pct % of (a * hits of the densest bin pair)
     int ev_div;          // min(go - a(k-1), ge) when both are positive, else 0: no evidence bound for this scoring
     int ev_alpha, ev_pa; // max(0, a(k-1) - p); p + a
+    int band;            // 1: certifiable pairs take the banded forward kernel (a parallelogram of diagonals); 0: the column
+                         // range [c0, c1] through the wavefront kernels (a rectangle)
 };
+constexpr int kFltBandMaxBins = 15;  // widest margin the banded forward kernel takes: 32 (2 * 15 + 2) = 1024 diagonals
+// Cells the banded forward kernel computes for a pair: its strips of S rows each sweep S + Wd - 1 columns.
+constexpr int kBandVariants = 5;  // strips of 32, 64, 128, 256, 1024 rows (rev_band.cuh)
+__host__ __device__ __forceinline__ int band_variant_rows(int v) { return v == 0 ? 32 : v == 1 ? 64 : v == 2 ? 128 : v == 3 ? 256 : 1024; }
+__host__ __device__ __forceinline__ long long band_cells(int q, int w, long long wd, int v) {
+    const long long S = band_variant_rows(v);
+    const long long cols = S + wd - 1 < w ? S + wd - 1 : w;
+    return ((q + S - 1) / S) * S * cols;
+}
+__host__ __device__ __forceinline__ int band_best_variant(int q, int w, long long wd, int few_pairs) {
+    if (few_pairs && q > 256) return 4;  // a whole warp per pair when there are few of them (latency)
+    int best = 0;
+    long long bc = band_cells(q, w, wd, 0);
+    for (int v = 1; v < 4; v++) {
+        // a taller strip wastes triangle cells but crosses the ring less often: take it when it costs at most 10 % more
+        const long long c = band_cells(q, w, wd, v);
+        if (c * 10 <= bc * 11) { best = v; if (c < bc) bc = c; }
+    }
+    return best;
+}
 constexpr int kFltHc = 16;  // hc(j), j < kFltHc, is kept per pair for the certificate
 
 inline FilterConst make_filter_const(int match, int mismatch, int ambiguous, int go, int ge) {
@@ -131,7 +153,7 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
     for (int p = blockIdx.x * kFltWarps + wib; p < n; p += gridDim.x * kFltWarps) {
         const int64_t qo = io.seq_off[p], ro = io.ref_off[p];
         const int q = (int)(io.seq_off[p + 1] - qo), w = (int)(io.ref_off[p + 1] - ro);
-        FilterRec r{0, w, 0, 0, -1};
+        FilterRec r{0, w, 0, 0, -1, 0, 0};
         const bool eligible = fc.ok && q >= kFltK && w >= kFltK && q <= kFltMaxQ && (long long)q + w <= 32ll * kFltMaxBins - 64 &&
                               q <= sm.link_cap && ((q + w - 2) >> kFltBinShift) + 3 <= sm.bins_cap && !(*any_n != 0 && wflags[p]);
         if (!eligible) {  // warp-uniform
@@ -251,7 +273,8 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
         const long long nmin = min(q, w);
         const long long s_est = min((long long)fc.a * bh * fc.est_pct / 100, 32767ll);
         const long long L = s_est > 0 ? max_gap_bases(nmin, fc.a, (int)s_est, fc.go, fc.ge) : -1;
-        bool go_on = L >= 0, evidence_only = false;
+        bool go_on = L >= 0, evidence_only = false, use_band = false;
+        long long band_lo = 0, band_hi = 0;
         int m_old = 0, m_band = 0;
         long long c0 = 0, c1 = w - 1;
         uint32_t noise = 0u;
@@ -297,18 +320,57 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
             // be told from the noise
             const bool told_apart = m_old <= 255 && flt_hits_floor(fc, (long long)fc.a * bh, nmin) > (long long)noise;
             go_on = told_apart && (c1 - c0 + 1) * 10 <= 7ll * w;
+            if (fc.band && told_apart) {
+                // the parallelogram pays when its strips compute clearly fewer cells than the whole window holds
+                const long long Dl = max(Dlo, 0ll), Dh = min(Dhi, (long long)q + w - 2), wd = Dh - Dl + 1;
+                band_lo = Dl - (q - 1);
+                band_hi = Dh - (q - 1);
+                const int v = band_best_variant(q, w, wd, 0);
+                use_band = m_band <= kFltBandMaxBins && band_cells(q, w, wd, v) * 10 <= 6ll * q * w;
+                go_on = use_band;
+            }
             // A pair that sweeps its whole window anyway (long query in a short window) can still have the gap bases of its
             // alignments bounded by the hits, which is what the reverse pass's band is made of: keep the certificate data.
             evidence_only = told_apart && !go_on;
         }
         if (lane == 0) {
-            if (go_on) { r.c0 = (int32_t)c0; r.wlen = (int32_t)(c1 - c0 + 1); r.margin_bins = m_band | (m_old << 8); r.noise = (int32_t)noise; }
+            if (go_on && use_band) {  // (c0, wlen stay the whole window: what an unproven pair falls back to)
+                r.margin_bins = kFltBand | m_band | (m_old << 8); r.noise = (int32_t)noise; r.dlo = (int32_t)band_lo; r.dhi = (int32_t)band_hi;
+            } else if (go_on) { r.c0 = (int32_t)c0; r.wlen = (int32_t)(c1 - c0 + 1); r.margin_bins = m_band | (m_old << 8); r.noise = (int32_t)noise; }
             else if (evidence_only) { r.margin_bins = kFltWholeWindow | m_band | (m_old << 8); r.noise = (int32_t)noise; }
             rec[p] = r;
             if (counters) atomicAdd(counters + (go_on ? 0 : 1), 1ull);
         }
         __syncwarp();
     }
+}
+
+// Bins the kFltBand pairs of a chunk for the banded forward kernel: slot = strip-height variant, kBandVariants = not banded;
+// inside a slot the costly pairs come first. Also counts the cells those kernels will compute (cell_counts[1]).
+__global__ void band_keys_kernel(int n, const int64_t* __restrict__ seq_off, const int64_t* __restrict__ ref_off,
+                                 const FilterRec* __restrict__ rec, int few_pairs, uint32_t* __restrict__ keys, int* __restrict__ vals,
+                                 int* __restrict__ hist, unsigned long long* __restrict__ cell_counts) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long cells = 0;
+    if (p < n) {
+        const FilterRec r = rec[p];
+        int slot = kBandVariants;
+        uint32_t k2 = 0xFFFFFu;
+        if (r.margin_bins & kFltBand) {
+            const int q = (int)(seq_off[p + 1] - seq_off[p]), w = (int)(ref_off[p + 1] - ref_off[p]);
+            const long long wd = (long long)r.dhi - r.dlo + 1;
+            slot = band_best_variant(q, w, wd, few_pairs);
+            cells = (unsigned long long)band_cells(q, w, wd, slot);
+            const unsigned long long c = cells >> 10;
+            k2 = 0xFFFFFu - (uint32_t)(c > 0xFFFFFull ? 0xFFFFFull : c);
+        }
+        keys[p] = ((uint32_t)slot << 20) | k2;
+        vals[p] = p;
+        atomicAdd(&hist[slot], 1);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
+    if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cell_counts + 1, cells);
 }
 
 // After the sub-window forward pass: is the score it found a proof (see the header)? done[p] = 1 keeps the result,
@@ -323,6 +385,7 @@ __global__ void filter_certify_kernel(int n, const int64_t* __restrict__ seq_off
     if (r.margin_bins == 0) { done[p] = 1; return; }  // the first pass already swept the whole window, nothing to prove
     const bool whole = (r.margin_bins & kFltWholeWindow) != 0;  // swept the whole window; only the gap bound is sought
     const int m_band = whole ? 1 << 20 : r.margin_bins & 0xFF, m_old = (r.margin_bins >> 8) & 0xFF;
+    // (a kFltBand pair was swept by the banded forward kernel over bins [b - m_band, b + 1 + m_band]: the same test)
     const long long q = seq_off[p + 1] - seq_off[p], w = ref_off[p + 1] - ref_off[p];
     const long long nmin = q < w ? q : w;
     const int4 f = fwd[p];
@@ -344,7 +407,7 @@ __global__ void filter_certify_kernel(int n, const int64_t* __restrict__ seq_off
     } else if (whole) {
         // (the forward result is the full sweep's; the record stays as it is, without a gap bound)
     } else {
-        r.c0 = 0; r.wlen = (int32_t)w; r.margin_bins = 0; r.noise = 0; r.gap_bound = -1;
+        r.c0 = 0; r.wlen = (int32_t)w; r.margin_bins = 0; r.noise = 0; r.gap_bound = -1; r.dlo = r.dhi = 0;
         rec[p] = r;
         if (counters) atomicAdd(counters + 2, 1ull);
     }

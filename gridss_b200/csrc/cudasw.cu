@@ -164,6 +164,10 @@ struct cudasw {
     bool filter_always = false;         // CUDASW_FILTER=2: also for chunks of less than two waves of forward CTAs (tests)
     std::vector<char> chunk_filter;     // per chunk: the filter runs (scan_batch)
     DevBuf<FilterRec> frec;
+    DevBuf<uint32_t> fb_ring[kBandVariants];  // banded forward pass: per-group boundary rings of every strip-height launch
+    int* d_band_slots = nullptr;              // (start, count) per slot of that pass
+    DevBuf<uint32_t> bkeys, bkeys_alt;        // its sort keys / job lists (per chunk range, like keys / vals)
+    DevBuf<int> bvals, bvals_alt;
     DevBuf<uint32_t> fhc;  // per pair: hits of the core bins extended by j bins either side, j < kFltHc
     DevBuf<uint8_t> fdone;
     DevBuf<int> fwd_slots2;
@@ -342,6 +346,7 @@ extern "C" int cudasw_create_ex(const cudasw_scoring* s, int device, int tie_bre
     if ((e = cudaMalloc(&h->d_hist, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_rev_slots, 64 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_hist2, 256 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
+    if ((e = cudaMalloc(&h->d_band_slots, 32 * sizeof(int))) != cudaSuccess) return fail(cudaGetErrorString(e));
     if ((e = cudaMalloc(&h->d_fcount, 4 * sizeof(unsigned long long))) != cudaSuccess) return fail(cudaGetErrorString(e));
     cudaMemset(h->d_fcount, 0, 4 * sizeof(unsigned long long));
     h->fc = make_filter_const(sc.match, sc.mismatch, sc.ambiguous, sc.gap_open, sc.gap_extend);
@@ -350,6 +355,10 @@ extern "C" int cudasw_create_ex(const cudasw_scoring* s, int device, int tie_bre
         const char* fe = getenv("CUDASW_FILTER");  // 0: every pair sweeps its whole window (the pre-filter pipeline)
         h->use_filter = h->fc.ok && !(fe && atoi(fe) == 0);
         h->filter_always = fe && atoi(fe) == 2;
+        // CUDASW_BAND=1 (experiment, measured slower): certifiable pairs sweep their diagonal band with the strip
+        // kernels of the reverse pass run forwards, instead of a column range with the wavefront kernels
+        const char* be = getenv("CUDASW_BAND");
+        h->fc.band = be && atoi(be) == 1;
         if ((e = cudaFuncSetAttribute(filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kFltWarps * kFltSmemPerWarp))) != cudaSuccess)
             return fail(cudaGetErrorString(e));
     }
@@ -438,8 +447,10 @@ extern "C" void cudasw_destroy(cudasw_t* h) {
     h->hom_qs.release(); h->hom_ws.release(); h->hom_seq_off.release(); h->hom_ref_off.release(); h->hom_lit.release(); h->hom_res.release();
     if (h->d_hist) cudaFree(h->d_hist);
     if (h->d_hist2) cudaFree(h->d_hist2);
+    if (h->d_band_slots) cudaFree(h->d_band_slots);
+    for (auto& r : h->fb_ring) r.release();
     if (h->d_fcount) cudaFree(h->d_fcount);
-    h->frec.release(); h->fhc.release(); h->fdone.release(); h->fwd_slots2.release(); h->cub_tmp_fwd2.release();
+    h->frec.release(); h->fhc.release(); h->fdone.release(); h->bkeys.release(); h->bkeys_alt.release(); h->bvals.release(); h->bvals_alt.release(); h->fwd_slots2.release(); h->cub_tmp_fwd2.release();
     if (h->d_rev_slots) cudaFree(h->d_rev_slots);
     for (auto& r : h->rev_ring) r.release();
     if (h->d_pool) cudaFree(h->d_pool);
@@ -598,7 +609,7 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
     fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
                                                            keys.p + first, vals.p + first, d_hist, res.p + first, any_n,
                                                            wflags.p + first, anchor.p + first, d_strip + 2,
-                                                           flt ? frec.p + first : nullptr, nullptr);
+                                                           flt ? frec.p + first : nullptr, nullptr, 1, flt && fc.band ? 1 : 0);
     launches++;
     CK(cub::DeviceRadixSort::SortPairs(cub_tmp.p, cub_bytes, keys.p + first, keys_alt.p + first, vals.p + first,
                                        vals_alt.p + first, (int)n, 0, 32, st));
@@ -625,6 +636,38 @@ int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* 
     StripPool spool{strip_fwd.p, (unsigned long long)strip_fwd.cap, d_strip};
     const bool flt = use_filter && chunk_filter[ci];
     if (flt) io.sub = frec.p + first;
+    if (flt && fc.band) {
+        // Pairs with a diagonal band: binned by strip height on the device, swept by the persistent banded kernels (the
+        // forward flavour of the reverse pass's strips) side by side on the auxiliary streams. Uses the post stage's key
+        // arrays of this chunk's range (free until the reverse pass) and the second pass's sort workspace.
+        const int64_t n = cnt;
+        CK(cudaMemsetAsync(d_hist2, 0, 256 * sizeof(int), st));
+        band_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, frec.p + first, n < 4096 ? 1 : 0,
+                                                                bkeys.p + first, bvals.p + first, d_hist2, d_strip + 2);
+        size_t cub_bytes = cub_tmp_fwd2.cap;
+        CK(cub::DeviceRadixSort::SortPairs(cub_tmp_fwd2.p, cub_bytes, bkeys.p + first, bkeys_alt.p + first, bvals.p + first,
+                                           bvals_alt.p + first, (int)n, 0, 24, st));
+        slot_scan_kernel<<<1, 32, 0, st>>>(d_hist2, kBandVariants + 1, d_band_slots);
+        launches += 5;
+        CK(cudaEventRecord(fwd_set.fork_ev, st));
+        const long long kBandMaxWd = 32ll * (2 * kFltBandMaxBins + 2);
+        for (int v = 0; v < kBandVariants; v++) {
+            const int gpb = 128 / rev_variant_lanes(v);
+            long long half = std::min<long long>(band_variant_rows(v) + kBandMaxWd + 8, batch_max_w + 8);
+            long long blocks = std::min<long long>((n + gpb - 1) / gpb, 148 * 4);
+            const long long per_block = (long long)gpb * 2 * half * 4;
+            blocks = std::max<long long>(1, std::min<long long>(blocks, ((long long)1 << 30) / std::max<long long>(per_block, 1)));
+            CK(fb_ring[v].ensure((size_t)(blocks * gpb * 2 * half)));
+            cudaStream_t sx = fwd_set.aux[v % kAux];
+            if (v < kAux) CK(cudaStreamWaitEvent(sx, fwd_set.fork_ev, 0));
+            cusw::launch_fwd_band(v, (int)blocks, bvals_alt.p + first, d_band_slots + 2 * v, io, fwd.p + first, sc, fb_ring[v].p, (int)half, sx);
+            launches++;
+        }
+        for (int a = 0; a < kAux; a++) {
+            CK(cudaEventRecord(fwd_set.join_ev[a], fwd_set.aux[a]));
+            CK(cudaStreamWaitEvent(st, fwd_set.join_ev[a], 0));
+        }
+    }
     { int rc = launch_variants(fwd_set, false, vals_alt.p + first, io, nullptr, fwd.p + first, spool, &launches, fwd_counts[ci].data(),
                                fwd_slots.p + ci * (size_t)(2 * (2 * g_nvar + 1)), batch_maybe_n); if (rc != CUDASW_OK) return rc; }
     if (flt) {
@@ -642,7 +685,7 @@ int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* 
         CK(cudaMemsetAsync(d_hist2, 0, 256 * sizeof(int), st));
         fwd_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>((int)n, io.seq_off, io.ref_off, vt, max_rows, max_cols,
                                                                keys.p + first, vals.p + first, d_hist2, res.p + first, any_n,
-                                                               wflags.p + first, anchor.p + first, d_strip + 2, frec.p + first, fdone.p + first);
+                                                               wflags.p + first, anchor.p + first, d_strip + 2, frec.p + first, fdone.p + first, 0, 0);
         size_t cub_bytes = cub_tmp_fwd2.cap;
         CK(cub::DeviceRadixSort::SortPairs(cub_tmp_fwd2.p, cub_bytes, keys.p + first, keys_alt.p + first, vals.p + first,
                                            vals_alt.p + first, (int)n, 0, 32, st));
@@ -1065,10 +1108,10 @@ void cudasw::scan_batch(const std::vector<std::pair<int64_t, int64_t>>& ranges, 
     // alone (C1 10 k pairs = 3 G cells: 1.26 against 0.76 ms; C2 5 k pairs = 6 G cells: 2.13 against 1.37 ms; C3 10 k
     // pairs = 21 G cells: 15.4 against 33.4 ms).
     chunk_filter.assign(ranges.size(), 0);
-    // Nor does it pay when the windows are hardly longer than the queries (BreakpointHomology's 600 x 620: the column range
-    // a band can reach is the whole window, every pair would be passed on after the filter kernel had looked at it).
+    // Nor does the column-range flavour (CUDASW_BAND=0) pay when the windows are hardly longer than the queries
+    // (BreakpointHomology's 600 x 620: the columns a band can reach are the whole window); the diagonal-band kernel does.
     for (size_t ci = 0; ci < ranges.size(); ci++)
-        chunk_filter[ci] = use_filter && (filter_always || (chunk_cells[ci] >= 12e9 && chunk_w[ci] >= 1.5 * chunk_q[ci]));
+        chunk_filter[ci] = use_filter && (filter_always || (chunk_cells[ci] >= 12e9 && (fc.band || chunk_w[ci] >= 1.5 * chunk_q[ci])));
     batch_max_q = std::min<int64_t>(std::max<int64_t>(mq, 1), 32767);
     batch_max_w = std::min<int64_t>(std::max<int64_t>(mw, 1), (1 << 24));
 }
@@ -1179,7 +1222,7 @@ int cudasw::run(int64_t n, const uint8_t* d_seq_in, const int64_t* d_seq_off_in,
         if (use_filter) CK(cub_tmp_fwd2.ensure(cub_bytes + 16));
     }
     CK(fwd_slots.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1))));
-    if (use_filter) { CK(frec.ensure(n)); CK(fhc.ensure((size_t)n * kFltHc)); CK(fdone.ensure(n)); CK(fwd_slots2.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1)))); }
+    if (use_filter) { CK(frec.ensure(n)); CK(fhc.ensure((size_t)n * kFltHc)); CK(fdone.ensure(n)); CK(bkeys.ensure(n)); CK(bkeys_alt.ensure(n)); CK(bvals.ensure(n)); CK(bvals_alt.ensure(n)); CK(fwd_slots2.ensure(chunks.size() * (size_t)(2 * (2 * g_nvar + 1)))); }
     batch_maybe_n = !(packed && packed->refN == nullptr);
     if (!tb_pool.p) {
         size_t free_b = 0, total_b = 0;

@@ -89,10 +89,16 @@ __global__ void slot_scan_kernel(const int* __restrict__ hist, int nslots, int* 
 }
 #endif  // CUSW_MAIN_TU
 
-template <int G, int R, bool PROF>
+// FWD = true: the same strips run FORWARDS over the whole query inside the diagonal band [dlo, dhi] (d = column - row) that
+// the k-mer filter chose for the pair (io.sub, band_filter.cuh): the forward score pass of a banded pair, with the forward
+// pass's result convention (score, first column holding it, smallest row in that column). No target, no early stop; a DP
+// over a region that contains the band never exceeds the full DP and equals it on every path inside the band, which is all
+// the filter's certificate needs.
+template <int G, int R, bool PROF, bool FWD = false>
 __global__ void __launch_bounds__(128, score_min_blocks<R, PROF>())
 sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, PairIO io, const int4* __restrict__ fwd,
                    int4* __restrict__ out, ScoreConst sc, uint32_t* __restrict__ ring, int ring_half) {
+    constexpr int DIR = FWD ? 1 : -1;  // sequence bytes are read at base + DIR * index
     constexpr int GPB = 128 / G;
     constexpr int S = 2 * G * R;
     const int lig = threadIdx.x % G;
@@ -117,6 +123,7 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
     const bool active = gidx < njobs;
     int q = 0, w = 0, target = -1, pair = -1;
     long long dmax = 0;
+    long long dlo = 0, dhi = 0;  // the band: diagonals column - row in [dlo, dhi] (reverse pass: [-dmax, dmax])
     const uint8_t* qptr = io.enc_seq;
     const uint8_t* rptr = io.enc_ref;
 #ifdef CUSW_BOUNDS_CHECK
@@ -128,7 +135,17 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
         ck_r0 = io.enc_ref + io.ref_off[pr]; ck_r1 = io.enc_ref + io.ref_off[pr + 1];
     }
 #endif
-    if (active) {
+    if (active && FWD) {
+        pair = order[gidx];
+        const FilterRec fr = io.sub[pair];
+        q = (int)(io.seq_off[pair + 1] - io.seq_off[pair]);
+        w = (int)(io.ref_off[pair + 1] - io.ref_off[pair]);
+        qptr += io.seq_off[pair];
+        rptr += io.ref_off[pair];
+        dlo = fr.dlo;
+        dhi = fr.dhi;
+    }
+    if (active && !FWD) {
         pair = order[gidx];
         const int4 f = fwd[pair];
         target = f.x;
@@ -145,6 +162,8 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
         // an alignment of `target` inside q rows spans at most q + dmax columns
         const long long lim = (long long)q + dmax + 1;
         if (lim < w) w = (int)lim;
+        dlo = -dmax;
+        dhi = dmax;
     }
     unsigned long long key = 0;  // running (score, -col, -row) maximum of this thread's virtual lanes
     uint32_t* bnd_in = ring_a;
@@ -155,15 +174,19 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
     for (int strip = 0;; ++strip) {
     const int row0 = strip * S;
     int c0 = 0, wlen = 0;
-    bool has = active && row0 < q;
+    const bool alive = active && row0 < q;
+    bool has = alive;
     if (has) {
-        c0 = (int)max(0ll, (long long)row0 - dmax);
-        const long long c1 = min((long long)w - 1, (long long)row0 + S - 1 + dmax);
-        wlen = (int)(c1 - c0 + 1);
+        const long long c0l = max(0ll, (long long)row0 + dlo);
+        const long long c1 = min((long long)w - 1, (long long)row0 + S - 1 + dhi);
+        c0 = (int)min(c0l, (long long)w);
+        wlen = (int)(c1 - c0l + 1);
         if (wlen <= 0) { has = false; wlen = 0; }
         else if (q > S && wlen > ring_half) { has = false; wlen = 0; failed = true; }  // (multi-strip pairs only) the host sized the ring from the batch maxima
     }
-    if (!__any_sync(0xffffffffu, has)) break;
+    // (reverse pass: the first strip without columns is the last one that matters; forward: the band may start below row 0 of
+    //  the window's reach or end above the last rows, so only the rows decide)
+    if (!__any_sync(0xffffffffu, FWD ? alive : has)) break;
 
     uint32_t Q[R], QB[PROF ? R : 1];
     {
@@ -171,10 +194,10 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
 #pragma unroll
         for (int k = 0; k < R; k++) {
             const int a = r0 + k, b = r0 + R + k;
-            if (has && a < q) CUSW_CHECK_PTR(qptr - (int64_t)a, ck_q0, ck_q1, "query row (reverse)");
-            if (has && b < q) CUSW_CHECK_PTR(qptr - (int64_t)b, ck_q0, ck_q1, "query row (reverse)");
-            const uint32_t qa = (has && a < q) ? (uint32_t)qptr[-(int64_t)a] : kQueryPad;
-            const uint32_t qb = (has && b < q) ? (uint32_t)qptr[-(int64_t)b] : kQueryPad;
+            if (has && a < q) CUSW_CHECK_PTR(qptr + (int64_t)a * DIR, ck_q0, ck_q1, "query row (band)");
+            if (has && b < q) CUSW_CHECK_PTR(qptr + (int64_t)b * DIR, ck_q0, ck_q1, "query row (band)");
+            const uint32_t qa = (has && a < q) ? (uint32_t)qptr[(int64_t)a * DIR] : kQueryPad;
+            const uint32_t qb = (has && b < q) ? (uint32_t)qptr[(int64_t)b * DIR] : kQueryPad;
             if (PROF) {
                 Q[k] = cptr[8 + (qa & 7u)];
                 QB[k] = cptr[8 + (qb & 7u)];
@@ -191,12 +214,12 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
     uint32_t pend = 0u;
     uint32_t Hout = cBB, Fout = 0u, Hdiag_top = cBB;
     uint32_t Rsel = kOut | (kOut << 8);
-    const uint8_t* rp = rptr - c0;  // local column cl of this strip = byte rp[-cl]
+    const uint8_t* rp = rptr + (int64_t)c0 * DIR;  // local column cl of this strip = byte rp[DIR * cl]
     int t_end = has ? wlen + 2 * G - 1 : 0;
     int t_end_warp = (__reduce_max_sync(0xffffffffu, t_end) + 1) & ~1;
     int c = -2 * lig;  // local column of the low virtual lane
-    if ((unsigned)c < (unsigned)wlen) CUSW_CHECK_PTR(rp - (int64_t)c, ck_r0, ck_r1, "window column (reverse)");
-    uint32_t rb_next = ((unsigned)c < (unsigned)wlen) ? (uint32_t)rp[-(int64_t)c] : kOut;
+    if ((unsigned)c < (unsigned)wlen) CUSW_CHECK_PTR(rp + (int64_t)c * DIR, ck_r0, ck_r1, "window column (band)");
+    uint32_t rb_next = ((unsigned)c < (unsigned)wlen) ? (uint32_t)rp[(int64_t)c * DIR] : kOut;
     const bool read_top = has && strip > 0 && lig == 0;
     const bool write_bot = has && lig == G - 1 && row0 + S < q;
     const int shift = c0 - p0;  // local column -> index into the previous strip's bottom row
@@ -220,8 +243,8 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
             rb_next = kOut;
             top_next = cBB & 0xFFFFu;
             if ((unsigned)cn < (unsigned)wlen) {
-                CUSW_CHECK_PTR(rp - (int64_t)cn, ck_r0, ck_r1, "window column (reverse)");
-                rb_next = (uint32_t)rp[-(int64_t)cn];
+                CUSW_CHECK_PTR(rp + (int64_t)cn * DIR, ck_r0, ck_r1, "window column (band)");
+                rb_next = (uint32_t)rp[(int64_t)cn * DIR];
                 if (read_top && cn + shift < plen) { CUSW_CHECK_PTR(bnd_in + cn + shift, ring_a, ck_b1, "ring read"); top_next = bnd_in[cn + shift]; }
             }
         }
@@ -296,7 +319,7 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
         step(HB, HA);
         // early stop (ssw.c:296): once a lane holds `target`, later lanes may still find it in an earlier column, so
         // run on until the last virtual lane has passed this column
-        if ((t & 2) == 2) {
+        if (!FWD && (t & 2) == 2) {
             const int tg = target + sc.B;
             const bool found = has && (((int)(best & 0xFFFFu) == tg) || ((int)(best >> 16) == tg));
             if (found) t_end = min(t_end, t + 1 + 2 * G + 1);
@@ -328,8 +351,10 @@ sw_rev_band_kernel(const int* __restrict__ order, const int* __restrict__ slot, 
         uint32_t* tmp = bnd_in; bnd_in = bnd_out; bnd_out = tmp;
         p0 = c0;
         plen = wlen;
+    } else if (FWD) {
+        plen = 0;  // a strip without columns leaves nothing above the next one
     }
-    {
+    if (!FWD) {
         // columns from the first one that reached `target` on cannot matter any more (later strips hold larger rows)
         unsigned long long kk = key;
 #pragma unroll

@@ -25,4 +25,23 @@ void launch_rev_band(int v, bool prof, int blocks, const int* order, const int* 
 #undef RB
 }
 
+// The forward flavour of the same strips (rev_band.cuh, FWD): the banded forward pass of the k-mer filter's pairs
+// (band_filter.cuh). Query-profile flavour only: the filter never takes a window that holds an N.
+template <int G>
+static void launch_fwd_one(int blocks, const int* order, const int* slot, PairIO io, int4* out, ScoreConst sc, uint32_t* ring, int ring_half,
+                           cudaStream_t st) {
+    sw_rev_band_kernel<G, kRevR, true, true><<<blocks, 128, 0, st>>>(order, slot, io, nullptr, out, sc, ring, ring_half);
+}
+
+void launch_fwd_band(int v, int blocks, const int* order, const int* slot, PairIO io, int4* out, ScoreConst sc, uint32_t* ring,
+                     int ring_half, cudaStream_t st) {
+    switch (v) {
+        case 0: launch_fwd_one<1>(blocks, order, slot, io, out, sc, ring, ring_half, st); break;
+        case 1: launch_fwd_one<2>(blocks, order, slot, io, out, sc, ring, ring_half, st); break;
+        case 2: launch_fwd_one<4>(blocks, order, slot, io, out, sc, ring, ring_half, st); break;
+        case 3: launch_fwd_one<8>(blocks, order, slot, io, out, sc, ring, ring_half, st); break;
+        default: launch_fwd_one<32>(blocks, order, slot, io, out, sc, ring, ring_half, st); break;
+    }
+}
+
 }  // namespace cusw

@@ -299,9 +299,11 @@ struct FilterRec {
     int32_t margin_bins;  // bins of margin either side of the core: m_band | (m_old << 8) [| kFltWholeWindow]
     int32_t noise;        // most hits in any run of m_old bins outside the band's core
     int32_t gap_bound;    // once certified: no alignment of the pair's score has more gap bases than this (-1: not known)
+    int32_t dlo, dhi;     // kFltBand: the diagonals (column - row) the banded forward kernel sweeps, inclusive
 };
 
 constexpr int32_t kFltWholeWindow = 1 << 30;  // FilterRec::margin_bins: the range is the whole window, the certificate only yields gap_bound
+constexpr int32_t kFltBand = 1 << 29;         // FilterRec::margin_bins: the pair's first forward pass is the banded kernel (rev_band.cuh, FWD)
 
 struct PairIO {
     const uint8_t* enc_seq;
@@ -430,23 +432,26 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
                                 int* __restrict__ hist, cudasw_result* __restrict__ res,
                                 const int* __restrict__ any_n, const uint8_t* __restrict__ wflags,
                                 const uint16_t* __restrict__ anchor, unsigned long long* __restrict__ cell_counts,
-                                const FilterRec* __restrict__ sub = nullptr, const uint8_t* __restrict__ done = nullptr) {
+                                const FilterRec* __restrict__ sub = nullptr, const uint8_t* __restrict__ done = nullptr, int first_call = 1,
+                                int skip_band = 0) {
     // sub: the k-mer filter's column ranges (band_filter.cuh): the forward pass sweeps ws = sub[p].wlen columns.
-    // done != nullptr: the second (full-window) pass after the filter: pairs with done[p] != 0 have nothing left to do.
+    // done != nullptr: pairs with done[p] != 0 have nothing left to do (their result is proven, band_filter.cuh).
+    // first_call: the chunk's first binning initialises the result records and counts its q x w cells.
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     // cell_counts: [0] sum of q*w, [1] cells the forward kernels compute (padded rows, fill/drain columns)
     unsigned long long my_cells = 0, my_padded = 0;
     int64_t q = 0, w = 0, ws = 0;
-    const bool skip = p < n && done && done[p];
+    // skip_band: pairs the filter gave a diagonal band are swept by the banded forward kernel first (rev_band.cuh, FWD)
+    const bool skip = p < n && ((done && done[p]) || (skip_band && sub && (sub[p].margin_bins & kFltBand)));
     bool banded = false;
     if (p < n) {
         q = seq_off[p + 1] - seq_off[p];
         w = ref_off[p + 1] - ref_off[p];
         ws = w;
         if (sub) { const FilterRec fr = sub[p]; ws = fr.wlen; banded = fr.margin_bins != 0 && !(fr.margin_bins & kFltWholeWindow); }
-        if (q > 0 && w > 0 && !skip) {
-            if (!done) my_cells = (unsigned long long)q * (unsigned long long)w;
-            if (q <= max_rows) {
+        if (q > 0 && w > 0) {
+            if (first_call) my_cells = (unsigned long long)q * (unsigned long long)w;
+            if (q <= max_rows && !skip) {
                 const int v0 = variant_of(vt, (int)q);
                 const unsigned long long strips = ((unsigned long long)q + vt.rows[v0] - 1) / vt.rows[v0];
                 my_padded = strips * (unsigned long long)vt.rows[v0] * (unsigned long long)(ws + 2 * vt.lanes[v0] - 1);
@@ -469,7 +474,7 @@ __global__ void fwd_keys_kernel(int n, const int64_t* __restrict__ seq_off,
     else if (q > max_rows || w > max_cols) { r.status = CUDASW_ETOOLARGE; v = 2 * vt.n; }
     else if (skip) v = 2 * vt.n;
     else v = variant_of(vt, (int)q) + ((*any_n != 0 && wflags[p]) ? vt.n : 0);
-    if (!done) res[p] = r;
+    if (first_call) res[p] = r;
     w = ws;
     // key = (slot : 7 | 0x1FFF - window length / 64 : 13 | seed anchor column / 4 : 12): inside a slot the LONGEST windows
     // come first, so the CTAs that run longest start first and a launch does not end in a tail of its slowest pairs

@@ -34,4 +34,8 @@ std::vector<Variant> collect_variants();
 void launch_rev_band(int v, bool prof, int blocks, const int* order, const int* slot, PairIO io, const int4* fwd, int4* out,
                      ScoreConst sc, uint32_t* ring, int ring_half, cudaStream_t st);
 
+// ... and their forward flavour: the banded forward pass of the pairs the k-mer filter gave a diagonal band (band_filter.cuh)
+void launch_fwd_band(int v, int blocks, const int* order, const int* slot, PairIO io, int4* out, ScoreConst sc, uint32_t* ring,
+                     int ring_half, cudaStream_t st);
+
 }  // namespace cusw

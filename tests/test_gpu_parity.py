@@ -819,3 +819,12 @@ def test_filter_other_scorings_on_off(synth, monkeypatch):
     for sc in ((2, -3, -1, 5, 2), (1, -1, -1, 2, 1), (3, -2, -2, 4, 0), (1, -4, -4, 0, 1), (5, -4, -4, 10, 1)):
         bad, r0, r1 = _digest_on_off(sb, so, rb, ro, monkeypatch, sc)
         assert bad.size == 0, (sc, bad[:5], r0[bad[:3]], r1[bad[:3]])
+
+
+@pytest.mark.parametrize("cfg,n", [(2, 30000), (3, 5000)])
+def test_filter_band_mode_identical(synth, monkeypatch, cfg, n):
+    """CUDASW_BAND=1: certified pairs sweep their diagonal band with the strip kernels run forwards (not the default)."""
+    monkeypatch.setenv("CUDASW_BAND", "1")
+    sb, so, rb, ro = synth.generate(cfg, n)
+    bad, r0, r1 = _digest_on_off(sb, so, rb, ro, monkeypatch)
+    assert bad.size == 0, (bad[:5], r0[bad[:3]], r1[bad[:3]])
