@@ -1560,19 +1560,44 @@ extern "C" int cudasw_reference_load(cudasw_t* h, int32_t n_contigs, const uint8
 // pipeline reports as a per-pair CUDASW_EINVAL (like an empty `ref`, SswJniAligner.java:48-50).
 static void window_offsets(const cudasw_t* h, int64_t n, const cudasw_window* win, const int64_t* win_off,
                            std::vector<int64_t>& ref_off) {
+    // window lengths, then their prefix sums; several threads for large batches (one serial pass over a million descriptors
+    // is milliseconds, on the critical path of every call)
     ref_off.assign((size_t)n + 1, 0);
     const int64_t ncontig = (int64_t)h->contig_off.size() - 1;
-    for (int64_t p = 0; p < n; p++) {
-        int64_t len = 0;
-        bool ok = win_off[p + 1] >= win_off[p];
-        for (int64_t s = win_off[p]; ok && s < win_off[p + 1]; s++) {
-            const cudasw_window& w = win[s];
-            if (w.contig < 0 || w.contig >= ncontig || w.start < 0 || w.end < w.start ||
-                w.end > h->contig_off[w.contig + 1] - h->contig_off[w.contig]) ok = false;
-            else len += w.end - w.start;
+    const int nt = (int)std::min<int64_t>(8, std::max<int64_t>(1, n / 65536));
+    std::vector<int64_t> part((size_t)nt + 1, 0);
+    auto lengths = [&](int t) {
+        const int64_t a = n * t / nt, b = n * (t + 1) / nt;
+        int64_t sum = 0;
+        for (int64_t p = a; p < b; p++) {
+            int64_t len = 0;
+            bool ok = win_off[p + 1] >= win_off[p];
+            for (int64_t s = win_off[p]; ok && s < win_off[p + 1]; s++) {
+                const cudasw_window& w = win[s];
+                if (w.contig < 0 || w.contig >= ncontig || w.start < 0 || w.end < w.start ||
+                    w.end > h->contig_off[w.contig + 1] - h->contig_off[w.contig]) ok = false;
+                else len += w.end - w.start;
+            }
+            sum += ok ? len : 0;
+            ref_off[p + 1] = sum;  // prefix inside the part
         }
-        ref_off[p + 1] = ref_off[p] + (ok ? len : 0);
-    }
+        part[(size_t)t + 1] = sum;
+    };
+    auto shift = [&](int t) {
+        const int64_t a = n * t / nt, b = n * (t + 1) / nt, base = part[(size_t)t];
+        if (base != 0)
+            for (int64_t p = a; p < b; p++) ref_off[p + 1] += base;
+    };
+    auto run_all = [&](auto&& fn) {
+        if (nt == 1) { fn(0); return; }
+        std::vector<std::thread> th;
+        for (int t = 1; t < nt; t++) th.emplace_back(fn, t);
+        fn(0);
+        for (auto& x : th) x.join();
+    };
+    run_all(lengths);
+    for (int t = 0; t < nt; t++) part[(size_t)t + 1] += part[(size_t)t];
+    run_all(shift);
 }
 
 extern "C" int cudasw_align_batch_windows(cudasw_t* h, int64_t n, const uint8_t* seq_blob, const int64_t* seq_off,
