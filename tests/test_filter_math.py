@@ -156,3 +156,35 @@ def test_bounds_hold_on_the_oracle_s_optimal_alignments(fm, oracle, synth):
             assert Lg <= gb.value and fm.fm_bins_of(Lg) <= mt <= m0, (p, S, n, Lg, gb.value, mt, m0, hits)
             checked += 1
     assert checked > 1000
+
+
+@pytest.fixture(scope="module")
+def fb():
+    src = os.path.join(HERE, "native", "filter_bruteforce.cu")
+    out_dir = os.path.join(HERE, "native", "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    so = os.path.join(out_dir, "libfb.so")
+    deps = [src, os.path.join(HERE, "..", "gridss_b200", "csrc", "band_filter.cuh"), os.path.join(HERE, "..", "gridss_b200", "csrc", "sw_kernels.cuh")]
+    if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
+        subprocess.check_call([NVCC, "-O2", "-std=c++17", "-w", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-shared", "-o", so, src])
+    lib = ctypes.CDLL(so)
+    lib.fb_run.argtypes = [ctypes.c_uint64] + [ctypes.c_int] * 8 + [ctypes.POINTER(ctypes.c_longlong)]
+    return lib
+
+
+@pytest.mark.parametrize("sc", [(1, -4, -4, 6, 1), (2, -3, -1, 5, 2), (1, -1, -1, 2, 1), (5, -4, -4, 10, 1), (1, -6, -2, 7, 1), (1, -4, -4, 6, 3)])
+def test_certified_range_equals_the_full_sweep_by_brute_force(fb, sc):
+    """The theorem itself on small instances (tests/native/filter_bruteforce.cu): whenever the certificate holds for the score
+    found inside the column range, (score, first column, smallest row) of the range equal those of the whole matrix; and a
+    range never scores above the whole. Exact and mutated copies, two copies at equal score (ties), decoys placed first,
+    tandem repeats, indel-heavy copies, two-letter noise, half-noise queries, N in the query."""
+    out = (ctypes.c_longlong * 5)()
+    tried = certified = 0
+    for seed, qmax, wmax in ((1, 60, 300), (2, 140, 700), (3, 300, 1500)):
+        assert fb.fb_run(seed, 1600, *sc, qmax, wmax, out) == 0
+        assert out[2] == 0 and out[3] == 0, (sc, seed, list(out))
+        tried += out[0]
+        certified += out[1]
+    assert tried > 1000
+    if sc == (1, -4, -4, 6, 1):
+        assert certified > 500, (tried, certified)  # the default scoring certifies most planted copies
