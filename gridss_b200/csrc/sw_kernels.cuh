@@ -738,9 +738,17 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
     // Chains pay when most of the sweep is away from the alignment (measured, profiles/chain_sweep_r01j.txt): they are
     // switched off for warps whose shortest window is below CUSW_CHAIN_GATE times the rows of a group.
     int t_hi = 0;
-    if (CHAIN) {
+    int t_hb = 0;           // steps [2G, t_hb) are interior in the same sense, whatever the gate says (busy steps, see bstep)
+    bool was_full = false;  // warp-uniform: the last general step took the full recurrence
+#ifndef CUSW_NO_BUSY  // A/B switch
+    constexpr bool BUSY = PROF && !REV && !MULTI;
+#else
+    constexpr bool BUSY = false;
+#endif
+    if (CHAIN || BUSY) {
         const int w_min = __reduce_min_sync(0xffffffffu, active ? w : 0);
-        t_hi = w_min >= CUSW_CHAIN_GATE * S ? w_min - 1 : 0;
+        t_hi = CHAIN && w_min >= CUSW_CHAIN_GATE * S ? w_min - 1 : 0;
+        t_hb = w_min - 1;
     }
 
     auto step = [&](uint32_t (&Ho)[R], uint32_t (&Hn)[R]) {
@@ -879,6 +887,7 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         ++c;
         ++tt;
         if (CHAIN) { chain = quiet && tt >= 2 * G && tt + 2 < t_hi; skipq = false; }
+        if (BUSY) was_full = !quiet;
     };
 
     // ---- chained quiet step. After a verified quiet step every F handed down is dead and every E of the warp
@@ -938,6 +947,70 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
         ++tt;
         return true;
     };
+    // ---- busy step: the full recurrence of `step` on interior columns, for the stretches where step after step is full (the
+    // alignment and the E/F tails it leaves behind: most steps of a filtered column range, every step of a squarish pair).
+    // No quiet attempt (the caller looks every other step whether one has become possible), no border reset and no range
+    // masks (interior), the window byte loaded unguarded, best / column tracking behind one test as in qstep.
+    auto bstep = [&](uint32_t (&Ho)[R], uint32_t (&Hn)[R]) {
+        uint32_t rH = __shfl_up_sync(0xffffffffu, Hout, 1, G);
+        uint32_t rF = __shfl_up_sync(0xffffffffu, Fout, 1, G);
+        if (lig == 0) { rH = cBB; rF = 0u; }
+        const uint32_t Hin = prmt(rH, Hout, 0x5432u);
+        uint32_t F = prmt(rF, Fout, 0x5432u);
+        const uint32_t rb = rb_next;
+        CUSW_CHECK_PTR(rptr + c + 1, ck_r0, ck_r1, "busy window column (c + 1)");  // unguarded by design: t_hb keeps it inside
+        rb_next = (uint32_t)rptr[c + 1];
+        Rsel = prmt(Rsel, rb, 0x3204u);
+        const uint32_t Rs = Rsel + 0x4400u;
+        uint32_t diag = Hdiag_top;
+        Hdiag_top = Hin;
+        uint32_t cm = cBB;
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const uint32_t s = prmt(Q[k], QB[PROF ? k : 0], Rs);
+            const uint32_t m = __vimax3_s16x2(E[k], F, cBB);
+            const uint32_t h = __viaddmax_s16x2(diag, s, m);
+            diag = Ho[k];
+            Hn[k] = h;
+            const uint32_t hg = h - cGO2;
+            E[k] = __viaddmax_s16x2(E[k], cNGE2, hg);
+            F = __viaddmax_s16x2(F, cNGE2, hg);
+            if (k & 1) cm = __vimax3_s16x2(cm, Hn[k - 1], h);
+        }
+        if (R & 1) cm = __vmaxs2(cm, Hn[R - 1]);
+        Emax = __viaddmax_s16x2(Emax, cNGE2, cm - cGO2);
+#ifdef CUSW_STEP_STATS
+        if ((threadIdx.x & 31) == 0) atomicAdd((unsigned long long*)(sc.pool_dev + 512) + 2, 1ull);
+#endif
+        Hout = Hn[R - 1];
+        Fout = F;
+        const uint32_t nb = __vmaxs2(best, cm);
+        const uint32_t changed = nb ^ best;
+        if ((changed | pend) != 0u) {
+            const bool imp_lo = (changed & 0xFFFFu) != 0u, imp_hi = (changed >> 16) != 0u;
+            const bool due_lo = (pend & 0xFFFFu) != 0u && !imp_lo, due_hi = (pend >> 16) != 0u && !imp_hi;
+            if (due_lo || due_hi) {
+                const uint32_t cnt = first_row_of(Ho, best, cBB);
+                if (due_lo) row_lo = (int)(cnt & 0xFFFFu);
+                if (due_hi) row_hi = (int)(cnt >> 16);
+            }
+            if (imp_lo) col_lo = c;
+            if (imp_hi) col_hi = c - 1;
+            pend = changed;
+            best = nb;
+        }
+        ++c;
+        ++tt;
+    };
+    // full steps tend to come in long runs: stay on the lean twin while the columns are interior, and look every other step
+    // whether every E of the warp and every F handed down has died (then `step` may try a quiet one)
+    auto busy_run = [&]() {
+        while (tt >= 2 * G && tt + 2 < t_hb) {
+            bstep(HA, HB);
+            bstep(HB, HA);
+            if (__all_sync(0xffffffffu, __vimax3_s16x2(Emax, Fout, cBB) == cBB)) break;
+        }
+    };
     if (CHAIN) {
         while (tt < t_end_warp) {
             if (chain) {
@@ -972,6 +1045,17 @@ sw_score_kernel(const int* __restrict__ order, int njobs, PairIO io, const int4*
             // (a realigned chain makes the step count odd: the extra step at the end only sees pad columns)
             step(HA, HB);
             step(HB, HA);
+            if (BUSY && was_full) {
+                busy_run();
+                chain = false;
+                skipq = false;
+            }
+        }
+    } else if (BUSY) {
+        while (tt < t_end_warp) {
+            step(HA, HB);
+            step(HB, HA);
+            if (was_full) busy_run();
         }
     } else
     for (int t = 0; t < t_end_warp; t += 2) {
