@@ -12,12 +12,12 @@
 //       symbol), hence P passes through at least M - (k-1)(X + g + 1) hits. Minimised over (1) - a fractional knapsack
 //       with one budget, solved in closed form by flt_hits_floor() - that is T(S0), non-decreasing in S0;
 //   (3) the diagonals j - i it visits span at most Lg <= L(S0) = max_gap_bases(n, a, S0, go, ge) (the bound the banded
-//       reverse pass rests on, rev_band.cuh), i.e. they touch at most m(S0) = ceil(L / 32) + 1 consecutive bins of 32.
+//       reverse pass rests on, rev_band.cuh), i.e. they touch at most m(S0) = ceil(L / W) + 1 consecutive bins of W = 16 diagonals.
 // The filter counts ALL hits of the pair per diagonal bin (never fewer: query k-mers are chained, not hashed away),
-// picks the densest bin pair [b, b+1], a margin of m_r bins either side, and runs the forward pass on the columns
-// [c0, c1] that the diagonals of bins [b - m_r, b + 1 + m_r] can reach, which gives a true score S0 (a DP over a
+// picks the densest bin pair [b, b+1], calls it and c = kFltCore bins either side of it the CORE [b-c, b+1+c], adds a margin of
+// m_r - 1 bins either side, and runs the forward pass on the columns [c0, c1] that the diagonals of those bins can reach, which gives a true score S0 (a DP over a
 // sub-rectangle never exceeds the full DP). If m(S0) <= m_r and every run of m_r bins that lies outside
-// [b - 1, b + 2] holds fewer than T(S0) hits ("noise"), then a path of score >= S0 that leaves the band would have to
+// the core holds fewer than T(S0) hits ("noise"), then a path of score >= S0 that leaves the band would have to
 // collect >= T(S0) hits inside a window of m(S0) bins that is not inside the band - there is none. So every cell whose
 // true H is >= S0 is reached by paths inside the computed rectangle only: its value there is exact, the maximum is the
 // true maximum and the set of cells holding it - all the reference's tie-break (first column, then smallest row,
@@ -27,8 +27,8 @@
 // bases, so M <= hits(P) + (k-1)(X + g + 1); with (1): S0 <= a hits(P) + a(k-1) + X (a(k-1) - p) + g (a(k-1) - go)
 // - ge (Lg - g), and X <= Xmax(S0) = (a n - S0) / (p + a) (from M + X <= n and a M >= S0 + p X). When go > a(k-1) and
 // ge > 0 that bounds the gap bases of P by its hits: Lg <= R / min(go - a(k-1), ge), R = a hits(P) + a(k-1) - S0 +
-// max(0, a(k-1) - p) Xmax. A path whose bins all lie outside the core [b-1, b+2] is excluded by the noise test above; any
-// other path spanning m bins lies inside bins [b-1-(m-1), b+2+(m-1)], whose hit total hc(m-1) bounds hits(P). Starting
+// max(0, a(k-1) - p) Xmax. A path whose bins all lie outside the core is excluded by the noise test above; any
+// other path spanning m bins lies inside bins [b-c-(m-1), b+1+c+(m-1)], whose hit total hc(m-1) bounds hits(P). Starting
 // from m = m(L(S0)) and iterating m <- min(m, m(Lg bound from hc(m-1))) only ever applies sound implications, so its
 // fixed point m_t bounds the bins of EVERY path of score >= S0, and the band only needs a margin of m_t bins. The same
 // bound on Lg (gap_bound) narrows the band of the reverse pass (rev_band.cuh), whose paths are alignment paths of
@@ -40,9 +40,16 @@ namespace cusw {
 
 constexpr int kFltK = 6;                      // k-mer length: 4^6 direct-mapped heads
 constexpr int kFltHeads = 1 << (2 * kFltK);
-constexpr int kFltBinShift = 5;               // 32 diagonals per bin
-constexpr int kFltMaxBins = 1024;             // q + w - 1 <= 32 * 1024 diagonals
-constexpr int kFltMaxQ = 2040;                // chain links are 16 bit; a bin then holds at most 32 * 2040 hits
+#ifndef CUSW_FLT_BIN_SHIFT  // A/B switch
+#define CUSW_FLT_BIN_SHIFT 4
+#endif
+constexpr int kFltBinShift = CUSW_FLT_BIN_SHIFT;  // 16 diagonals per bin (32 at first: C2's column ranges were 12 % longer)
+constexpr int kFltBinW = 1 << kFltBinShift;
+// The core: the densest pair of adjacent bins [b, b + 1] and kFltCore bins either side of it, 96 diagonals in all (an
+// alignment with a 50-base indel still has its hits inside). Everything outside it is "noise" to the certificate.
+constexpr int kFltCore = kFltBinShift == 5 ? 1 : 2;
+constexpr int kFltMaxBins = 32768 >> kFltBinShift;  // q + w - 1 <= 32 k diagonals
+constexpr int kFltMaxQ = 2040;                // chain links are 16 bit; a bin then holds at most 16 * 2040 hits
 constexpr int kFltWarps = 4;                  // pairs per CTA of filter_kernel
 constexpr size_t kFltSmemPerWarp = kFltHeads * 2 + 2048 * 2 + kFltMaxBins * 2;  // heads, links, bins: 16 bit each (14 KB at most)
 // The launch sizes the links and bins for the batch's longest query / most diagonals (the host knows both), so that short
@@ -50,7 +57,7 @@ constexpr size_t kFltSmemPerWarp = kFltHeads * 2 + 2048 * 2 + kFltMaxBins * 2;  
 struct FilterSmem { int link_cap, bins_cap; };  // entries; both multiples of 64
 __host__ __device__ __forceinline__ size_t flt_smem_per_warp(FilterSmem m) { return (size_t)kFltHeads * 2 + (size_t)m.link_cap * 2 + (size_t)m.bins_cap * 2; }
 inline FilterSmem make_filter_smem(long long max_q, long long max_w) {
-    long long lc = std::min<long long>(std::max<long long>(max_q, 64), 2048), bc = std::min<long long>((max_q + max_w) / 32 + 4, kFltMaxBins);
+    long long lc = std::min<long long>(std::max<long long>(max_q, 64), 2048), bc = std::min<long long>((max_q + max_w) / kFltBinW + 4, kFltMaxBins);
     FilterSmem m;
     m.link_cap = (int)((lc + 63) & ~63ll);
     m.bins_cap = (int)std::min<long long>((bc + 63) & ~63ll, kFltMaxBins);
@@ -67,7 +74,8 @@ struct FilterConst {
     int band;            // 1: certifiable pairs take the banded forward kernel (a parallelogram of diagonals); 0: the column
                          // range [c0, c1] through the wavefront kernels (a rectangle)
 };
-constexpr int kFltBandMaxBins = 15;  // widest margin the banded forward kernel takes: 32 (2 * 15 + 2) = 1024 diagonals
+constexpr int kFltBandMaxWd = 1024;  // widest band the banded forward kernel takes (its rings are sized for it)
+constexpr int kFltBandMaxBins = (kFltBandMaxWd / kFltBinW - 2 - 2 * kFltCore) / 2 + 1;  // the margin that gives that width
 // Cells the banded forward kernel computes for a pair: its strips of S rows each sweep S + Wd - 1 columns.
 constexpr int kBandVariants = 5;  // strips of 32, 64, 128, 256, 1024 rows (rev_band.cuh)
 __host__ __device__ __forceinline__ int band_variant_rows(int v) { return v == 0 ? 32 : v == 1 ? 64 : v == 2 ? 128 : v == 3 ? 256 : 1024; }
@@ -116,8 +124,8 @@ __host__ __device__ __forceinline__ long long flt_hits_floor(const FilterConst& 
     if (num % den != 0 && num < 0) --t;
     return t;
 }
-// m(L): bins of 32 diagonals that a window of L + 1 consecutive diagonals can touch
-__host__ __device__ __forceinline__ int flt_bins_of(long long L) { return (int)((L + 31) >> kFltBinShift) + 1; }
+// m(L): bins that a window of L + 1 consecutive diagonals can touch
+__host__ __device__ __forceinline__ int flt_bins_of(long long L) { return (int)((L + kFltBinW - 1) >> kFltBinShift) + 1; }
 
 // The evidence iteration (header): hc(j) = hits in the core bins extended by j bins either side. Starts from m0 bins (from the
 // worst-case gap bound L0), returns the fixed point m_t and leaves the gap-base bound that goes with it in *gap_bound.
@@ -140,7 +148,7 @@ __host__ __device__ __forceinline__ int flt_tight_bins(const FilterConst& f, lon
 
 #ifdef CUSW_MAIN_TU
 // One warp per pair. Shared memory per warp: heads[4^k] (first query row + 1 of every k-mer), link[row] (next row with
-// the same k-mer), bins[diagonal / 32]; all 16 bit.
+// the same k-mer), bins[diagonal / kFltBinW]; all 16 bit.
 __global__ void __launch_bounds__(32 * kFltWarps)
 filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __restrict__ wflags, FilterConst fc,
               FilterRec* __restrict__ rec, uint32_t* __restrict__ hc_out, unsigned long long* __restrict__ counters, FilterSmem sm) {
@@ -148,13 +156,13 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     unsigned short* heads = reinterpret_cast<unsigned short*>(flt_smem + (size_t)wib * flt_smem_per_warp(sm));
     unsigned short* link = heads + kFltHeads;
-    uint32_t* bins2 = reinterpret_cast<uint32_t*>(link + sm.link_cap);  // two 16-bit counters per word (a bin holds <= 32 * kFltMaxQ hits)
+    uint32_t* bins2 = reinterpret_cast<uint32_t*>(link + sm.link_cap);  // two 16-bit counters per word (a bin holds <= kFltBinW * kFltMaxQ hits)
     uint32_t* psum = reinterpret_cast<uint32_t*>(heads);         // prefix sums of the bins: overlays the heads once the scan is over
     for (int p = blockIdx.x * kFltWarps + wib; p < n; p += gridDim.x * kFltWarps) {
         const int64_t qo = io.seq_off[p], ro = io.ref_off[p];
         const int q = (int)(io.seq_off[p + 1] - qo), w = (int)(io.ref_off[p + 1] - ro);
         FilterRec r{0, w, 0, 0, -1, 0, 0};
-        const bool eligible = fc.ok && q >= kFltK && w >= kFltK && q <= kFltMaxQ && (long long)q + w <= 32ll * kFltMaxBins - 64 &&
+        const bool eligible = fc.ok && q >= kFltK && w >= kFltK && q <= kFltMaxQ && (long long)q + w <= (long long)kFltBinW * kFltMaxBins - 64 &&
                               q <= sm.link_cap && ((q + w - 2) >> kFltBinShift) + 3 <= sm.bins_cap && !(*any_n != 0 && wflags[p]);
         if (!eligible) {  // warp-uniform
             if (lane == 0) rec[p] = r;
@@ -295,25 +303,26 @@ filter_kernel(int n, PairIO io, const int* __restrict__ any_n, const uint8_t* __
                 carry = __shfl_sync(0xffffffffu, v, 31);
             }
             __syncwarp();
-            // runs [bs, be) of m_old bins that lie entirely left of bin bb - 1 or right of bin bb + 2
+            // runs [bs, be) of m_old bins that lie entirely left or entirely right of the core [bb - kFltCore, bb + 1 + kFltCore]
             for (int bs = lane; bs < nb; bs += 32) {
                 const int be = min(bs + m_old, nb);
-                if (be - 1 <= bb - 2 || bs >= bb + 3) {
+                if (be - 1 <= bb - kFltCore - 1 || bs >= bb + kFltCore + 2) {
                     const uint32_t s = psum[be - 1] - (bs > 0 ? psum[bs - 1] : 0u);
                     noise = max(noise, s);
                 }
             }
             noise = __reduce_max_sync(0xffffffffu, noise);
-            // hc(lane): hits of the core bins [bb - 1, bb + 2] extended by `lane` bins either side
+            // hc(lane): hits of the core bins extended by `lane` bins either side
             uint32_t my_hc;
             {
-                const int lo = max(0, bb - 1 - lane), hi = min(nb - 1, bb + 2 + lane);
+                const int lo = max(0, bb - kFltCore - lane), hi = min(nb - 1, bb + 1 + kFltCore + lane);
                 my_hc = psum[hi] - (lo > 0 ? psum[lo - 1] : 0u);
             }
             if (lane < kFltHc) hc_out[(size_t)p * kFltHc + lane] = my_hc;
             long long gb;
             m_band = flt_tight_bins(fc, s_est, nmin, m_old, L, [&](int j) { return __shfl_sync(0xffffffffu, my_hc, j); }, &gb);
-            const long long Dlo = 32ll * (bb - m_band), Dhi = 32ll * (bb + 2 + m_band) - 1;  // diagonal index j - i + q - 1
+            // a path through the core spans at most m_band bins: bins [bb - kFltCore - (m_band - 1), bb + 1 + kFltCore + (m_band - 1)]
+            const long long Dlo = (long long)kFltBinW * (bb - kFltCore - m_band + 1), Dhi = (long long)kFltBinW * (bb + 1 + kFltCore + m_band) - 1;  // diagonal index j - i + q - 1
             c0 = max(0ll, Dlo - (q - 1));
             c1 = min((long long)w - 1, Dhi);
             // nothing to win when the range is most of the window; not worth trying when even the estimated score could not

@@ -598,7 +598,7 @@ int cudasw::pack_chunk(size_t ci, int64_t first, int64_t cnt, const uint8_t* d_s
         CK(cudaMemsetAsync(frec.p + first, 0xFF, (size_t)n * sizeof(FilterRec), st));
     if (flt) {
         // per pair: hits per diagonal bin -> the column range the forward pass sweeps first (band_filter.cuh)
-        const FilterSmem fsm = make_filter_smem(std::min<int64_t>(batch_max_q, kFltMaxQ), std::min<int64_t>(batch_max_w, 32ll * kFltMaxBins));
+        const FilterSmem fsm = make_filter_smem(std::min<int64_t>(batch_max_q, kFltMaxQ), std::min<int64_t>(batch_max_w, (int64_t)kFltBinW * kFltMaxBins));
         filter_kernel<<<(int)std::min<int64_t>((n + kFltWarps - 1) / kFltWarps, 148 * 2 * 8), 32 * kFltWarps, kFltWarps * flt_smem_per_warp(fsm), st>>>(
             (int)n, io, any_n, wflags.p + first, fc, frec.p + first, fhc.p + (size_t)first * kFltHc, d_fcount, fsm);
         launches++;
@@ -650,7 +650,7 @@ int cudasw::forward_chunk(size_t ci, int64_t first, int64_t cnt, const int64_t* 
         slot_scan_kernel<<<1, 32, 0, st>>>(d_hist2, kBandVariants + 1, d_band_slots);
         launches += 5;
         CK(cudaEventRecord(fwd_set.fork_ev, st));
-        const long long kBandMaxWd = 32ll * (2 * kFltBandMaxBins + 2);
+        const long long kBandMaxWd = kFltBandMaxWd;
         for (int v = 0; v < kBandVariants; v++) {
             const int gpb = 128 / rev_variant_lanes(v);
             long long half = std::min<long long>(band_variant_rows(v) + kBandMaxWd + 8, batch_max_w + 8);

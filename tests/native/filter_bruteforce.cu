@@ -119,13 +119,13 @@ extern "C" int fb_run(uint64_t seed, int n_pairs, int match, int mismatch, int a
         long long noise = 0;
         for (int bs = 0; bs < nb; bs++) {
             const int be = std::min(bs + m_old, nb);
-            if (be - 1 <= bb - 2 || bs >= bb + 3) noise = std::max(noise, ps[be] - ps[bs]);
+            if (be - 1 <= bb - kFltCore - 1 || bs >= bb + kFltCore + 2) noise = std::max(noise, ps[be] - ps[bs]);
         }
         uint32_t hc[kFltHc];
-        for (int j = 0; j < kFltHc; j++) { const int lo = std::max(0, bb - 1 - j), hi = std::min(nb - 1, bb + 2 + j); hc[j] = (uint32_t)(ps[hi + 1] - ps[lo]); }
+        for (int j = 0; j < kFltHc; j++) { const int lo = std::max(0, bb - kFltCore - j), hi = std::min(nb - 1, bb + 1 + kFltCore + j); hc[j] = (uint32_t)(ps[hi + 1] - ps[lo]); }
         long long gb;
         const int m_band = flt_tight_bins(fc, s_est, nmin, m_old, L, [&](int j) { return hc[j]; }, &gb);
-        const long long Dlo = 32ll * (bb - m_band), Dhi = 32ll * (bb + 2 + m_band) - 1;
+        const long long Dlo = (long long)kFltBinW * (bb - kFltCore - m_band + 1), Dhi = (long long)kFltBinW * (bb + 1 + kFltCore + m_band) - 1;
         const long long c0 = std::max(0ll, Dlo - (q - 1)), c1 = std::min<long long>(wl - 1, Dhi);
         // (the kernel also requires told_apart and a range below 70 % of the window before it bothers; the theorem does not)
         if (m_old > 255 || c1 < c0) continue;

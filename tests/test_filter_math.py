@@ -84,7 +84,7 @@ def test_native_functions_equal_the_python_model(fm):
     for L in list(range(0, 200)) + [1000, 4095, 4096, 4097]:
         assert fm.fm_bins_of(L) == F.bins_of(L)
         # a window of L + 1 consecutive diagonals never touches more bins than that, and some window touches as many
-        assert max((d + L) // 32 - d // 32 + 1 for d in range(64)) == F.bins_of(L)
+        assert max((d + L) // F.BIN - d // F.BIN + 1 for d in range(2 * F.BIN)) == F.bins_of(L)
 
 
 def _path_stats(seq, ref, r, cigar):

@@ -8,7 +8,8 @@ import sys
 import numpy as np
 
 K = 6
-BIN = 32
+BIN = 16
+CORE = 2  # bins either side of the densest pair that belong to the core
 EVIDENCE = True
 REV = []
 
@@ -114,7 +115,7 @@ def probe(cfg, n, sc=(1, -4, -4, 6, 1), est=0.8, est_t=1.0):
             continue
         kq, bq = kmers(qs)
         kw, bw = kmers(ws)
-        nb = ((q + w - 2) >> 5) + 1
+        nb = ((q + w - 2) // BIN) + 1
         cnt = np.zeros(nb + 2, np.int64)
         order = np.argsort(kq, kind="stable")
         ks = kq[order]
@@ -123,7 +124,7 @@ def probe(cfg, n, sc=(1, -4, -4, 6, 1), est=0.8, est_t=1.0):
         for j in np.flatnonzero((hi > lo) & ~bw):
             for i in order[lo[j] : hi[j]]:
                 if not bq[i]:
-                    cnt[(j - i + q - 1) >> 5] += 1
+                    cnt[(j - i + q - 1) // BIN] += 1
         pair = cnt[:-1] + cnt[1:]
         bstar = int(np.argmax(pair[:nb]))
         hstar = int(pair[bstar])
@@ -139,11 +140,11 @@ def probe(cfg, n, sc=(1, -4, -4, 6, 1), est=0.8, est_t=1.0):
         noise = 0
         for bs in range(0, nb):
             be = min(bs + m_r, nb)
-            if be - 1 <= bstar - 2 or bs >= bstar + 3:
+            if be - 1 <= bstar - CORE - 1 or bs >= bstar + CORE + 2:
                 noise = max(noise, int(cs[be] - cs[bs]))
         # evidence-based gap bound: a path through the core sees at most hc(j) hits when it spans j extra bins either side
         def hc(j):
-            lo, hi = max(0, bstar - 1 - j), min(nb - 1, bstar + 2 + j)
+            lo, hi = max(0, bstar - CORE - j), min(nb - 1, bstar + 1 + CORE + j)
             return int(cs[hi + 1] - cs[lo])
 
         def m_tight(S, m0):
@@ -168,7 +169,7 @@ def probe(cfg, n, sc=(1, -4, -4, 6, 1), est=0.8, est_t=1.0):
         m_old = m_r
         if EVIDENCE:
             m_r, _ = m_tight(S_est, m_old)
-        Dlo, Dhi = BIN * (bstar - m_r), BIN * (bstar + 2 + m_r) - 1
+        Dlo, Dhi = BIN * (bstar - CORE - m_r + 1), BIN * (bstar + 1 + CORE + m_r) - 1
         Dlo, Dhi = max(Dlo, 0), min(Dhi, q + w - 2)
         wd = Dhi - Dlo + 1
         c0, c1 = max(0, Dlo - (q - 1)), min(w - 1, Dhi)
