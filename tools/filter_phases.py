@@ -13,8 +13,11 @@ for cfg, n in runs:
     d = [torch.from_numpy(x).cuda() for x in (sb, so, rb, ro)]
     torch.cuda.synchronize()
     for flt in os.environ.get("EXP_FILTER", "1,0").split(","):
-        for est in os.environ.get("EXP_EST", "80").split(","):
-            os.environ["CUDASW_FILTER_EST"] = est
+        for est in os.environ.get("EXP_EST", "default").split(","):
+            if est == "default":
+                os.environ.pop("CUDASW_FILTER_EST", None)
+            else:
+                os.environ["CUDASW_FILTER_EST"] = est
             os.environ["CUDASW_FILTER"] = flt
             al = g.CudaAligner()
             for rep in range(3):
